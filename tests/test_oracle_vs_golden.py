@@ -1,0 +1,154 @@
+"""Pins the CPU oracle (oracle/dmnerf_oracle.py) to vectors produced by the unmodified
+reference (oracle/gen_golden.py, torch 2.11 CPU).  Elementwise/scan stages are bit-exact;
+GEMM-bearing stages allow 2e-5 because sgemm blocking depends on the host's thread count."""
+import numpy as np
+import torch
+
+import dmnerf_oracle as orc
+
+T = torch.from_numpy
+
+
+def same(a, b, tol=0.0):
+    a = a.detach().numpy() if isinstance(a, torch.Tensor) else a
+    if tol == 0.0:
+        np.testing.assert_array_equal(a, b)
+    else:
+        np.testing.assert_allclose(a, b, rtol=tol, atol=tol)
+
+
+def test_embed(golden):
+    g = golden("embed")
+    x = T(g["x"])
+    same(orc.embed(x, 10), g["pos"])
+    same(orc.embed(x, 4), g["dir"])
+    e = orc.embed(torch.tensor([[0.1, 0.2, 0.3]]), 10)[0]
+    ref = [0.1, 0.2, 0.3, np.sin(0.1), np.sin(0.2), np.sin(0.3), np.cos(0.1), np.cos(0.2), np.cos(0.3),
+           np.sin(0.2), np.sin(0.4), np.sin(0.6)]
+    np.testing.assert_allclose(e[:12].numpy(), np.array(ref, dtype=np.float32), rtol=1e-6)
+
+
+def test_mlp(golden):
+    for k in (32, 16, 93):
+        g = golden(f"mlp_k{k}")
+        p = orc.init_params(k, int(g["seed"]))
+        x = torch.cat([orc.embed(T(g["pts"]), 10), orc.embed(T(g["dirs"]), 4)], -1)
+        same(orc.mlp_forward(p, x), g["out"], 2e-5)
+
+
+def test_param_count():
+    assert sum(int(np.prod(s)) for s in orc.param_shapes(32).values()) == 698789
+
+
+def test_composite(golden):
+    for tag in ("c64", "f192", "k93", "k16"):
+        g = golden(f"composite_{tag}")
+        a = orc.render_train(T(g["raw"]), T(g["z"]), T(g["rays_d"]))
+        for got, key in zip(a, ("rgb", "weights", "depth", "ins")):
+            same(got, g[key])
+        b = orc.manipulator_render(T(g["raw"]), T(g["z"]), T(g["rays_d"]))
+        for got, key in zip(b, ("m_rgb", "m_weights", "m_depth", "m_ins")):
+            same(got, g[key])
+
+
+def test_composite_kat(golden):
+    g = golden("composite_kat")
+    rgb, w, depth, ins = orc.render_train(T(g["raw"]), T(g["z"]), T(g["rays_d"]))
+    same(rgb, g["rgb"]); same(w, g["weights"]); same(depth, g["depth"]); same(ins, g["ins"])
+    # closed forms
+    assert torch.all(w[0] == 0) and torch.all(rgb[0] == 0) and depth[0] == 0 and torch.all(ins[0] == 0.5)
+    assert w[1, 2] == 1.0 and w[1].sum() == 1.0 and depth[1] == g["z"][1, 2]
+    np.testing.assert_allclose(rgb[1].numpy(), torch.sigmoid(torch.tensor([0.3, -0.7, 1.1])).numpy(), rtol=1e-6)
+    assert w[2, -1] == 1.0          # 1e10 last interval -> alpha 1 for any sigma > 0
+    assert torch.all(w[3] == 0)      # zero-length ray direction
+
+
+def test_sample_pdf(golden):
+    g = golden("sample_pdf")
+    z, inds, cdf = orc.sample_pdf(T(g["bins"]), T(g["weights"]), 128, det=False, u=T(g["u"]), return_inds=True)
+    same(z, g["z_rand"]); same(inds, g["inds_rand"]); same(cdf, g["cdf"])
+    z, inds, _ = orc.sample_pdf(T(g["bins"]), T(g["weights"]), 128, det=True, return_inds=True)
+    same(z, g["z_det"]); same(inds, g["inds_det"])
+
+
+def _dm(g):
+    k = int(g["ins_num"])
+    pc = orc.init_params(k, int(g["seed_c"]), float(g["head_gain"]))
+    pf = orc.init_params(k, int(g["seed_f"]), float(g["head_gain"]))
+    rays = T(g["rays"])
+    zc = orc.z_val_sample(rays.shape[1], float(g["near"]), float(g["far"]), 64)
+    with torch.no_grad():
+        return orc.dm_nerf(rays, pc, pf, zc, perturb=float(g["perturb"]), n_importance=128,
+                           t_rand=T(g["t_rand"]), u=T(g["u"]))
+
+
+def test_dm_nerf(golden):
+    for tag in ("det_k32", "rand_k32", "det_k16"):
+        g = golden(f"dm_nerf_{tag}")
+        out = _dm(g)
+        same(out["z_vals_coarse"], g["z_vals_coarse"])
+        for key in ("rgb_fine", "rgb_coarse", "depth_fine", "depth_coarse", "ins_fine", "ins_coarse",
+                    "z_vals_fine"):
+            same(out[key], g[key], 1e-4)
+        np.testing.assert_allclose(out["raw_fine"].numpy(), g["raw_fine"], rtol=1e-3, atol=2e-3)
+
+
+def test_penalizer(golden):
+    for name in ("penalizer", "penalizer_empty"):
+        g = golden(name)
+        raw = T(g["raw"]).requires_grad_(True)
+        loss = orc.ins_penalizer(raw, T(g["z"]), T(g["depth"]), T(g["rays_d"]), float(g["tolerance"]), float(g["deta_w"]))
+        loss.backward()
+        same(loss, g["loss"], 1e-6)
+        same(raw.grad, g["d_raw"], 1e-7)
+        assert torch.all(raw.grad[..., :4] == 0)
+
+
+def test_exchanger(golden):
+    g = golden("exchanger")
+    ori = T(g["ori_raw"]).clone()
+    tars = [T(g["tar_raw0"]).clone(), T(g["tar_raw1"]).clone()]
+    o, _, lab, tlab = orc.exchanger(ori, tars, T(g["ori_acc"]), [T(g["tar_acc0"]), T(g["tar_acc1"])],
+                                    [int(m) for m in g["move_labels"]])
+    same(o, g["out_raw"]); same(lab, g["out_label"]); same(tlab, g["tar_label"])
+    assert o.data_ptr() == ori.data_ptr()          # in place, like the reference
+
+
+def test_manipulator(golden):
+    g = golden("manipulator")
+    pc = orc.init_params(32, int(g["seed_c"]), float(g["head_gain"]))
+    pf = orc.init_params(32, int(g["seed_f"]), float(g["head_gain"]))
+    with torch.no_grad():
+        rgb, ins, t_rgb, t_acc = orc.manipulator(
+            pc, pf, T(g["ori_rays"]), T(g["tar_rays"]), n_samples=64, n_importance=128, near=4.0, far=15.0,
+            target_label=[int(m) for m in g["target_label"]], us=[T(g["u0"]), T(g["u1"]), T(g["u2"])])
+    same(t_rgb, g["tar_rgb"], 1e-4); same(t_acc, g["tar_acc"], 1e-4)
+    same(rgb, g["final_rgb"], 1e-4); same(ins, g["final_ins"], 1e-4)
+
+
+def test_rays_k(golden):
+    g = golden("rays_k")
+    ro, rd = orc.get_rays_k(int(g["H"]), int(g["W"]), T(g["K"]), T(g["c2w"]))
+    same(ro, g["rays_o"]); same(rd, g["rays_d"])
+
+
+def test_train_grads(golden):
+    g = golden("train_grads")
+    pc = {k: v.requires_grad_(True) for k, v in orc.init_params(32, int(g["seed_c"])).items()}
+    pf = {k: v.requires_grad_(True) for k, v in orc.init_params(32, int(g["seed_f"])).items()}
+    rays = T(g["rays"])
+    zc = orc.z_val_sample(rays.shape[1], 4.0, 15.0, 64)
+    o = orc.dm_nerf(rays, pc, pf, zc, perturb=1.0, n_importance=128, t_rand=T(g["t_rand"]), u=T(g["u"]), is_train=True)
+    tr, ti = T(g["tgt_rgb"]), T(g["tgt_ins"])
+    loss = ((o["rgb_fine"] - tr) ** 2).mean() + ((o["rgb_coarse"] - tr) ** 2).mean()
+    loss = loss + ((o["ins_fine"] - ti) ** 2).mean() + ((o["ins_coarse"] - ti) ** 2).mean()
+    loss = loss + orc.ins_penalizer(o["raw_coarse"], o["z_vals_coarse"], o["depth_coarse"], rays[1], 0.05, 0.05)
+    loss = loss + orc.ins_penalizer(o["raw_fine"], o["z_vals_fine"], o["depth_fine"], rays[1], 0.05, 0.05)
+    loss.backward()
+    same(loss.reshape(1), g["loss"], 1e-5)
+    for tag, p in (("c", pc), ("f", pf)):
+        for name, v in p.items():
+            ref = g[f"{tag}.{name}.sub"]
+            got = v.grad.reshape(-1)[::97].numpy()
+            scale = max(float(g[f"{tag}.{name}.norm"]) / np.sqrt(v.numel()), 1e-12)
+            assert np.max(np.abs(got - ref)) <= 2e-3 * scale + 1e-9, (tag, name)
