@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- rays/sec of DM-NeRF's per-ray hot path on B200 (BASELINE.json metric).
+
+Workload at every N: DM-SR full-image render (BASELINE.json configs[1]): 640x480 = 307,200 rays,
+64 coarse + 128 fine samples per ray, K=32 instances, RGB + depth + instance map (+ uint8 labels),
+synthetic pose, random-init weights.  One "step" = one full frame per rank (weak scaling: each rank
+renders its own view of the sweep; rank 0 gathers the label maps).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode bf16|fp32] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput (rays already in HBM),
+`e2e` = same frame through the public API with pinned HOST ray buffers in and host results out,
+`roofline` = the dominant kernel (fused PE+MLP, fine pass) against the measured bf16 tensor peak,
+`cpu_baseline` = the CPU oracle port (torch CPU fp32, all host threads) on a bounded ray sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+from types import SimpleNamespace
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W, K_INS, SC, NIMP = 480, 640, 32, 64, 128
+NEAR, FAR = 4.0, 15.0
+N_RAYS = H * W
+MACS_PER_POINT = 691840 + 128 * K_INS            # algorithmic, padding not counted
+FLOP_PER_RAY = 2 * MACS_PER_POINT * (SC + SC + NIMP)
+
+
+def synth_camera(torch, view: int):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    focal = 0.5 * W / math.tan(0.5 * 0.6911)
+    Kmat = torch.tensor([[focal, 0, W / 2], [0, -focal, H / 2], [0, 0, -1]], dtype=torch.float32)
+    th, ph, rad = (37.0 + 45.0 * view) / 180 * math.pi, -65.0 / 180 * math.pi, 7.0
+    t = torch.eye(4); t[2, 3] = rad
+    rp = torch.tensor([[1, 0, 0, 0], [0, math.cos(ph), -math.sin(ph), 0], [0, math.sin(ph), math.cos(ph), 0], [0, 0, 0, 1]])
+    rt = torch.tensor([[math.cos(th), 0, -math.sin(th), 0], [0, 1, 0, 0], [math.sin(th), 0, math.cos(th), 0], [0, 0, 0, 1]])
+    flip = torch.tensor([[-1., 0, 0, 0], [0, 0, 1, 0], [0, 1, 0, 0], [0, 0, 0, 1]])
+    return Kmat, (flip @ rt.float() @ rp.float() @ t)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self._stop_evt.is_set():
+            try:
+                r = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5)
+                if r.returncode == 0 and r.stdout.strip():
+                    self.rows.append([c.strip() for c in r.stdout.strip().split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def summary(self):
+        self._stop_evt.set()
+        self.join(timeout=3)
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        reasons = []
+        for i, name in enumerate(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")):
+            if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows):
+                reasons.append(name)
+        mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_oracle_rays_per_s(torch, n_rays: int, repeats: int = 1):
+    """The oracle port (torch CPU fp32, reference op order) on a bounded sample of the same workload:
+    n_rays of the frame, tester.py-style chunk.  Returns (rays/s, cores, seconds)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import dmnerf_oracle as orc
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    pc, pf = orc.init_params(K_INS, 1), orc.init_params(K_INS, 2)
+    Kmat, c2w = synth_camera(torch, 0)
+    ro, rd = orc.get_rays_k(H, W, Kmat, c2w)
+    sel = torch.linspace(0, N_RAYS - 1, n_rays).long()
+    rays = torch.stack([ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel]], 0)
+    zc = orc.z_val_sample(n_rays, NEAR, FAR, SC)
+    best = None
+    with torch.no_grad():
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            orc.dm_nerf(rays, pc, pf, zc, perturb=0.0, n_importance=NIMP)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+    return n_rays / best, cores, best
+
+
+def run_reference(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = 2048
+    times = []
+    for i in range(args.warmup + args.steps):
+        rps, cores, dt = cpu_oracle_rays_per_s(torch, n)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1000 * sum(times) / len(times)
+    val = n / (ms / 1000)
+    sample = f"{n} rays of the 640x480 frame per step (oracle port, torch CPU fp32, {cores} threads)"
+    print(json.dumps({
+        "impl": "reference", "metric": "rays/sec render (64+128 samples/ray)", "value": val, "unit": "rays/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "DM-SR full-image render 640x480, 64+128 samples/ray, K=32 (bounded sample)"},
+        "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import dmnerf_oracle as orc
+    from dm_nerf_b200 import ops, _lib
+    from dm_nerf_b200.frame import render_pixels
+    from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
+    from dm_nerf_b200.parallel import gather_rows
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    mode = args.mode
+    if mode == "bf16" and _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) <= 0:
+        raise RuntimeError("bf16 tensor-core mode is not built")
+    ops.set_mode(mode)
+    mc, mf = DM_NeRF(8, 256, 63, 27, [4], K_INS), DM_NeRF(8, 256, 63, 27, [4], K_INS)
+    mc.load_state_dict(orc.init_params(K_INS, 1)); mf.load_state_dict(orc.init_params(K_INS, 2))
+    mc, mf = mc.to(dev), mf.to(dev)
+    pe, ve = get_embedder(10, 0)[0], get_embedder(4, 0)[0]
+    Kmat, c2w = synth_camera(torch, rank)                      # each rank renders its own view of the sweep
+    hwk = (H, W, Kmat)
+    ro, rd = ops.rays_k(H, W, Kmat, c2w, 0, N_RAYS, dev)
+    rays_dev = torch.stack([ro, rd], 0)
+    rays_host = rays_dev.cpu().pin_memory()
+    out = {"rgb": torch.empty((N_RAYS, 3), device=dev), "depth": torch.empty((N_RAYS,), device=dev),
+           "ins": torch.empty((N_RAYS, K_INS), device=dev), "labels": torch.empty((N_RAYS,), dtype=torch.uint8, device=dev)}
+    host_out = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in out.items() if k != "ins"}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    def frame(rays):
+        render_pixels(pe, ve, mc, mf, hwk, c2w, NEAR, FAR, SC, NIMP, rays=rays, chunk=args.chunk, out=out)
+        if world > 1:
+            gather_rows(out["labels"], N_RAYS * world)          # the final gather (rank 0 collects label maps)
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """max-over-ranks device time (ms) of `steps` calls, CUDA events on the launching stream."""
+        evs = []
+        sync()
+        for _ in range(steps):
+            flush.zero_()                                        # L2 flush between timed iterations
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            evs.append((a, b))
+        sync()
+        ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / steps
+
+    for _ in range(args.warmup):
+        frame(rays_dev)
+    sync()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ops.launches
+    with ops.KernelTimer() as kt:
+        ms_step = timed(lambda: frame(rays_dev), args.steps)
+    launches = (ops.launches - l0)
+    totals = kt.totals()
+
+    def e2e_step():
+        r = rays_host.to(dev, non_blocking=True)
+        frame(r)
+        for k in host_out:
+            host_out[k].copy_(out[k], non_blocking=True)
+    e2e_step(); sync()
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.summary()
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    mode_id = _lib.MODE_BF16 if mode == "bf16" else _lib.MODE_FP32
+    name = f"dmnerf_mlp_fwd[S={SC + NIMP},mode={mode_id}]"
+    n_launch, ms_kernel = totals.get(name, (0, 0.0))
+    rays_per_launch = min(args.chunk, N_RAYS)
+    roofline = None
+    if n_launch:
+        # achieved = algorithmic FLOPs per launch / mean launch duration (fine pass: 192 points per ray)
+        flops_total = 2.0 * MACS_PER_POINT * (SC + NIMP) * N_RAYS * args.steps
+        achieved = flops_total / (ms_kernel / 1000) / 1e12
+        peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": None, "kernel": name, "launches": n_launch, "ms_per_launch": ms_kernel / n_launch,
+                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback",
+                    "kernel_share_of_step": ms_kernel / (ms_step * args.steps)}
+    stage_ms = {k: round(v[1] / args.steps, 3) for k, v in totals.items()}
+
+    if rank == 0:
+        cpu = None
+        try:
+            rps, cores, secs = cpu_oracle_rays_per_s(torch, 2048)
+            cpu = {"value": rps, "unit": "rays/s", "cores": cores, "kind": "port",
+                   "sample": f"2048 of the frame's 307200 rays, one pass ({secs:.1f} s), oracle port torch CPU fp32"}
+        except Exception as e:  # pragma: no cover
+            cpu = {"value": None, "error": str(e)}
+        total_rays = N_RAYS * world
+        h2d = rays_host.numel() * 4
+        d2h = sum(v.numel() * v.element_size() for v in host_out.values())
+        print(json.dumps({
+            "metric": "rays/sec render (64+128 samples/ray)", "value": total_rays / (ms_step / 1000), "unit": "rays/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if mode == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": "DM-SR full-image render 640x480 = 307200 rays x (64+128) samples, K=32, "
+                                   "rgb+depth+instance map+labels, one frame per rank per step",
+                       "mode": mode, "chunk_rays": args.chunk, "l2": "flushed between timed iterations (256 MiB write)",
+                       "parallelism": f"rays/views sharded x{world}, final gather of label maps"},
+            "e2e": {"value": total_rays / (ms_e2e / 1000), "unit": "rays/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+            "stage_ms_per_step": stage_ms,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default=os.environ.get("DMNERF_BENCH_MODE", "auto"), choices=["auto", "bf16", "fp32"])
+    ap.add_argument("--chunk", type=int, default=32768)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    if args.mode == "auto":
+        from dm_nerf_b200 import _lib
+        args.mode = "bf16" if _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) > 0 else "fp32"
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:
+        # convenience: relaunch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

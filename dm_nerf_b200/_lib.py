@@ -1,0 +1,119 @@
+"""ctypes loader for libdmnerf_b200.so (the C-ABI in include/dmnerf_b200.h).
+
+There is no fallback: if the shared library has not been built, or a call returns a non-zero
+code, a RuntimeError is raised.  Build with ``python -m dm_nerf_b200._lib`` (or
+``__graft_entry__.build()``): plain ``nvcc -gencode arch=compute_100a,code=sm_100a``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import glob
+import os
+import subprocess
+import sys
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG_DIR, "csrc")
+SO_PATH = os.path.join(PKG_DIR, "libdmnerf_b200.so")
+
+MODE_FP32, MODE_BF16 = 0, 1
+COMP_DROP_EMPTY, COMP_RAW_INS = 1, 2
+NUM_PARAMS = 30
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+
+def sources():
+    return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+
+
+def needs_build() -> bool:
+    if not os.path.exists(SO_PATH):
+        return True
+    t = os.path.getmtime(SO_PATH)
+    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.join(PKG_DIR, "..", "include", "dmnerf_b200.h")]
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile every .cu under csrc/ into one shared library for sm_100a (cross-compiles without a GPU)."""
+    if not force and not needs_build():
+        return SO_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH] + sources()
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return SO_PATH
+
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_int = C.c_int
+_f = C.c_float
+
+_SIGNATURES = {
+    "dmnerf_version": (_int, []),
+    "dmnerf_built_arch": (_int, []),
+    "dmnerf_last_error": (_int, [C.c_char_p, _int]),
+    "dmnerf_packed_bytes": (_i64, [_int, _int]),
+    "dmnerf_weights_pack": (_int, [C.POINTER(_p), _int, _int, _p, _p]),
+    "dmnerf_mlp_fwd": (_int, [_p, _p, _p, _i64, _int, _p, _int, _int, _p, _p, _p]),
+    "dmnerf_mlp_fwd_embedded": (_int, [_p, _i64, _p, _int, _int, _p, _p, _p]),
+    "dmnerf_acts_bytes": (_i64, [_i64, _int]),
+    "dmnerf_mlp_bwd": (_int, [_p, _p, _p, _i64, _int, C.POINTER(_p), _p, _p]),
+    "dmnerf_bwd_workspace_bytes": (_i64, [_i64, _int]),
+    "dmnerf_composite_fwd": (_int, [_p, _p, _p, _i64, _int, _int, _int, _p, _p, _p, _p, _p]),
+    "dmnerf_composite_bwd": (_int, [_p, _p, _p, _i64, _int, _int, _int, _int, _p, _p, _p, _p, _p, _p]),
+    "dmnerf_sample_pdf": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
+    "dmnerf_sample_cdf": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
+    "dmnerf_fine_z": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
+    "dmnerf_sort_cat": (_int, [C.POINTER(_p), C.POINTER(_int), _int, _i64, _p, _p]),
+    "dmnerf_jitter_z": (_int, [_p, _p, _i64, _int, _p, _p]),
+    "dmnerf_penalizer_fwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _p, _p, _p]),
+    "dmnerf_penalizer_bwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _p, _p, _p, _p]),
+    "dmnerf_exchange": (_int, [_p, _p, _p, _p, _int, _int, _i64, _int, _int, _p, _p, _p]),
+    "dmnerf_rays_k": (_int, [_int, _int, C.POINTER(_f), C.POINTER(_f), _i64, _p, _i64, _p, _p, _p]),
+    "dmnerf_embed": (_int, [_p, _i64, _int, _p, _p]),
+    "dmnerf_label_argmax": (_int, [_p, _i64, _int, _p, _p]),
+    "dmnerf_selftest_umma": (_int, [_p, _p, _int, _int, _p, _p]),
+}
+
+EXPORTS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the shared library.  Raises if it is missing -- no CPU fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(
+                f"dm_nerf_b200: {SO_PATH} is missing. Build it with `python -m dm_nerf_b200._lib` "
+                "(nvcc, sm_100a). There is no CPU or PyTorch fallback for this path.")
+        handle = C.CDLL(SO_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def last_error() -> str:
+    buf = C.create_string_buffer(512)
+    lib().dmnerf_last_error(buf, 512)
+    return buf.value.decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed with code {rc}: {last_error()}")
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,125 @@
+// api.cu -- error plumbing and the extern "C" entry points of the MLP path (include/dmnerf_b200.h).
+#include <stdarg.h>
+#include "mlp_layout.cuh"
+
+namespace dmnerf {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error("CUDA error %d (%s) at %s", static_cast<int>(e), cudaGetErrorString(e), what);
+    return DMNERF_ECUDA;
+}
+
+
+// mlp_simt.cu
+int pack_fp32(const float* const* params, int ins_num, float* packed, cudaStream_t st);
+int launch_mlp_fp32(const MlpInput& in, const float* packed, int ins_num, float* raw_out, float* acts,
+                    cudaStream_t st);
+// mlp_bwd.cu
+int launch_mlp_bwd_fp32(const float* packed, const float* acts, const float* d_raw, int64_t n_points, int ins_num,
+                        float* const* grads, cudaStream_t st);
+// mlp_tc.cu
+int64_t bf16_image_bytes(int ins_num);
+int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st);
+int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, cudaStream_t st);
+
+}  // namespace dmnerf
+
+using namespace dmnerf;
+
+extern "C" int dmnerf_version(void) { return 100; }
+
+extern "C" int dmnerf_built_arch(void) { return 100; }
+
+extern "C" int dmnerf_last_error(char* buf, int cap) {
+    const int len = static_cast<int>(strlen(g_err));
+    if (buf && cap > 0) {
+        strncpy(buf, g_err, cap - 1);
+        buf[cap - 1] = 0;
+    }
+    return len;
+}
+
+static int check_ins(int ins_num, const char* who) {
+    DM_REQUIRE(ins_num >= 1 && ins_num <= kMaxIns, DMNERF_EUNSUPPORTED, "%s: ins_num %d outside [1,%d]", who, ins_num,
+               kMaxIns);
+    return DMNERF_OK;
+}
+
+extern "C" int64_t dmnerf_packed_bytes(int ins_num, int mode) {
+    if (ins_num < 1 || ins_num > kMaxIns) return -1;
+    if (mode == DMNERF_MODE_FP32) return fp32_image(ins_num).total_floats * 4;
+    if (mode == DMNERF_MODE_BF16) return bf16_image_bytes(ins_num);
+    return -1;
+}
+
+extern "C" int dmnerf_weights_pack(const float* const* params, int ins_num, int mode, void* packed, void* stream) {
+    DM_REQUIRE(params && packed, DMNERF_EINVAL, "weights_pack: null pointer");
+    if (int rc = check_ins(ins_num, "weights_pack")) return rc;
+    for (int i = 0; i < kNumParams; ++i) DM_REQUIRE(params[i], DMNERF_EINVAL, "weights_pack: params[%d] is null", i);
+    if (mode == DMNERF_MODE_FP32) return pack_fp32(params, ins_num, static_cast<float*>(packed), as_stream(stream));
+    if (mode == DMNERF_MODE_BF16) return pack_bf16(params, ins_num, packed, as_stream(stream));
+    DM_REQUIRE(false, DMNERF_EUNSUPPORTED, "weights_pack: unknown mode %d", mode);
+}
+
+extern "C" int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num) {
+    (void)ins_num;
+    const int64_t tiles = (n_points + kTileM - 1) / kTileM;
+    return tiles * kActRows * kTileM * 4;
+}
+
+static int run_mlp(const MlpInput& in, const void* packed, int ins_num, int mode, float* raw_out, void* acts,
+                   void* stream) {
+    DM_REQUIRE(packed && raw_out, DMNERF_EINVAL, "mlp_fwd: null pointer");
+    if (int rc = check_ins(ins_num, "mlp_fwd")) return rc;
+    if (in.n_points <= 0) return DMNERF_OK;
+    if (mode == DMNERF_MODE_FP32)
+        return launch_mlp_fp32(in, static_cast<const float*>(packed), ins_num, raw_out, static_cast<float*>(acts),
+                               as_stream(stream));
+    if (mode == DMNERF_MODE_BF16) {
+        DM_REQUIRE(acts == nullptr, DMNERF_EUNSUPPORTED,
+                   "mlp_fwd: the activation stash (training) is only produced in DMNERF_MODE_FP32");
+        return launch_mlp_bf16(in, packed, ins_num, raw_out, as_stream(stream));
+    }
+    DM_REQUIRE(false, DMNERF_EUNSUPPORTED, "mlp_fwd: unknown mode %d", mode);
+}
+
+extern "C" int dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
+                              const void* packed, int ins_num, int mode, float* raw_out, void* acts, void* stream) {
+    DM_REQUIRE(rays_o && rays_d && z, DMNERF_EINVAL, "mlp_fwd: null ray pointer");
+    DM_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 4096, DMNERF_EUNSUPPORTED,
+               "mlp_fwd: n_samples %d outside [1,4096]", n_samples);
+    MlpInput in{rays_o, rays_d, z, nullptr, n_rays * n_samples, n_samples};
+    return run_mlp(in, packed, ins_num, mode, raw_out, acts, stream);
+}
+
+extern "C" int dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int ins_num, int mode,
+                                       float* raw_out, void* acts, void* stream) {
+    DM_REQUIRE(x, DMNERF_EINVAL, "mlp_fwd_embedded: null input");
+    MlpInput in{nullptr, nullptr, nullptr, x, m, 1};
+    return run_mlp(in, packed, ins_num, mode, raw_out, acts, stream);
+}
+
+extern "C" int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num) {
+    (void)n_points; (void)ins_num;
+    return 0;
+}
+
+extern "C" int dmnerf_mlp_bwd(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
+                              int ins_num, float* const* grads, void* workspace, void* stream) {
+    (void)workspace;
+    DM_REQUIRE(packed && acts && d_raw && grads, DMNERF_EINVAL, "mlp_bwd: null pointer");
+    if (int rc = check_ins(ins_num, "mlp_bwd")) return rc;
+    for (int i = 0; i < kNumParams; ++i) DM_REQUIRE(grads[i], DMNERF_EINVAL, "mlp_bwd: grads[%d] is null", i);
+    if (n_points <= 0) return DMNERF_OK;
+    return launch_mlp_bwd_fp32(static_cast<const float*>(packed), static_cast<const float*>(acts), d_raw, n_points,
+                               ins_num, grads, as_stream(stream));
+}

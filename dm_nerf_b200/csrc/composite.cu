@@ -1,0 +1,310 @@
+// composite.cu -- a5/a8 volume compositing, one warp per ray.
+//
+// Forward (render_train, networks/render.py:6-28; manipulator_render, networks/manipulator.py:86-105):
+//   delta_s = (z[s+1]-z[s]) * |d|   (last: 1e10*|d|)          alpha_s = 1 - exp(-relu(sigma_s)*delta_s)
+//   T_s = prod_{r<s} (1 - alpha_r + 1e-10)   (warp-shuffle exclusive product scan + running carry)
+//   w_s = alpha_s*T_s     rgb = sum w*sigmoid(raw_rgb)    depth = sum w*z    ins = sigmoid(sum w*raw_ins)
+// Data movement: each 32-sample chunk of raw (32*C contiguous floats) is staged once into shared
+// memory with fully coalesced loads; lanes then act as samples (scan) and as channels (logit sums).
+// HBM traffic = the algorithmic bytes (raw read once); roofline: HBM.
+#include "common.cuh"
+
+namespace dmnerf {
+
+constexpr int kCompWarps = 8;
+
+__device__ __forceinline__ void stage_chunk(float* tile, const float* __restrict__ src, int cnt, int C, int CP,
+                                            float invC, int lane) {
+    const int total = cnt * C;
+    for (int i = lane; i < total; i += 32) {
+        int row = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
+        int col = i - row * C;
+        tile[row * CP + col] = __ldg(src + i);
+    }
+}
+
+__device__ __forceinline__ void unstage_chunk(const float* tile, float* __restrict__ dst, int cnt, int C, int CP,
+                                              float invC, int lane) {
+    const int total = cnt * C;
+    for (int i = lane; i < total; i += 32) {
+        int row = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
+        int col = i - row * C;
+        dst[i] = tile[row * CP + col];
+    }
+}
+
+// per-sample alpha / transmittance for one chunk; returns w, updates carry.
+__device__ __forceinline__ void scan_chunk(float sigma, float dist, bool valid, int lane, float& carry,
+                                           float& alpha, float& trans, float& w) {
+    alpha = 1.0f - expf(-fmaxf(sigma, 0.0f) * dist);
+    float t = valid ? (1.0f - alpha) + 1e-10f : 1.0f;
+    float incl = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl *= v;
+    }
+    float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane == 0) excl = 1.0f;
+    trans = carry * excl;
+    w = valid ? alpha * trans : 0.0f;
+    carry *= __shfl_sync(0xffffffffu, incl, 31);
+}
+
+__global__ void __launch_bounds__(kCompWarps * 32)
+composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
+                     int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,
+                     float* __restrict__ weights, float* __restrict__ ins) {
+    extern __shared__ float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t ray = static_cast<int64_t>(blockIdx.x) * kCompWarps + warp;
+    if (ray >= n) return;
+    const int CP = C | 1;
+    float* tile = smem + warp * (32 * CP + 32);
+    float* wbuf = tile + 32 * CP;
+    const float invC = 1.0f / static_cast<float>(C);
+    const int L = C - 4;  // instance logits incl. the "empty" class
+
+    const float dx = rays_d[ray * 3 + 0], dy = rays_d[ray * 3 + 1], dz = rays_d[ray * 3 + 2];
+    const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
+    const float* zrow = z + ray * S;
+    const float* rrow = raw + ray * S * static_cast<int64_t>(C);
+
+    float carry = 1.0f, a_r = 0.f, a_g = 0.f, a_b = 0.f, a_d = 0.f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c0 = 0; c0 < S; c0 += 32) {
+        const int cnt = min(32, S - c0);
+        stage_chunk(tile, rrow + static_cast<int64_t>(c0) * C, cnt, C, CP, invC, lane);
+        __syncwarp();
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        float zc = valid ? zrow[s] : 0.f;
+        float dist = 0.f, sigma = 0.f;
+        if (valid) {
+            dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            sigma = tile[lane * CP + 3];
+        }
+        float alpha, trans, w;
+        scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
+        if (valid) {
+            if (weights) weights[ray * S + s] = w;
+            a_r += w * sigmoidf_ref(tile[lane * CP + 0]);
+            a_g += w * sigmoidf_ref(tile[lane * CP + 1]);
+            a_b += w * sigmoidf_ref(tile[lane * CP + 2]);
+            a_d += w * zc;
+        }
+        wbuf[lane] = w;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) {
+                float a = acc[q];
+                const float* col = tile + 4 + j;
+                for (int r = 0; r < cnt; ++r) a += wbuf[r] * col[r * CP];
+                acc[q] = a;
+            }
+        }
+        __syncwarp();
+    }
+    a_r = warp_sum(a_r); a_g = warp_sum(a_g); a_b = warp_sum(a_b); a_d = warp_sum(a_d);
+    if (lane == 0) {
+        rgb[ray * 3 + 0] = a_r; rgb[ray * 3 + 1] = a_g; rgb[ray * 3 + 2] = a_b;
+        depth[ray] = a_d;
+    }
+    const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int j = lane + 32 * q;
+        if (j < Lout) ins[ray * Lout + j] = (flags & DMNERF_COMP_RAW_INS) ? acc[q] : sigmoidf_ref(acc[q]);
+    }
+}
+
+// Backward.  Phase A recomputes alpha/T/w (kept in shared memory per ray) and the logit sums,
+// phase C walks the chunks in reverse with a running suffix sum  R_s = sum_{r>s} dw_r*w_r:
+//   dalpha_s = dw_s*T_s - R_s/(1-alpha_s+1e-10)        dsigma_s = [sigma>0]*dalpha_s*delta_s*(1-alpha_s)
+__global__ void __launch_bounds__(kCompWarps * 32)
+composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
+                     int64_t n, int S, int C, int flags, int ins_detach, const float* __restrict__ d_rgb,
+                     const float* __restrict__ d_depth, const float* __restrict__ d_weights,
+                     const float* __restrict__ d_ins, float* __restrict__ d_raw) {
+    extern __shared__ float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t ray = static_cast<int64_t>(blockIdx.x) * kCompWarps + warp;
+    if (ray >= n) return;
+    const int CP = C | 1;
+    float* tile = smem + warp * (32 * CP + 32 + 3 * S);
+    float* wbuf = tile + 32 * CP;
+    float* s_alpha = wbuf + 32;
+    float* s_trans = s_alpha + S;
+    float* s_w = s_trans + S;
+    const float invC = 1.0f / static_cast<float>(C);
+    const int L = C - 4;
+    const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
+
+    const float dx = rays_d[ray * 3 + 0], dy = rays_d[ray * 3 + 1], dz = rays_d[ray * 3 + 2];
+    const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
+    const float* zrow = z + ray * S;
+    const float* rrow = raw + ray * S * static_cast<int64_t>(C);
+    float* grow = d_raw + ray * S * static_cast<int64_t>(C);
+
+    // ---- phase A
+    float carry = 1.0f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c0 = 0; c0 < S; c0 += 32) {
+        const int cnt = min(32, S - c0);
+        const bool need_logits = (d_ins != nullptr);
+        if (need_logits) stage_chunk(tile, rrow + static_cast<int64_t>(c0) * C, cnt, C, CP, invC, lane);
+        __syncwarp();
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        float dist = 0.f, sigma = 0.f;
+        if (valid) {
+            float zc = zrow[s];
+            dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            sigma = need_logits ? tile[lane * CP + 3] : rrow[static_cast<int64_t>(s) * C + 3];
+        }
+        float alpha, trans, w;
+        scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
+        if (valid) { s_alpha[s] = alpha; s_trans[s] = trans; s_w[s] = w; }
+        wbuf[lane] = w;
+        __syncwarp();
+        if (need_logits) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int j = lane + 32 * q;
+                if (j < L) {
+                    float a = acc[q];
+                    const float* col = tile + 4 + j;
+                    for (int r = 0; r < cnt; ++r) a += wbuf[r] * col[r * CP];
+                    acc[q] = a;
+                }
+            }
+        }
+        __syncwarp();
+    }
+    // ---- phase B: gradient w.r.t. the accumulated logits
+    float dA[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int j = lane + 32 * q;
+        float g = 0.f;
+        if (d_ins != nullptr && j < Lout) {
+            g = d_ins[ray * Lout + j];
+            if (!(flags & DMNERF_COMP_RAW_INS)) {
+                float p = sigmoidf_ref(acc[q]);
+                g *= p * (1.0f - p);
+            }
+        }
+        dA[q] = g;
+    }
+    const float g_r = d_rgb ? d_rgb[ray * 3 + 0] : 0.f;
+    const float g_g = d_rgb ? d_rgb[ray * 3 + 1] : 0.f;
+    const float g_b = d_rgb ? d_rgb[ray * 3 + 2] : 0.f;
+    const float g_d = d_depth ? d_depth[ray] : 0.f;
+
+    // ---- phase C
+    float suffix = 0.f;
+    const int last0 = ((S - 1) / 32) * 32;
+    for (int c0 = last0; c0 >= 0; c0 -= 32) {
+        const int cnt = min(32, S - c0);
+        stage_chunk(tile, rrow + static_cast<int64_t>(c0) * C, cnt, C, CP, invC, lane);
+        __syncwarp();
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        float dw = 0.f, w = 0.f, alpha = 0.f, trans = 0.f, zc = 0.f;
+        float c_r = 0.f, c_g = 0.f, c_b = 0.f;
+        if (valid) {
+            w = s_w[s]; alpha = s_alpha[s]; trans = s_trans[s]; zc = zrow[s];
+            c_r = sigmoidf_ref(tile[lane * CP + 0]);
+            c_g = sigmoidf_ref(tile[lane * CP + 1]);
+            c_b = sigmoidf_ref(tile[lane * CP + 2]);
+            dw = g_r * c_r + g_g * c_g + g_b * c_b + g_d * zc;
+            if (d_weights) dw += d_weights[ray * S + s];
+        }
+        if (!ins_detach && d_ins != nullptr) {
+            for (int r = 0; r < cnt; ++r) {
+                float part = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int j = lane + 32 * q;
+                    if (j < L) part += dA[q] * tile[r * CP + 4 + j];
+                }
+                part = warp_sum(part);
+                if (lane == r) dw += part;
+            }
+        }
+        // suffix sums of g = dw*w over later samples
+        float g = valid ? dw * w : 0.f;
+        float incl = g;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            float v = __shfl_down_sync(0xffffffffu, incl, o);
+            if (lane + o < 32) incl += v;
+        }
+        const float after = suffix + (incl - g);
+        suffix += __shfl_sync(0xffffffffu, incl, 0);
+        if (valid) {
+            const float t = (1.0f - alpha) + 1e-10f;
+            const float dalpha = dw * trans - after / t;
+            const float sigma = tile[lane * CP + 3];
+            const float dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            const float dsigma = (sigma > 0.f) ? dalpha * dist * (1.0f - alpha) : 0.f;
+            tile[lane * CP + 0] = g_r * w * c_r * (1.0f - c_r);
+            tile[lane * CP + 1] = g_g * w * c_g * (1.0f - c_g);
+            tile[lane * CP + 2] = g_b * w * c_b * (1.0f - c_b);
+            tile[lane * CP + 3] = dsigma;
+        }
+        wbuf[lane] = w;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) {
+                float* col = tile + 4 + j;
+                for (int r = 0; r < cnt; ++r) col[r * CP] = dA[q] * wbuf[r];
+            }
+        }
+        __syncwarp();
+        unstage_chunk(tile, grow + static_cast<int64_t>(c0) * C, cnt, C, CP, invC, lane);
+        __syncwarp();
+    }
+}
+
+}  // namespace dmnerf
+
+using namespace dmnerf;
+
+extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
+                                    int flags, float* rgb, float* depth, float* weights, float* ins, void* stream) {
+    DM_REQUIRE(raw && z && rays_d && rgb && depth && ins, DMNERF_EINVAL, "composite_fwd: null pointer");
+    DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_fwd: n_samples %d outside [1,1024]", s);
+    DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "composite_fwd: channels %d outside [6,128]", c);
+    if (n == 0) return DMNERF_OK;
+    const int CP = c | 1;
+    const size_t smem = static_cast<size_t>(kCompWarps) * (32 * CP + 32) * sizeof(float);
+    DM_CUDA(cudaFuncSetAttribute(composite_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = static_cast<unsigned>((n + kCompWarps - 1) / kCompWarps);
+    composite_fwd_kernel<<<grid, kCompWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb,
+                                                                            depth, weights, ins);
+    DM_LAUNCH_CHECK("composite_fwd_kernel");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
+                                    int flags, int ins_detach, const float* d_rgb, const float* d_depth,
+                                    const float* d_weights, const float* d_ins, float* d_raw, void* stream) {
+    DM_REQUIRE(raw && z && rays_d && d_raw, DMNERF_EINVAL, "composite_bwd: null pointer");
+    DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_bwd: n_samples %d outside [1,1024]", s);
+    DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "composite_bwd: channels %d outside [6,128]", c);
+    if (n == 0) return DMNERF_OK;
+    const int CP = c | 1;
+    const size_t smem = static_cast<size_t>(kCompWarps) * (32 * CP + 32 + 3 * s) * sizeof(float);
+    DM_REQUIRE(smem <= 227 * 1024, DMNERF_EUNSUPPORTED, "composite_bwd: shared memory %zu too large", smem);
+    DM_CUDA(cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = static_cast<unsigned>((n + kCompWarps - 1) / kCompWarps);
+    composite_bwd_kernel<<<grid, kCompWarps * 32, smem, as_stream(stream)>>>(
+        raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins, d_raw);
+    DM_LAUNCH_CHECK("composite_bwd_kernel");
+    return DMNERF_OK;
+}

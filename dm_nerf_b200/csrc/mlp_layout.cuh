@@ -1,0 +1,98 @@
+// mlp_layout.cuh -- packed weight images and activation-stash layout shared by the MLP kernels.
+//
+// The DM_NeRF network (networks/dm_nerf.py:58-106) as the kernels see it, "big" layers first:
+//   id  module                     K (padded)        N    act   input
+//    0  mlps.0                      63 (64)          256  relu  pos-embedding
+//   1-4 mlps.1..4                   256              256  relu  h
+//    5  mlps.5                      256+63 (320)     256  relu  [h | pos-embedding]   (skip, :86-87)
+//   6,7 mlps.6,7                    256              256  relu  h
+//    8  ins_feature_linear          256              256  -     h7 (detached, :95)
+//    9  ins_feature_linears.0       256              128  relu  ins_feat
+//   10  rgb_feature_linear          256              256  -     h7
+//   11  rgb_feature_linears.0       256+27 (288)     128  relu  [rgb_feat | dir-embedding]
+// and three small heads evaluated as dot products: density (256->1), rgb (128->3), ins (128->K+1).
+#pragma once
+#include "common.cuh"
+
+namespace dmnerf {
+
+constexpr int kBigLayers = 12;
+
+struct BigLayer {
+    int w_idx;     // index of the weight tensor in the 30-entry state_dict order (bias = w_idx+1)
+    int k_src;     // columns of the torch weight
+    int k_pad;     // padded reduction length (multiple of 16)
+    int n;         // outputs
+    int k_grad;    // leading input columns that need a gradient (dgrad width); 0 = none
+};
+
+__host__ __device__ inline BigLayer big_layer(int id) {
+    switch (id) {
+        case 0:  return {0, 63, 64, 256, 0};
+        case 5:  return {10, 319, 320, 256, 256};
+        case 8:  return {P_INSF_W, 256, 256, 256, 0};      // h.detach(): no gradient into the trunk
+        case 9:  return {P_INS0_W, 256, 256, 128, 256};
+        case 10: return {P_RGBF_W, 256, 256, 256, 256};
+        case 11: return {P_RGB0_W, 283, 288, 128, 256};
+        default: return {2 * id, 256, 256, 256, 256};      // mlps.1-4, 6, 7
+    }
+}
+
+// ---- fp32 packed image (DMNERF_MODE_FP32) ------------------------------------------------------------
+// per big layer:  Wt [k_pad][n]  (transposed, zero padded)   | bias [n] | Wg [n][k_grad] (row-major copy
+// trimmed to the columns that receive a gradient; used by the backward's dgrad)
+// then heads:     w_density[256], b_density[1] (padded to 4), W_rgb[3][128], b_rgb[4], W_ins[K+1][128], b_ins[K+1 pad4]
+struct Fp32Image {
+    int64_t wt[kBigLayers];
+    int64_t bias[kBigLayers];
+    int64_t wg[kBigLayers];
+    int64_t w_dens, b_dens, w_rgb, b_rgb, w_ins, b_ins;
+    int64_t total_floats;
+    int ins_num;
+};
+
+__host__ __device__ inline int64_t round4(int64_t x) { return (x + 3) & ~int64_t(3); }
+
+__host__ __device__ inline Fp32Image fp32_image(int ins_num) {
+    Fp32Image im;
+    int64_t off = 0;
+    for (int l = 0; l < kBigLayers; ++l) {
+        const BigLayer b = big_layer(l);
+        im.wt[l] = off;   off += static_cast<int64_t>(b.k_pad) * b.n;
+        im.bias[l] = off; off += b.n;
+        im.wg[l] = off;   off += static_cast<int64_t>(b.n) * b.k_grad;
+    }
+    im.w_dens = off; off += 256;
+    im.b_dens = off; off += 4;
+    im.w_rgb = off;  off += 3 * 128;
+    im.b_rgb = off;  off += 4;
+    im.w_ins = off;  off += static_cast<int64_t>(ins_num + 1) * 128;
+    im.b_ins = off;  off += round4(ins_num + 1);
+    im.total_floats = off;
+    im.ins_num = ins_num;
+    return im;
+}
+
+// ---- activation stash (training mode), per tile of 64 points: rows of 64 floats --------------------
+constexpr int kTileM = 64;
+constexpr int kActPos = 0;                    // 64 rows  pos-embedding (row 63 = 0)
+constexpr int kActDir = 64;                   // 32 rows  dir-embedding (rows 27.. = 0)
+constexpr int kActH0 = 96;                    // 8 x 256  post-ReLU trunk activations h0..h7
+constexpr int kActInsF = kActH0 + 8 * 256;    // 256      ins_feature_linear output
+constexpr int kActInsH = kActInsF + 256;      // 128      relu(ins_feature_linears.0)
+constexpr int kActRgbF = kActInsH + 128;      // 256      rgb_feature_linear output
+constexpr int kActRgbH = kActRgbF + 256;      // 128      relu(rgb_feature_linears.0)
+constexpr int kActRows = kActRgbH + 128;      // 2912
+
+// Input of one MLP launch: either rays (points o + d*z and both embeddings computed in-kernel) or
+// already-embedded rows x[m,90].
+struct MlpInput {
+    const float* rays_o;   // [n_rays,3]       (rays mode)
+    const float* rays_d;   // [n_rays,3]
+    const float* z;        // [n_rays,S]
+    const float* x;        // [m,90]           (embedded mode; rays_* == nullptr)
+    int64_t n_points;
+    int S;
+};
+
+}  // namespace dmnerf

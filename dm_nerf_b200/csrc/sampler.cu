@@ -1,0 +1,249 @@
+// sampler.cu -- a4 hierarchical sampling (networks/helpers.py:123-155), the coarse tail of
+// dm_nerf (networks/render.py:66-70), sorted merges (networks/manipulator.py:190,195) and the
+// stratified jitter (networks/render.py:40-47).  One warp per ray, everything in shared memory.
+//
+// CDF summation order (fixed and documented; oracle/dmnerf_oracle_c.c uses the same one, so indices are
+// bit-exact against it): w_j = weights_j + 1e-5; total = ((w_0 + w_1) + w_2) + ... sequential fp32;
+// pdf_j = w_j / total (IEEE division); cdf_0 = 0, cdf_{j+1} = cdf_j + pdf_j sequential fp32.
+// searchsorted(right=True): inds = #{j : cdf_j <= u}.  The lerp uses un-fused mul/add like ATen.
+#include "common.cuh"
+#include <math_constants.h>
+
+namespace dmnerf {
+
+constexpr int kSampWarps = 4;
+
+// torch.linspace(0,1,n) in fp32: step=(1-0)/(n-1); i < n/2 ? step*i : 1 - step*(n-1-i)
+__device__ __forceinline__ float linspace01(int i, int n) {
+    const float step = 1.0f / static_cast<float>(n - 1);
+    return (i < n / 2) ? __fmul_rn(step, static_cast<float>(i))
+                       : __fsub_rn(1.0f, __fmul_rn(step, static_cast<float>(n - 1 - i)));
+}
+
+// Builds cdf[0..nb-1] in shared memory from wv[0..nb-2] (= weights + 1e-5 already stored).
+__device__ __forceinline__ void build_cdf(float* cdf, float* wv, int nb, int lane) {
+    float total = 0.f;
+    for (int j = 0; j < nb - 1; ++j) total = __fadd_rn(total, wv[j]);   // every lane, same order
+    __syncwarp();
+    for (int j = lane; j < nb - 1; j += 32) wv[j] = __fdiv_rn(wv[j], total);
+    __syncwarp();
+    if (lane == 0) {
+        float c = 0.f;
+        cdf[0] = 0.f;
+        for (int j = 0; j < nb - 1; ++j) { c = __fadd_rn(c, wv[j]); cdf[j + 1] = c; }
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ float invert_cdf(const float* cdf, const float* bins, int nb, float u, int& inds) {
+    int lo = 0, hi = nb;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+    }
+    inds = lo;
+    const int below = max(lo - 1, 0);
+    const int above = min(lo, nb - 1);
+    const float cb = cdf[below], ca = cdf[above];
+    float denom = __fsub_rn(ca, cb);
+    if (denom < 1e-5f) denom = 1.0f;
+    const float t = __fdiv_rn(__fsub_rn(u, cb), denom);
+    const float bb = bins[below], ba = bins[above];
+    return __fadd_rn(bb, __fmul_rn(t, __fsub_rn(ba, bb)));
+}
+
+// In-warp bitonic sort of P (power of two) floats in shared memory, ascending.
+__device__ __forceinline__ void bitonic_sort(float* v, int P, int lane) {
+    for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = lane; i < (P >> 1); i += 32) {
+                const int lo = ((i / j) * (j << 1)) + (i % j);
+                const int hi = lo + j;
+                const bool up = (lo & k) == 0;
+                const float a = v[lo], b = v[hi];
+                if ((a > b) == up) { v[lo] = b; v[hi] = a; }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+__device__ __forceinline__ int next_pow2(int x) { int p = 1; while (p < x) p <<= 1; return p; }
+
+// mode 0: weights given, cdf built here.  mode 1: cdf given (strict mode).
+__global__ void __launch_bounds__(kSampWarps * 32)
+sample_pdf_kernel(const float* __restrict__ bins, const float* __restrict__ weights_or_cdf, int cdf_given,
+                  const float* __restrict__ u, int64_t u_stride, int64_t n, int nb, int ns,
+                  float* __restrict__ z_out, int64_t* __restrict__ inds_out) {
+    extern __shared__ float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t ray = static_cast<int64_t>(blockIdx.x) * kSampWarps + warp;
+    if (ray >= n) return;
+    float* s_bins = smem + warp * (3 * nb);
+    float* s_cdf = s_bins + nb;
+    float* s_w = s_cdf + nb;
+    for (int j = lane; j < nb; j += 32) s_bins[j] = bins[ray * nb + j];
+    if (cdf_given) {
+        for (int j = lane; j < nb; j += 32) s_cdf[j] = weights_or_cdf[ray * nb + j];
+        __syncwarp();
+    } else {
+        for (int j = lane; j < nb - 1; j += 32) s_w[j] = __fadd_rn(weights_or_cdf[ray * (nb - 1) + j], 1e-5f);
+        __syncwarp();
+        build_cdf(s_cdf, s_w, nb, lane);
+    }
+    for (int i = lane; i < ns; i += 32) {
+        const float uu = u ? u[ray * u_stride + i] : linspace01(i, ns);
+        int inds;
+        const float zz = invert_cdf(s_cdf, s_bins, nb, uu, inds);
+        z_out[ray * ns + i] = zz;
+        if (inds_out) inds_out[ray * ns + i] = inds;
+    }
+}
+
+// Coarse tail: mids -> pdf over weights[1:-1] -> n_imp samples -> sort(cat(z_coarse, samples)).
+__global__ void __launch_bounds__(kSampWarps * 32)
+fine_z_kernel(const float* __restrict__ z_coarse, const float* __restrict__ weights, const float* __restrict__ u,
+              int64_t u_stride, int64_t n, int sc, int n_imp, int P, float* __restrict__ z_fine,
+              float* __restrict__ z_samples) {
+    extern __shared__ float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t ray = static_cast<int64_t>(blockIdx.x) * kSampWarps + warp;
+    if (ray >= n) return;
+    const int nb = sc - 1;
+    float* s_sort = smem + warp * (P + 3 * sc);
+    float* s_bins = s_sort + P;
+    float* s_cdf = s_bins + sc;
+    float* s_w = s_cdf + sc;
+    for (int j = lane; j < sc; j += 32) s_sort[j] = z_coarse[ray * sc + j];
+    __syncwarp();
+    for (int j = lane; j < nb; j += 32) s_bins[j] = __fmul_rn(0.5f, __fadd_rn(s_sort[j + 1], s_sort[j]));
+    for (int j = lane; j < nb - 1; j += 32) s_w[j] = __fadd_rn(weights[ray * sc + 1 + j], 1e-5f);
+    __syncwarp();
+    build_cdf(s_cdf, s_w, nb, lane);
+    for (int i = lane; i < n_imp; i += 32) {
+        const float uu = u ? u[ray * u_stride + i] : linspace01(i, n_imp);
+        int inds;
+        const float zz = invert_cdf(s_cdf, s_bins, nb, uu, inds);
+        s_sort[sc + i] = zz;
+        if (z_samples) z_samples[ray * n_imp + i] = zz;
+    }
+    for (int i = sc + n_imp + lane; i < P; i += 32) s_sort[i] = CUDART_INF_F;
+    __syncwarp();
+    bitonic_sort(s_sort, P, lane);
+    const int tot = sc + n_imp;
+    for (int i = lane; i < tot; i += 32) z_fine[ray * tot + i] = s_sort[i];
+}
+
+struct CatParts {
+    const float* src[8];
+    int len[8];
+    int parts;
+};
+
+__global__ void __launch_bounds__(kSampWarps * 32)
+sort_cat_kernel(CatParts cp, int64_t n, int tot, int P, float* __restrict__ out) {
+    extern __shared__ float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t ray = static_cast<int64_t>(blockIdx.x) * kSampWarps + warp;
+    if (ray >= n) return;
+    float* s_sort = smem + warp * P;
+    int off = 0;
+    for (int p = 0; p < cp.parts; ++p) {
+        const float* src = cp.src[p] + ray * cp.len[p];
+        for (int i = lane; i < cp.len[p]; i += 32) s_sort[off + i] = src[i];
+        off += cp.len[p];
+    }
+    for (int i = tot + lane; i < P; i += 32) s_sort[i] = CUDART_INF_F;
+    __syncwarp();
+    bitonic_sort(s_sort, P, lane);
+    for (int i = lane; i < tot; i += 32) out[ray * tot + i] = s_sort[i];
+}
+
+// z' = lower + (upper-lower)*t with mids between neighbours (render.py:42-47), un-fused like ATen.
+__global__ void jitter_z_kernel(const float* __restrict__ z, const float* __restrict__ t_rand, int64_t total, int S,
+                                float* __restrict__ out) {
+    const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int s = static_cast<int>(idx % S);
+    const float zc = z[idx];
+    const float upper = (s + 1 < S) ? __fmul_rn(0.5f, __fadd_rn(z[idx + 1], zc)) : zc;
+    const float lower = (s > 0) ? __fmul_rn(0.5f, __fadd_rn(zc, z[idx - 1])) : zc;
+    out[idx] = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), t_rand[idx]));
+}
+
+}  // namespace dmnerf
+
+using namespace dmnerf;
+
+static int launch_sample(const float* bins, const float* w_or_cdf, int cdf_given, const float* u, int64_t u_stride,
+                         int64_t n, int nb, int ns, float* z_out, int64_t* inds_out, void* stream) {
+    DM_REQUIRE(bins && w_or_cdf && z_out, DMNERF_EINVAL, "sample_pdf: null pointer");
+    DM_REQUIRE(nb >= 2 && nb <= 1024 && ns >= 2 && ns <= 4096, DMNERF_EUNSUPPORTED,
+               "sample_pdf: n_bins %d / n_samples %d unsupported", nb, ns);
+    if (n <= 0) return DMNERF_OK;
+    const size_t smem = static_cast<size_t>(kSampWarps) * 3 * nb * sizeof(float);
+    const unsigned grid = static_cast<unsigned>((n + kSampWarps - 1) / kSampWarps);
+    sample_pdf_kernel<<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(bins, w_or_cdf, cdf_given, u, u_stride, n,
+                                                                         nb, ns, z_out, inds_out);
+    DM_LAUNCH_CHECK("sample_pdf_kernel");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_sample_pdf(const float* bins, const float* weights, const float* u, int64_t u_stride, int64_t n,
+                                 int n_bins, int n_samples, float* z_out, int64_t* inds_out, void* stream) {
+    return launch_sample(bins, weights, 0, u, u_stride, n, n_bins, n_samples, z_out, inds_out, stream);
+}
+
+extern "C" int dmnerf_sample_cdf(const float* bins, const float* cdf, const float* u, int64_t u_stride, int64_t n,
+                                 int n_bins, int n_samples, float* z_out, int64_t* inds_out, void* stream) {
+    return launch_sample(bins, cdf, 1, u, u_stride, n, n_bins, n_samples, z_out, inds_out, stream);
+}
+
+extern "C" int dmnerf_fine_z(const float* z_coarse, const float* weights, const float* u, int64_t u_stride, int64_t n,
+                             int sc, int n_imp, float* z_fine, float* z_samples, void* stream) {
+    DM_REQUIRE(z_coarse && weights && z_fine, DMNERF_EINVAL, "fine_z: null pointer");
+    DM_REQUIRE(sc >= 4 && sc <= 512 && n_imp >= 2 && sc + n_imp <= 1024, DMNERF_EUNSUPPORTED,
+               "fine_z: sc %d / n_importance %d unsupported", sc, n_imp);
+    if (n <= 0) return DMNERF_OK;
+    int P = 1;
+    while (P < sc + n_imp) P <<= 1;
+    const size_t smem = static_cast<size_t>(kSampWarps) * (P + 3 * sc) * sizeof(float);
+    const unsigned grid = static_cast<unsigned>((n + kSampWarps - 1) / kSampWarps);
+    fine_z_kernel<<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(z_coarse, weights, u, u_stride, n, sc, n_imp, P,
+                                                                     z_fine, z_samples);
+    DM_LAUNCH_CHECK("fine_z_kernel");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_sort_cat(const float* const* srcs, const int* lens, int parts, int64_t n, float* out,
+                               void* stream) {
+    DM_REQUIRE(srcs && lens && out, DMNERF_EINVAL, "sort_cat: null pointer");
+    DM_REQUIRE(parts >= 1 && parts <= 8, DMNERF_EUNSUPPORTED, "sort_cat: %d parts (max 8)", parts);
+    CatParts cp;
+    int tot = 0;
+    for (int p = 0; p < parts; ++p) {
+        DM_REQUIRE(srcs[p] && lens[p] > 0, DMNERF_EINVAL, "sort_cat: part %d empty", p);
+        cp.src[p] = srcs[p]; cp.len[p] = lens[p]; tot += lens[p];
+    }
+    cp.parts = parts;
+    DM_REQUIRE(tot <= 2048, DMNERF_EUNSUPPORTED, "sort_cat: %d samples per ray (max 2048)", tot);
+    if (n <= 0) return DMNERF_OK;
+    int P = 1;
+    while (P < tot) P <<= 1;
+    const size_t smem = static_cast<size_t>(kSampWarps) * P * sizeof(float);
+    const unsigned grid = static_cast<unsigned>((n + kSampWarps - 1) / kSampWarps);
+    sort_cat_kernel<<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(cp, n, tot, P, out);
+    DM_LAUNCH_CHECK("sort_cat_kernel");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_jitter_z(const float* z, const float* t_rand, int64_t n, int s, float* z_out, void* stream) {
+    DM_REQUIRE(z && t_rand && z_out, DMNERF_EINVAL, "jitter_z: null pointer");
+    DM_REQUIRE(s >= 1, DMNERF_EINVAL, "jitter_z: bad sample count");
+    const int64_t total = n * s;
+    if (total <= 0) return DMNERF_OK;
+    const unsigned grid = static_cast<unsigned>((total + 255) / 256);
+    jitter_z_kernel<<<grid, 256, 0, as_stream(stream)>>>(z, t_rand, total, s, z_out);
+    DM_LAUNCH_CHECK("jitter_z_kernel");
+    return DMNERF_OK;
+}

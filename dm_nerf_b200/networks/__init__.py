@@ -1,0 +1,2 @@
+"""Shadow of the reference's ``networks`` package for the per-ray hot path."""
+from . import dm_nerf, helpers, render, penalizer, manipulator  # noqa: F401

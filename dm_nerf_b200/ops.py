@@ -1,0 +1,402 @@
+"""Tensor-level wrappers over the C-ABI (one function per entry point) plus the autograd
+Functions that give the ray path its backward.  torch is used for device memory, streams and
+autograd bookkeeping only; every computation happens in libdmnerf_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import MODE_BF16, MODE_FP32, COMP_DROP_EMPTY, COMP_RAW_INS, NUM_PARAMS, check
+
+_MODE_NAMES = {"fp32": MODE_FP32, "bf16": MODE_BF16}
+_default_mode = _MODE_NAMES[os.environ.get("DMNERF_MODE", "fp32").lower()]
+
+# launch counter: how many of OUR kernels-launching C-ABI calls were made (bench reports it)
+launches = 0
+
+
+def set_mode(mode) -> None:
+    """'fp32' (CUDA-core parity mode) or 'bf16' (tcgen05 tensor-core mode) for no-grad MLP queries."""
+    global _default_mode
+    _default_mode = _MODE_NAMES[mode] if isinstance(mode, str) else int(mode)
+
+
+def get_mode() -> int:
+    return _default_mode
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name}: expected a torch.Tensor")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: tensor must live on a CUDA device (dm_nerf_b200 has no CPU path)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _count(n: int = 1) -> None:
+    global launches
+    launches += n
+
+
+class KernelTimer:
+    """Per-kernel device timing with CUDA events on the launching (current) stream.  Usage:
+    ``with KernelTimer() as kt: ...`` then ``kt.totals()`` -> {name: (launches, total_ms)}."""
+
+    active = None
+
+    def __init__(self):
+        self.records = []
+
+    def __enter__(self):
+        KernelTimer.active = self
+        return self
+
+    def __exit__(self, *exc):
+        KernelTimer.active = None
+
+    def totals(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, a, b in self.records:
+            n, ms = out.get(name, (0, 0.0))
+            out[name] = (n + 1, ms + a.elapsed_time(b))
+        return out
+
+
+def _timed_call(name: str, fn, *args) -> None:
+    kt = KernelTimer.active
+    if kt is None:
+        check(fn(*args), name)
+        return
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    check(fn(*args), name)
+    b.record()
+    kt.records.append((name, a, b))
+
+
+# ---------------------------------------------------------------------------------------------------
+# weights
+# ---------------------------------------------------------------------------------------------------
+
+PARAM_ORDER: Tuple[str, ...] = tuple(
+    [f"mlps.{i}.{w}" for i in range(8) for w in ("weight", "bias")]
+    + [f"{m}.{w}" for m in ("rgb_feature_linear", "ins_feature_linear", "rgb_feature_linears.0",
+                           "ins_feature_linears.0", "density_linear", "ins_linear", "rgb_linear")
+       for w in ("weight", "bias")])
+assert len(PARAM_ORDER) == NUM_PARAMS
+
+
+def _ptr_array(tensors: Sequence[torch.Tensor]):
+    arr = (C.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr
+
+
+def pack_weights(params: Sequence[torch.Tensor], ins_num: int, mode: int) -> torch.Tensor:
+    """params: the 30 tensors in state_dict order (fp32, CUDA).  Returns the packed image (uint8)."""
+    params = [_f32(p.detach(), "param") for p in params]
+    nbytes = _lib.lib().dmnerf_packed_bytes(ins_num, mode)
+    if nbytes <= 0:
+        raise RuntimeError(f"pack_weights: unsupported ins_num={ins_num} / mode={mode}: {_lib.last_error()}")
+    out = torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
+    check(_lib.lib().dmnerf_weights_pack(_ptr_array(params), ins_num, mode, _ptr(out), _stream()), "dmnerf_weights_pack")
+    _count(0)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# MLP
+# ---------------------------------------------------------------------------------------------------
+
+
+def mlp_fwd(rays_o, rays_d, z, packed, ins_num: int, mode: int, stash: bool = False):
+    rays_o, rays_d, z = _f32(rays_o, "rays_o"), _f32(rays_d, "rays_d"), _f32(z, "z")
+    n, s = z.shape
+    raw = torch.empty((n, s, ins_num + 5), dtype=torch.float32, device=z.device)
+    acts = None
+    if stash:
+        acts = torch.empty(_lib.lib().dmnerf_acts_bytes(n * s, ins_num), dtype=torch.uint8, device=z.device)
+    _timed_call(f"dmnerf_mlp_fwd[S={s},mode={mode}]", _lib.lib().dmnerf_mlp_fwd, _ptr(rays_o), _ptr(rays_d), _ptr(z),
+                n, s, _ptr(packed), ins_num, mode, _ptr(raw), _ptr(acts), _stream())
+    _count()
+    return raw, acts
+
+
+def mlp_fwd_embedded(x, packed, ins_num: int, mode: int, stash: bool = False):
+    x = _f32(x, "x")
+    if x.shape[-1] != 90:
+        raise RuntimeError(f"DM_NeRF.forward: expected 63+27=90 input channels, got {x.shape[-1]}")
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, 90)
+    m = x2.shape[0]
+    raw = torch.empty((m, ins_num + 5), dtype=torch.float32, device=x.device)
+    acts = None
+    if stash:
+        acts = torch.empty(_lib.lib().dmnerf_acts_bytes(m, ins_num), dtype=torch.uint8, device=x.device)
+    check(_lib.lib().dmnerf_mlp_fwd_embedded(_ptr(x2), m, _ptr(packed), ins_num, mode, _ptr(raw), _ptr(acts),
+                                             _stream()), "dmnerf_mlp_fwd_embedded")
+    _count()
+    return raw.reshape(*lead, ins_num + 5), acts
+
+
+def mlp_bwd(packed_fp32, acts, d_raw, n_points: int, ins_num: int, shapes: Sequence[torch.Size]) -> List[torch.Tensor]:
+    d_raw = _f32(d_raw, "d_raw")
+    grads = [torch.zeros(s, dtype=torch.float32, device=d_raw.device) for s in shapes]
+    check(_lib.lib().dmnerf_mlp_bwd(_ptr(packed_fp32), _ptr(acts), _ptr(d_raw), n_points, ins_num, _ptr_array(grads),
+                                    None, _stream()), "dmnerf_mlp_bwd")
+    _count()
+    return grads
+
+
+class _MlpFn(torch.autograd.Function):
+    """raw = MLP(embed(o + d z), embed(d/|d|)) with parameter gradients (a12).  rays/z get no gradient
+    (the reference detaches z_samples, render.py:68, and rays are data)."""
+
+    @staticmethod
+    def forward(ctx, rays_o, rays_d, z, x, ins_num, packed_fp32, *params):
+        if x is None:
+            raw, acts = mlp_fwd(rays_o, rays_d, z, packed_fp32, ins_num, MODE_FP32, stash=True)
+            ctx.n_points = z.numel()
+        else:
+            raw, acts = mlp_fwd_embedded(x, packed_fp32, ins_num, MODE_FP32, stash=True)
+            ctx.n_points = x.numel() // 90
+        ctx.save_for_backward(packed_fp32, acts)
+        ctx.ins_num = ins_num
+        ctx.shapes = [p.shape for p in params]
+        return raw
+
+    @staticmethod
+    def backward(ctx, d_raw):
+        packed, acts = ctx.saved_tensors
+        grads = mlp_bwd(packed, acts, d_raw.reshape(-1, ctx.ins_num + 5), ctx.n_points, ctx.ins_num, ctx.shapes)
+        return (None, None, None, None, None, None, *grads)
+
+
+# ---------------------------------------------------------------------------------------------------
+# compositing
+# ---------------------------------------------------------------------------------------------------
+
+
+def composite_fwd(raw, z, rays_d, flags: int, want_weights: bool = True):
+    raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
+    n, s, c = raw.shape
+    dev = raw.device
+    lout = c - 4 - (1 if flags & COMP_DROP_EMPTY else 0)
+    rgb = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    depth = torch.empty((n,), dtype=torch.float32, device=dev)
+    ins = torch.empty((n, lout), dtype=torch.float32, device=dev)
+    weights = torch.empty((n, s), dtype=torch.float32, device=dev) if want_weights else None
+    _timed_call(f"dmnerf_composite_fwd[S={s}]", _lib.lib().dmnerf_composite_fwd, _ptr(raw), _ptr(z), _ptr(rays_d),
+                n, s, c, flags, _ptr(rgb), _ptr(depth), _ptr(weights), _ptr(ins), _stream())
+    _count()
+    return rgb, weights, depth, ins
+
+
+def composite_bwd(raw, z, rays_d, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins):
+    n, s, c = raw.shape
+    d_raw = torch.empty_like(raw)
+    opt = lambda t: None if t is None else _f32(t, "grad")
+    d_rgb, d_depth, d_weights, d_ins = opt(d_rgb), opt(d_depth), opt(d_weights), opt(d_ins)
+    check(_lib.lib().dmnerf_composite_bwd(_ptr(raw), _ptr(z), _ptr(rays_d), n, s, c, flags, int(ins_detach),
+                                          _ptr(d_rgb), _ptr(d_depth), _ptr(d_weights), _ptr(d_ins), _ptr(d_raw),
+                                          _stream()), "dmnerf_composite_bwd")
+    _count()
+    return d_raw
+
+
+class _CompositeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, raw, z, rays_d, flags, ins_detach):
+        raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
+        rgb, weights, depth, ins = composite_fwd(raw, z, rays_d, flags)
+        ctx.save_for_backward(raw, z, rays_d)
+        ctx.flags, ctx.ins_detach = flags, ins_detach
+        return rgb, weights, depth, ins
+
+    @staticmethod
+    def backward(ctx, d_rgb, d_weights, d_depth, d_ins):
+        raw, z, rays_d = ctx.saved_tensors
+        d_raw = composite_bwd(raw, z, rays_d, ctx.flags, ctx.ins_detach, d_rgb, d_depth, d_weights, d_ins)
+        return d_raw, None, None, None, None
+
+
+def composite(raw, z, rays_d, flags: int, ins_detach: bool):
+    if torch.is_grad_enabled() and isinstance(raw, torch.Tensor) and raw.requires_grad:
+        return _CompositeFn.apply(raw, z, rays_d, flags, ins_detach)
+    return composite_fwd(raw, z, rays_d, flags)
+
+
+# ---------------------------------------------------------------------------------------------------
+# sampler
+# ---------------------------------------------------------------------------------------------------
+
+
+def _u_args(u: Optional[torch.Tensor], n: int, ns: int):
+    if u is None:
+        return None, 0
+    u = _f32(u, "u")
+    if u.dim() == 1:
+        assert u.shape[0] == ns
+        return u, 0
+    assert tuple(u.shape) == (n, ns), (u.shape, n, ns)
+    return u, ns
+
+
+def sample_pdf(bins, weights, n_samples: int, u: Optional[torch.Tensor], want_inds: bool = False,
+               cdf: Optional[torch.Tensor] = None):
+    bins = _f32(bins, "bins")
+    n, nb = bins.shape
+    u, stride = _u_args(u, n, n_samples)
+    z = torch.empty((n, n_samples), dtype=torch.float32, device=bins.device)
+    inds = torch.empty((n, n_samples), dtype=torch.int64, device=bins.device) if want_inds else None
+    if cdf is not None:
+        cdf = _f32(cdf, "cdf")
+        check(_lib.lib().dmnerf_sample_cdf(_ptr(bins), _ptr(cdf), _ptr(u), stride, n, nb, n_samples, _ptr(z),
+                                           _ptr(inds), _stream()), "dmnerf_sample_cdf")
+    else:
+        weights = _f32(weights, "weights")
+        assert weights.shape == (n, nb - 1), (weights.shape, bins.shape)
+        check(_lib.lib().dmnerf_sample_pdf(_ptr(bins), _ptr(weights), _ptr(u), stride, n, nb, n_samples, _ptr(z),
+                                           _ptr(inds), _stream()), "dmnerf_sample_pdf")
+    _count()
+    return (z, inds) if want_inds else z
+
+
+def fine_z(z_coarse, weights, n_importance: int, u: Optional[torch.Tensor], want_samples: bool = False):
+    z_coarse, weights = _f32(z_coarse, "z_vals_coarse"), _f32(weights, "weights")
+    n, sc = z_coarse.shape
+    u, stride = _u_args(u, n, n_importance)
+    z_fine = torch.empty((n, sc + n_importance), dtype=torch.float32, device=z_coarse.device)
+    zs = torch.empty((n, n_importance), dtype=torch.float32, device=z_coarse.device) if want_samples else None
+    _timed_call("dmnerf_fine_z", _lib.lib().dmnerf_fine_z, _ptr(z_coarse), _ptr(weights), _ptr(u), stride, n, sc,
+                n_importance, _ptr(z_fine), _ptr(zs), _stream())
+    _count()
+    return (z_fine, zs) if want_samples else z_fine
+
+
+def sort_cat(parts: Sequence[torch.Tensor]) -> torch.Tensor:
+    parts = [_f32(p, "part") for p in parts]
+    n = parts[0].shape[0]
+    lens = (C.c_int * len(parts))(*[p.shape[1] for p in parts])
+    out = torch.empty((n, sum(p.shape[1] for p in parts)), dtype=torch.float32, device=parts[0].device)
+    check(_lib.lib().dmnerf_sort_cat(_ptr_array(parts), lens, len(parts), n, _ptr(out), _stream()), "dmnerf_sort_cat")
+    _count()
+    return out
+
+
+def jitter_z(z, t_rand):
+    z, t_rand = _f32(z, "z_vals"), _f32(t_rand, "t_rand")
+    out = torch.empty_like(z)
+    check(_lib.lib().dmnerf_jitter_z(_ptr(z), _ptr(t_rand), z.shape[0], z.shape[1], _ptr(out), _stream()),
+          "dmnerf_jitter_z")
+    _count()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# penalizer
+# ---------------------------------------------------------------------------------------------------
+
+
+class _PenalizerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, raw, z, depth, rays_d, tolerance, deta_w):
+        raw, z, depth, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(depth, "depth"), _f32(rays_d, "rays_d")
+        n, s, c = raw.shape
+        partials = torch.empty(4, dtype=torch.float32, device=raw.device)
+        loss = torch.empty(1, dtype=torch.float32, device=raw.device)
+        check(_lib.lib().dmnerf_penalizer_fwd(_ptr(raw), _ptr(z), _ptr(depth), _ptr(rays_d), n, s, c, tolerance,
+                                              deta_w, _ptr(partials), _ptr(loss), _stream()), "dmnerf_penalizer_fwd")
+        _count(2)
+        ctx.save_for_backward(raw, z, depth, rays_d, partials)
+        ctx.tol, ctx.dw = tolerance, deta_w
+        return loss
+
+    @staticmethod
+    def backward(ctx, d_loss):
+        raw, z, depth, rays_d, partials = ctx.saved_tensors
+        n, s, c = raw.shape
+        d_loss = _f32(d_loss, "d_loss").reshape(1)
+        d_raw = torch.empty_like(raw)
+        check(_lib.lib().dmnerf_penalizer_bwd(_ptr(raw), _ptr(z), _ptr(depth), _ptr(rays_d), n, s, c, ctx.tol, ctx.dw,
+                                              _ptr(partials), _ptr(d_loss), _ptr(d_raw), _stream()),
+              "dmnerf_penalizer_bwd")
+        _count()
+        return d_raw, None, None, None, None, None
+
+
+def penalizer(raw, z, depth, rays_d, tolerance: float, deta_w: float) -> torch.Tensor:
+    return _PenalizerFn.apply(raw, z, depth.reshape(-1).detach(), rays_d, float(tolerance), float(deta_w))
+
+
+# ---------------------------------------------------------------------------------------------------
+# exchanger / rays / labels
+# ---------------------------------------------------------------------------------------------------
+
+
+def exchange(ori_raw, tar_raw, ori_acc, tar_acc, move_label: int, ori_label: Optional[torch.Tensor]):
+    """One move label, in place on ori_raw.  Returns (ori_label, tar_label) int64 [n,s]."""
+    if not (ori_raw.is_cuda and ori_raw.dtype == torch.float32 and ori_raw.is_contiguous()):
+        raise RuntimeError("exchanger: ori_raw must be a contiguous fp32 CUDA tensor (it is edited in place)")
+    tar_raw, ori_acc, tar_acc = _f32(tar_raw, "tar_raw"), _f32(ori_acc, "ori_raw_pred"), _f32(tar_acc, "tar_raw_pred")
+    n, s, c = ori_raw.shape
+    first = ori_label is None
+    if first:
+        ori_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device)
+    tar_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device)
+    check(_lib.lib().dmnerf_exchange(_ptr(ori_raw), _ptr(tar_raw), _ptr(ori_acc), _ptr(tar_acc), int(move_label),
+                                     int(first), n, s, c, _ptr(ori_label), _ptr(tar_label), _stream()),
+          "dmnerf_exchange")
+    _count()
+    return ori_label, tar_label
+
+
+def embed(x, n_freqs: int) -> torch.Tensor:
+    x = _f32(x, "inputs")
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, 3)
+    out = torch.empty((x2.shape[0], 3 + 6 * n_freqs), dtype=torch.float32, device=x.device)
+    check(_lib.lib().dmnerf_embed(_ptr(x2), x2.shape[0], n_freqs, _ptr(out), _stream()), "dmnerf_embed")
+    _count()
+    return out.reshape(*lead, 3 + 6 * n_freqs)
+
+
+def rays_k(H: int, W: int, K, c2w, pix0: int, n: int, device, pix_idx: Optional[torch.Tensor] = None
+           ) -> Tuple[torch.Tensor, torch.Tensor]:
+    kf = (C.c_float * 9)(*[float(v) for v in torch.as_tensor(K, dtype=torch.float32).cpu().reshape(-1)[:9]])
+    cm = torch.as_tensor(c2w, dtype=torch.float32).cpu()[:3, :4].reshape(-1)
+    cf = (C.c_float * 12)(*[float(v) for v in cm])
+    ro = torch.empty((n, 3), dtype=torch.float32, device=device)
+    rd = torch.empty((n, 3), dtype=torch.float32, device=device)
+    if pix_idx is not None:
+        pix_idx = pix_idx.to(device=device, dtype=torch.int64).contiguous()
+    check(_lib.lib().dmnerf_rays_k(H, W, kf, cf, pix0, _ptr(pix_idx), n, _ptr(ro), _ptr(rd), _stream()),
+          "dmnerf_rays_k")
+    _count()
+    return ro, rd
+
+
+def label_argmax(ins) -> torch.Tensor:
+    ins = _f32(ins, "ins")
+    n, k = ins.shape
+    out = torch.empty((n,), dtype=torch.uint8, device=ins.device)
+    check(_lib.lib().dmnerf_label_argmax(_ptr(ins), n, k, _ptr(out), _stream()), "dmnerf_label_argmax")
+    _count()
+    return out

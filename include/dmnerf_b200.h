@@ -1,0 +1,147 @@
+/* dmnerf_b200.h -- C ABI of libdmnerf_b200.so (hand-written sm_100a CUDA for DM-NeRF's
+ * per-ray hot path).  This is the drop-in boundary: plain pointers and sizes only, no torch
+ * types.  The reference (ChenLu-china/DM-NeRF) is pure Python with no FFI layer, so each entry
+ * point cites the reference *function* it stands in for (paths relative to the reference root);
+ * dm_nerf_b200/networks/*.py is the ctypes host side that mirrors the reference's call surface.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer to fp32 row-major contiguous data unless stated;
+ *  - the caller owns every buffer; nothing is allocated inside;
+ *  - calls enqueue on `stream` (a cudaStream_t passed as void*) and never synchronise;
+ *  - return 0 on success, a DMNERF_E* code otherwise; text via dmnerf_last_error();
+ *  - supported network shape (the only one config.py:23-26,56-59,153 ever builds):
+ *    D=8, W=256, skips=[4], L_pos=10 (63 ch), L_dir=4 (27 ch), 1 <= ins_num <= 123,
+ *    n_samples <= 1024.  Anything else is DMNERF_EUNSUPPORTED (there is no fallback).
+ */
+#ifndef DMNERF_B200_H
+#define DMNERF_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DMNERF_OK            0
+#define DMNERF_EINVAL        1   /* null pointer / bad size / misaligned */
+#define DMNERF_EUNSUPPORTED  2   /* shape outside the supported contract */
+#define DMNERF_ECUDA         3   /* a CUDA runtime call failed */
+
+#define DMNERF_MODE_FP32     0   /* CUDA-core fp32 FFMA chain: <=1e-4 parity mode            */
+#define DMNERF_MODE_BF16     1   /* tcgen05 bf16 tensor-core chain (fp32 accumulate in TMEM) */
+
+#define DMNERF_NUM_PARAMS   30   /* tensors in DM_NeRF.state_dict(), networks/dm_nerf.py:65-78 */
+
+/* composite flags */
+#define DMNERF_COMP_DROP_EMPTY 1 /* render_train: ins_map[..., :-1] (render.py:26)            */
+#define DMNERF_COMP_RAW_INS    2 /* do not sigmoid the accumulated instance logits            */
+
+int  dmnerf_version(void);
+int  dmnerf_last_error(char* buf, int cap);        /* copies the last message, returns its length */
+int  dmnerf_built_arch(void);                      /* 100 => sm_100a image present               */
+
+/* ---- weights -------------------------------------------------------------------------------
+ * params: HOST array of DMNERF_NUM_PARAMS device pointers in state_dict order:
+ *   mlps.0..7 {weight,bias}, rgb_feature_linear, ins_feature_linear, rgb_feature_linears.0,
+ *   ins_feature_linears.0, density_linear, ins_linear, rgb_linear  (networks/dm_nerf.py:65-78).
+ * The packed image is a derived cache (K-major tiles, padded, fp32 or bf16 by mode); refresh it
+ * after every optimizer step. */
+int64_t dmnerf_packed_bytes(int ins_num, int mode);
+int  dmnerf_weights_pack(const float* const* params, int ins_num, int mode, void* packed, void* stream);
+
+/* ---- a1+a2+a9: embedding + DM_NeRF MLP ------------------------------------------------------
+ * Replaces Embedder.embed + DM_NeRF.forward (networks/dm_nerf.py:37-38, 80-106) as called from
+ * dm_nerf (networks/render.py:49-61, 71-83) and manipulator_nerf (networks/manipulator.py:108-134).
+ * rays_o, rays_d [n_rays,3]; z [n_rays,n_samples]; raw_out [n_rays,n_samples,5+ins_num].
+ * Points o + d*z, view dirs d/|d| and both embeddings are computed in-kernel.
+ * acts (may be NULL): training-mode activation stash of dmnerf_acts_bytes() bytes for the backward. */
+int  dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
+                    const void* packed, int ins_num, int mode, float* raw_out, void* acts, void* stream);
+/* Same network on already-embedded rows x[m,90] (DM_NeRF.forward(x) called directly,
+ * tools/mesh_generator.py:45). */
+int  dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int ins_num, int mode,
+                             float* raw_out, void* acts, void* stream);
+int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num);
+/* a12: parameter gradients of the MLP given d(raw) [n_points, 5+ins_num].  packed: the
+ * DMNERF_MODE_FP32 image of the SAME weights the forward used; acts: the stash that forward wrote.
+ * grads: HOST array of DMNERF_NUM_PARAMS device pointers (same order/shapes as params), ACCUMULATED
+ * into (caller zeroes).  Honors h.detach() on the instance branch (networks/dm_nerf.py:95): the
+ * instance head's gradient stops at ins_feature_linear.  workspace: dmnerf_bwd_workspace_bytes(). */
+int  dmnerf_mlp_bwd(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
+                    int ins_num, float* const* grads, void* workspace, void* stream);
+int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num);
+
+/* ---- a5/a8: volume compositing ---------------------------------------------------------------
+ * Replaces render_train (networks/render.py:6-28) [flags=DROP_EMPTY] and manipulator_render
+ * (networks/manipulator.py:86-105) [flags=0].  raw [n,s,c]; z [n,s]; rays_d [n,3];
+ * rgb [n,3]; depth [n]; weights [n,s] (may be NULL); ins [n, c-4-(DROP_EMPTY?1:0)]. */
+int  dmnerf_composite_fwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
+                          int flags, float* rgb, float* depth, float* weights, float* ins, void* stream);
+/* Backward of the above.  d_ins touches only raw[...,4:] when ins_detach!=0 (render.py:22-24).
+ * Any of d_rgb/d_depth/d_weights/d_ins may be NULL (= zero).  d_raw [n,s,c] is overwritten. */
+int  dmnerf_composite_bwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
+                          int flags, int ins_detach, const float* d_rgb, const float* d_depth,
+                          const float* d_weights, const float* d_ins, float* d_raw, void* stream);
+
+/* ---- a4: hierarchical sampler ------------------------------------------------------------------
+ * Replaces sample_pdf (networks/helpers.py:123-155).  bins [n,n_bins]; weights [n,n_bins-1];
+ * u: uniforms, row r at u + r*u_stride (u_stride = n_samples for a dense [n,n_samples] tensor, 0 to
+ * broadcast one row, e.g. torch.linspace(0,1,n_samples) for det); u == NULL -> in-kernel linspace(0,1).
+ * z_out [n,n_samples]; inds_out (int64 [n,n_samples], the searchsorted(right=True) result) may be NULL.
+ * The CDF is summed in a fixed sequential fp32 order (see csrc/sampler.cu). */
+int  dmnerf_sample_pdf(const float* bins, const float* weights, const float* u, int64_t u_stride, int64_t n,
+                       int n_bins, int n_samples, float* z_out, int64_t* inds_out, void* stream);
+/* Strict variant: the caller supplies cdf [n,n_bins] (e.g. computed by torch); searchsorted, gather
+ * and lerp only -- indices and samples are bit-exact with ATen given identical cdf and u. */
+int  dmnerf_sample_cdf(const float* bins, const float* cdf, const float* u, int64_t u_stride, int64_t n,
+                       int n_bins, int n_samples, float* z_out, int64_t* inds_out, void* stream);
+/* Fused coarse tail of dm_nerf (networks/render.py:66-70): mids of z_coarse, sample_pdf on
+ * weights[:,1:-1] (weights is the full [n,sc] compositing output), sorted merge of z_coarse and the
+ * new samples.  z_fine [n, sc+n_imp]; z_samples [n,n_imp] may be NULL. */
+int  dmnerf_fine_z(const float* z_coarse, const float* weights, const float* u, int64_t u_stride, int64_t n,
+                   int sc, int n_imp, float* z_fine, float* z_samples, void* stream);
+/* Sorted merge of `parts` ascending-unsorted rows: out[n, sum(len)] = sort(cat(...)) along the
+ * last dim (networks/manipulator.py:190,195).  srcs/lens are HOST arrays (<= 8 parts). */
+int  dmnerf_sort_cat(const float* const* srcs, const int* lens, int parts, int64_t n, float* out, void* stream);
+/* Stratified jitter of the coarse depths (networks/render.py:40-47). */
+int  dmnerf_jitter_z(const float* z, const float* t_rand, int64_t n, int s, float* z_out, void* stream);
+
+/* ---- a7: emptiness penalizer --------------------------------------------------------------------
+ * Replaces ins_penalizer/emptiness_penalizer (networks/penalizer.py:5-62).  partials: 4 floats
+ * (device) = {sum_before, count_before, sum_middle, count_middle}; zeroed by the call.
+ * loss (device scalar) = sum_before/((K+1)*max(count_before,1e-8)) + sum_middle/max(count_middle,1e-8). */
+int  dmnerf_penalizer_fwd(const float* raw, const float* z, const float* depth, const float* rays_d,
+                          int64_t n, int s, int c, float tolerance, float deta_w, float* partials,
+                          float* loss, void* stream);
+/* d_raw[n,s,c] = d_loss * dLoss/draw (channels 0..3 are written as 0). d_loss: device scalar. */
+int  dmnerf_penalizer_bwd(const float* raw, const float* z, const float* depth, const float* rays_d,
+                          int64_t n, int s, int c, float tolerance, float deta_w, const float* partials,
+                          const float* d_loss, float* d_raw, void* stream);
+
+/* ---- a10: exchanger -------------------------------------------------------------------------------
+ * Replaces exchanger (networks/manipulator.py:18-83) for ONE move label; call once per label in
+ * order (the reference's in-place order dependence is preserved through ori_label).
+ * ori_raw [n,s,c] is edited in place; tar_raw [n,s,c]; ori_acc/tar_acc [n,c-4] (already sigmoided
+ * accumulated maps); ori_label int64 [n,s] in/out (first_label!=0: initialise it from ori_raw);
+ * tar_label int64 [n,s] out. */
+int  dmnerf_exchange(float* ori_raw, const float* tar_raw, const float* ori_acc, const float* tar_acc,
+                     int move_label, int first_label, int64_t n, int s, int c, int64_t* ori_label,
+                     int64_t* tar_label, void* stream);
+
+/* ---- adjacent (8f-1): pinhole ray generation --------------------------------------------------------
+ * Replaces get_rays_k (networks/helpers.py:50-61) for pixels [pix0, pix0+n) of an HxW frame
+ * (row-major, pixel = j*W+i).  K: 9 floats, c2w: 12 floats (3x4 row-major), both HOST. */
+int  dmnerf_rays_k(int H, int W, const float* K_host, const float* c2w_host, int64_t pix0,
+                   const int64_t* pix_idx /* device, may be NULL: then pixels pix0..pix0+n-1 */, int64_t n,
+                   float* rays_o, float* rays_d, void* stream);
+/* Standalone Embedder.embed (networks/dm_nerf.py:37-38): x [n,3] -> out [n, 3+6*n_freqs]. */
+int  dmnerf_embed(const float* x, int64_t n, int n_freqs, float* out, void* stream);
+/* Per-ray label image: argmax over sigmoid'ed instance map (first max wins), uint8 out. */
+int  dmnerf_label_argmax(const float* ins, int64_t n, int k, uint8_t* labels, void* stream);
+
+/* ---- self test of the tcgen05 building blocks (used by tests/) ---------------------------------------
+ * D[128,n] = A[128,k] * B[n,k]^T in bf16 with fp32 accumulate; a,b fp32 in, d fp32 out. */
+int  dmnerf_selftest_umma(const float* a, const float* b, int n, int k, float* d, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
