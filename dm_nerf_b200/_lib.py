@@ -80,6 +80,7 @@ _SIGNATURES = {
     "dmnerf_embed": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_label_argmax": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_selftest_umma": (_int, [_p, _p, _int, _int, _p, _p]),
+    "dmnerf_debug_flags": (_int, [_int]),
 }
 
 EXPORTS = tuple(_SIGNATURES)

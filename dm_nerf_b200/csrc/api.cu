@@ -94,6 +94,7 @@ static int run_mlp(const MlpInput& in, const void* packed, int ins_num, int mode
 
 extern "C" int dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
                               const void* packed, int ins_num, int mode, float* raw_out, void* acts, void* stream) {
+    if (n_rays == 0) return DMNERF_OK;
     DM_REQUIRE(rays_o && rays_d && z, DMNERF_EINVAL, "mlp_fwd: null ray pointer");
     DM_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 4096, DMNERF_EUNSUPPORTED,
                "mlp_fwd: n_samples %d outside [1,4096]", n_samples);
@@ -103,6 +104,7 @@ extern "C" int dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const fl
 
 extern "C" int dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int ins_num, int mode,
                                        float* raw_out, void* acts, void* stream) {
+    if (m == 0) return DMNERF_OK;
     DM_REQUIRE(x, DMNERF_EINVAL, "mlp_fwd_embedded: null input");
     MlpInput in{nullptr, nullptr, nullptr, x, m, 1};
     return run_mlp(in, packed, ins_num, mode, raw_out, acts, stream);

@@ -277,6 +277,7 @@ using namespace dmnerf;
 
 extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
                                     int flags, float* rgb, float* depth, float* weights, float* ins, void* stream) {
+    if (n == 0) return DMNERF_OK;
     DM_REQUIRE(raw && z && rays_d && rgb && depth && ins, DMNERF_EINVAL, "composite_fwd: null pointer");
     DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_fwd: n_samples %d outside [1,1024]", s);
     DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "composite_fwd: channels %d outside [6,128]", c);
@@ -294,6 +295,7 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
 extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
                                     int flags, int ins_detach, const float* d_rgb, const float* d_depth,
                                     const float* d_weights, const float* d_ins, float* d_raw, void* stream) {
+    if (n == 0) return DMNERF_OK;
     DM_REQUIRE(raw && z && rays_d && d_raw, DMNERF_EINVAL, "composite_bwd: null pointer");
     DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_bwd: n_samples %d outside [1,1024]", s);
     DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "composite_bwd: channels %d outside [6,128]", c);

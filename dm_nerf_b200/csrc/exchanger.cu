@@ -167,6 +167,7 @@ extern "C" int dmnerf_embed(const float* x, int64_t n, int n_freqs, float* out, 
 extern "C" int dmnerf_exchange(float* ori_raw, const float* tar_raw, const float* ori_acc, const float* tar_acc,
                                int move_label, int first_label, int64_t n, int s, int c, int64_t* ori_label,
                                int64_t* tar_label, void* stream) {
+    if (n <= 0) return DMNERF_OK;
     DM_REQUIRE(ori_raw && tar_raw && ori_acc && tar_acc && ori_label && tar_label, DMNERF_EINVAL,
                "exchange: null pointer");
     DM_REQUIRE(s >= 1 && c >= 7 && c <= 128, DMNERF_EUNSUPPORTED, "exchange: n_samples %d / channels %d unsupported",

@@ -1,8 +1,528 @@
-// mlp_tc.cu -- tcgen05 bf16 path (placeholder until the kernel lands).
+// mlp_tc.cu -- a1+a2+a9 in DMNERF_MODE_BF16: positional encoding + the whole DM_NeRF MLP as ONE
+// persistent tcgen05 kernel.  bf16 operands, fp32 accumulation in TMEM, layers chained through
+// shared memory (activations never touch HBM), weights streamed L2 -> smem by the TMA engine
+// (1-D bulk async copies into a 3-stage mbarrier ring).
+//
+// Work decomposition: one CTA per SM, each looping over pairs of 128-point tiles (X, Y).  Both
+// tiles walk the layers in lockstep so every streamed weight chunk feeds 4 MMAs (2 k-steps x 2
+// tiles).  Warp roles: warps 0-3 epilogue of X, warps 4-7 epilogue of Y (thread == point/TMEM lane),
+// warp 8 weight producer, warp 9 MMA issuer (one elected thread) + TMEM owner.
+//
+// Layers as the tensor path sees them (the two linear->linear pairs of the reference are composed
+// at pack time: rgb_feature_linear o rgb_feature_linears.0 and ins_feature_linear o
+// ins_feature_linears.0 have no activation between them, networks/dm_nerf.py:89-99):
+//   T0      K= 64  N=256  relu   A = pos-embedding (EXT region)
+//   T1..T4  K=256  N=256  relu
+//   T5      K=320  N=256  relu   A = [h | pos-embedding]
+//   T6,T7   K=256  N=256  relu   (T7's epilogue also takes the density dot product in fp32)
+//   T8      K=288  N=256  relu   A = [h7 | dir-embedding]; rows 0..127 rgb_hid, 128..255 ins_hid
+//   T9      K=256  N=Np   -      A = [rgb_hid | ins_hid]; block-diagonal rgb / ins heads, Np = round16(C)
+//
+// Operand layout (A and B, both K-major, no swizzle): [k-group of 8][row][8 bf16] -> 8x16-byte core
+// matrices are 128 contiguous bytes; LBO (next k-group) = rows*16 B, SBO (next 8 rows) = 128 B.  An
+// epilogue thread owns one row, so one 16-byte store writes 8 consecutive features of the next
+// layer's A operand and a warp's stores are 512 contiguous bytes (conflict-free).
 #include "mlp_layout.cuh"
+#include "tc_ptx.cuh"
+#include <cuda_bf16.h>
+
 namespace dmnerf {
-int64_t bf16_image_bytes(int) { return -1; }
-int pack_bf16(const float* const*, int, void*, cudaStream_t) { set_error("bf16 mode: not built yet"); return DMNERF_EUNSUPPORTED; }
-int launch_mlp_bf16(const MlpInput&, const void*, int, float*, cudaStream_t) { set_error("bf16 mode: not built yet"); return DMNERF_EUNSUPPORTED; }
+
+static int g_tc_debug_flags = 0;   // bit0: swap LBO/SBO in the smem descriptors (bring-up aid)
+
+namespace tc {
+
+constexpr int kTile = 128;
+constexpr int kPair = 2 * kTile;
+constexpr int kLayers = 10;
+constexpr int kChunkK = 32;                       // K columns per streamed weight chunk
+constexpr int kStages = 3;
+constexpr int kStageBytes = kChunkK * 256 * 2;    // 16 KB
+constexpr int kKgBytes = kTile * 16;              // one k-group of the A operand: 128 rows x 16 B
+constexpr int kABytes = 40 * kKgBytes;            // 32 k-groups H + 8 k-groups EXT = 81,920 B per tile
+constexpr int kExtKg = 32;                        // first k-group of the EXT region
+constexpr int kBiasFloats = 2704;                 // 9*256 | T9 bias (128) | w_density (256) | b_density (+pad)
+constexpr int kBiasT9 = 9 * 256;
+constexpr int kBiasWd = kBiasT9 + 128;
+constexpr int kBiasBd = kBiasWd + 256;
+constexpr int kThreads = 320;
+
+// shared memory map (bytes)
+constexpr int kSmA = 0;
+constexpr int kSmRing = 2 * kABytes;                           // 163,840
+constexpr int kSmBias = kSmRing + kStages * kStageBytes;       // 212,992
+constexpr int kSmBar = kSmBias + kBiasFloats * 4;              // 223,808
+constexpr int kSmTotal = kSmBar + 128;                         // barriers + tmem slot
+
+__host__ __device__ inline int layer_k(int l) { return l == 0 ? 64 : (l == 5 ? 320 : (l == 8 ? 288 : 256)); }
+__host__ __device__ inline int layer_akg0(int l) { return l == 0 ? kExtKg : 0; }
+
+struct Image {
+    int64_t chunk_off[kLayers];   // byte offset of the layer's first chunk
+    int n[kLayers];               // MMA N of the layer
+    int64_t bias_off;             // fp32 block (kBiasFloats)
+    int64_t scratch_off;          // fp32 scratch: Wc_rgb[128][256], Wc_ins[128][256], bc[256]
+    int64_t total_bytes;
+    int npad, ins_num;
+};
+
+__host__ __device__ inline Image make_image(int ins_num) {
+    Image im;
+    im.ins_num = ins_num;
+    im.npad = ((ins_num + 5) + 15) & ~15;
+    int64_t off = 0;
+    for (int l = 0; l < kLayers; ++l) {
+        im.n[l] = (l == 9) ? im.npad : 256;
+        im.chunk_off[l] = off;
+        off += static_cast<int64_t>(layer_k(l)) * im.n[l] * 2;
+    }
+    im.bias_off = off;       off += kBiasFloats * 4;
+    im.scratch_off = off;    off += (2 * 128 * 256 + 256) * 4;
+    im.total_bytes = off;
+    return im;
+}
+
+// ---- pack --------------------------------------------------------------------------------------------
+struct Params { const float* p[kNumParams]; };
+
+// composed weights: Wc[i][k] = sum_j W1[i][j] * W0[j][k]  (W1 = *_feature_linears.0[:, :256], W0 = *_feature_linear)
+// bc[i] = sum_j W1[i][j]*b0[j] + b1[i].  scratch: [0,32768) rgb, [32768,65536) ins, then bc[256].
+__global__ void compose_kernel(Params pr, float* __restrict__ scratch) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;     // 2*128*256 + 256 work items
+    if (idx < 2 * 128 * 256) {
+        const int br = idx >> 15, i = (idx >> 8) & 127, k = idx & 255;
+        const float* w1 = br == 0 ? pr.p[P_RGB0_W] : pr.p[P_INS0_W];
+        const float* w0 = br == 0 ? pr.p[P_RGBF_W] : pr.p[P_INSF_W];
+        const int ld1 = br == 0 ? 283 : 256;
+        float a = 0.f;
+        for (int j = 0; j < 256; ++j) a = fmaf(w1[i * ld1 + j], w0[j * 256 + k], a);
+        scratch[idx] = a;
+    } else if (idx < 2 * 128 * 256 + 256) {
+        const int r = idx - 2 * 128 * 256, br = r >> 7, i = r & 127;
+        const float* w1 = br == 0 ? pr.p[P_RGB0_W] : pr.p[P_INS0_W];
+        const float* b0 = br == 0 ? pr.p[P_RGBF_B] : pr.p[P_INSF_B];
+        const float* b1 = br == 0 ? pr.p[P_RGB0_B] : pr.p[P_INS0_B];
+        const int ld1 = br == 0 ? 283 : 256;
+        float a = 0.f;
+        for (int j = 0; j < 256; ++j) a = fmaf(w1[i * ld1 + j], b0[j], a);
+        scratch[idx] = a + b1[i];
+    }
+}
+
+__device__ inline float logical_weight(const Params& pr, const float* scratch, int l, int n, int k, int ins_num) {
+    if (l == 0) return k < 63 ? pr.p[0][n * 63 + k] : 0.f;
+    if (l == 5) return k < 319 ? pr.p[10][n * 319 + k] : 0.f;
+    if (l <= 7) return pr.p[2 * l][n * 256 + k];
+    if (l == 8) {
+        if (n < 128) {
+            if (k < 256) return scratch[n * 256 + k];
+            return k < 283 ? pr.p[P_RGB0_W][n * 283 + k] : 0.f;
+        }
+        return k < 256 ? scratch[32768 + (n - 128) * 256 + k] : 0.f;
+    }
+    // l == 9: block-diagonal heads.  rows 0..2 rgb (k<128), row 3 density (filled in the epilogue), rows 4.. ins
+    if (n < 3) return k < 128 ? pr.p[P_RGBL_W][n * 128 + k] : 0.f;
+    if (n >= 4 && n < 5 + ins_num) return k >= 128 ? pr.p[P_INSL_W][(n - 4) * 128 + (k - 128)] : 0.f;
+    return 0.f;
+}
+
+// one thread per bf16 element of the chunk stream: layer l, chunk c, k-group g, row n, element e
+__global__ void pack_bf16_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+    const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
+    const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t total = im.bias_off / 2;
+    if (idx >= total) return;
+    int l = 0;
+    while (l + 1 < kLayers && idx * 2 >= im.chunk_off[l + 1]) ++l;
+    const int N = im.n[l];
+    int64_t r = idx - im.chunk_off[l] / 2;
+    const int per_chunk = kChunkK * N;
+    const int c = static_cast<int>(r / per_chunk);
+    r -= static_cast<int64_t>(c) * per_chunk;
+    const int g = static_cast<int>(r / (N * 8));
+    r -= static_cast<int64_t>(g) * N * 8;
+    const int n = static_cast<int>(r >> 3), e = static_cast<int>(r & 7);
+    const int k = c * kChunkK + g * 8 + e;
+    reinterpret_cast<__nv_bfloat16*>(image)[idx] = __float2bfloat16_rn(logical_weight(pr, scratch, l, n, k, im.ins_num));
+}
+
+__global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+    const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
+    float* b = reinterpret_cast<float*>(image + im.bias_off);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= kBiasFloats) return;
+    float v = 0.f;
+    if (i < 8 * 256) v = pr.p[2 * (i >> 8) + 1][i & 255];
+    else if (i < 9 * 256) v = scratch[65536 + (i - 8 * 256)];
+    else if (i < kBiasWd) {
+        const int n = i - kBiasT9;
+        if (n < 3) v = pr.p[P_RGBL_B][n];
+        else if (n >= 4 && n < 5 + im.ins_num) v = pr.p[P_INSL_B][n - 4];
+    } else if (i < kBiasBd) v = pr.p[P_DENS_W][i - kBiasWd];
+    else if (i == kBiasBd) v = pr.p[P_DENS_B][0];
+    b[i] = v;
+}
+
+
+// ---- device helpers ---------------------------------------------------------------------------------------
+// mbarrier addresses (8 B each) inside the barrier block
+struct Bars {
+    uint32_t base;
+    __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }
+    __device__ __forceinline__ uint32_t w_empty(int s) const { return base + 8 * (kStages + s); }
+    __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kStages + t); }
+    __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kStages + 2 + t); }
+};
+
+__device__ __forceinline__ uint64_t op_desc(uint32_t addr, uint32_t lbo, uint32_t sbo, int swap) {
+    return swap ? ptx::smem_desc(addr, sbo, lbo) : ptx::smem_desc(addr, lbo, sbo);
+}
+
+// 8 consecutive features of one row -> one 16-byte store into k-group `kg` of the A operand
+__device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const float v[8], bool relu) {
+    ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, ptx::pack_bf16(v[0], v[1], relu), ptx::pack_bf16(v[2], v[3], relu),
+                      ptx::pack_bf16(v[4], v[5], relu), ptx::pack_bf16(v[6], v[7], relu));
+}
+
+// Embedding of a 3-vector with F octaves into EXT k-groups: channel c = [x | f: sin(3) cos(3)].  The first
+// octave uses full-range sincosf; higher octaves follow by angle doubling (error << bf16 resolution).
+template <int F>
+__device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3]) {
+    constexpr int CH = 3 + 6 * F;
+    constexpr int KG = (CH + 7) / 8;
+    float ch[KG * 8];
+#pragma unroll
+    for (int i = 0; i < KG * 8; ++i) ch[i] = 0.f;
+    float s[3], c[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { ch[d] = x[d]; sincosf(x[d], &s[d], &c[d]); }
+#pragma unroll
+    for (int f = 0; f < F; ++f) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            ch[3 + 6 * f + d] = s[d];
+            ch[3 + 6 * f + 3 + d] = c[d];
+            const float s2 = 2.f * s[d] * c[d];
+            const float c2 = (c[d] - s[d]) * (c[d] + s[d]);
+            s[d] = s2; c[d] = c2;
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < KG; ++g) store_kg(a_base, kExtKg + g, row, &ch[g * 8], false);
+}
+
+__device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kgs) {
+    for (int g = 0; g < kgs; ++g) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = (src && g * 8 + e < count) ? __ldg(src + g * 8 + e) : 0.f;
+        store_kg(a_base, kExtKg + g, row, v, false);
+    }
+}
+
+// ---- the kernel -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1)
+mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sm0 = ptx::smem_u32(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const Bars bars{sm0 + kSmBar};
+    float* s_bias = reinterpret_cast<float*>(smem + kSmBias);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kSmBar + 8 * (2 * kStages + 4));
+    const int swap = flags & 1;
+    const int C = im.ins_num + 5;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
+        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 9) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
+    {
+        const float* gb = reinterpret_cast<const float*>(image + im.bias_off);
+        for (int i = threadIdx.x; i < kBiasFloats; i += kThreads) s_bias[i] = gb[i];
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const int64_t n_pairs = (in.n_points + kPair - 1) / kPair;
+
+    if (warp == 8) {
+        // ===== weight producer: walks the chunk stream of every layer for every tile pair =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+                for (int l = 0; l < kLayers; ++l) {
+                    const uint32_t bytes = kChunkK * im.n[l] * 2;
+                    const int chunks = layer_k(l) / kChunkK;
+                    const uint8_t* src = image + im.chunk_off[l];
+                    for (int c = 0; c < chunks; ++c) {
+                        ptx::mbar_wait(bars.w_empty(stage), phase ^ 1);
+                        ptx::mbar_arrive_expect_tx(bars.w_full(stage), bytes);
+                        ptx::bulk_g2s(sm0 + kSmRing + stage * kStageBytes, src + static_cast<int64_t>(c) * bytes, bytes,
+                                      bars.w_full(stage));
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+            // drain: every stage's last release (tcgen05.commit arrive) must have landed before the CTA exits
+            for (int i = 0; i < kStages; ++i) {
+                ptx::mbar_wait(bars.w_empty(stage), phase ^ 1);
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 9) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0, a_par[2] = {0, 0};
+            for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+                for (int l = 0; l < kLayers; ++l) {
+                    const int N = im.n[l];
+                    const uint32_t idesc = ptx::idesc_bf16(kTile, N);
+                    const int chunks = layer_k(l) / kChunkK;
+                    const int kg0 = layer_akg0(l);
+                    for (int c = 0; c < chunks; ++c) {
+                        ptx::mbar_wait(bars.w_full(stage), phase);
+                        ptx::tc_fence_after();
+                        const uint32_t b_base = sm0 + kSmRing + stage * kStageBytes;
+#pragma unroll
+                        for (int t = 0; t < 2; ++t) {
+                            if (c == 0) {
+                                ptx::mbar_wait(bars.a_ready(t), a_par[t]);
+                                a_par[t] ^= 1;
+                                ptx::tc_fence_after();
+                            }
+                            const uint32_t a_base = sm0 + kSmA + t * kABytes;
+#pragma unroll
+                            for (int kk = 0; kk < 2; ++kk) {
+                                const uint64_t ad = op_desc(a_base + (kg0 + c * 4 + kk * 2) * kKgBytes, kKgBytes, 128, swap);
+                                const uint64_t bd = op_desc(b_base + kk * 2 * (N * 16), N * 16, 128, swap);
+                                ptx::umma_bf16(tmem + t * 256, ad, bd, idesc, (c | kk) != 0);
+                            }
+                            if (c == chunks - 1) ptx::umma_commit(bars.acc_ready(t));
+                        }
+                        ptx::umma_commit(bars.w_empty(stage));
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else {
+        // ===== epilogue / embedding: thread == one point of tile t == one TMEM lane =====
+        const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
+        const uint32_t a_base = sm0 + kSmA + t * kABytes;
+        const uint32_t t_base = tmem + t * 256 + (static_cast<uint32_t>(q * 32) << 16);
+        float* stage_out = reinterpret_cast<float*>(smem + kSmA + t * kABytes);
+        uint32_t acc_par = 0;
+        for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+            const int64_t tile0 = pair * kPair + t * kTile;
+            const int64_t p = tile0 + row;
+            const bool valid = p < in.n_points;
+            float dir[3] = {0.f, 0.f, 0.f};
+            if (in.x == nullptr) {
+                float pos[3] = {0.f, 0.f, 0.f};
+                if (valid) {
+                    const int64_t ray = p / in.S;
+                    const float zz = __ldg(in.z + p);
+                    float d[3];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        d[c] = __ldg(in.rays_d + ray * 3 + c);
+                        pos[c] = __fadd_rn(__ldg(in.rays_o + ray * 3 + c), __fmul_rn(d[c], zz));
+                    }
+                    const float inv = 1.0f / sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) dir[c] = d[c] * inv;
+                }
+                embed_to_ext<kPosFreqs>(a_base, row, pos);
+            } else {
+                row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, 8);
+            }
+            ptx::fence_proxy_async_smem();
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(bars.a_ready(t));
+
+            float dens = 0.f;
+            for (int l = 0; l < kLayers - 1; ++l) {
+                ptx::mbar_wait(bars.acc_ready(t), acc_par);
+                acc_par ^= 1;
+                ptx::tc_fence_after();
+                const float* bias = s_bias + l * 256;
+#pragma unroll 1
+                for (int cb = 0; cb < 8; ++cb) {
+                    uint32_t r[32];
+                    ptx::tmem_ld32(t_base + cb * 32, r);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float v[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]) + bias[cb * 32 + g * 8 + e];
+                        if (l == 7) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_bias[kBiasWd + cb * 32 + g * 8 + e], dens);
+                        }
+                        store_kg(a_base, cb * 4 + g, row, v, true);
+                    }
+                }
+                if (l == 7) {
+                    // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it)
+                    if (in.x == nullptr) embed_to_ext<kDirFreqs>(a_base, row, dir);
+                    else row_to_ext(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 4);
+                }
+                ptx::fence_proxy_async_smem();
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(bars.a_ready(t));
+            }
+            // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored ----
+            ptx::mbar_wait(bars.acc_ready(t), acc_par);
+            acc_par ^= 1;
+            ptx::tc_fence_after();
+            for (int cb = 0; cb * 16 < im.npad; ++cb) {
+                uint32_t r[16];
+                ptx::tmem_ld16(t_base + cb * 16, r);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int col = cb * 16 + e;
+                    if (col < C) {
+                        float v = __uint_as_float(r[e]) + s_bias[kBiasT9 + col];
+                        if (col == 3) v = dens + s_bias[kBiasBd];
+                        stage_out[row * C + col] = v;
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            ptx::fence_proxy_async_smem();
+            ptx::named_bar_sync(1 + t, kTile);
+            const int64_t rows_left = in.n_points - tile0;
+            if (rows_left >= kTile) {
+                if (row == 0) {
+                    ptx::bulk_s2g(raw_out + tile0 * C, ptx::smem_u32(stage_out), kTile * C * 4);
+                    ptx::bulk_commit();
+                    ptx::bulk_wait_read0();
+                }
+            } else if (rows_left > 0) {
+                const int total = static_cast<int>(rows_left) * C;
+                for (int i = row; i < total; i += kTile) raw_out[tile0 * C + i] = stage_out[i];
+            }
+            // the next write into this region is T0's epilogue of the next pair, which cannot start before
+            // all 128 threads (incl. the bulk-store issuer, after its read-wait) arrived on a_ready again.
+            ptx::named_bar_sync(1 + t, kTile);
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem, 512);
+    }
+}
+
+// ---- bring-up self test: D[128,n] = A[128,k] * B[n,k]^T through the same descriptors ------------------------
+__global__ void __launch_bounds__(128, 1)
+umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, int n, int k, float* __restrict__ d,
+                     int flags) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sm0 = ptx::smem_u32(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, row = threadIdx.x;
+    const uint32_t a_base = sm0, b_base = sm0 + 65536, bar = sm0 + 65536 + 131072;
+    volatile uint32_t* slot = reinterpret_cast<volatile uint32_t*>(smem + 65536 + 131072 + 8);
+    __nv_bfloat16* sa = reinterpret_cast<__nv_bfloat16*>(smem);
+    __nv_bfloat16* sb = reinterpret_cast<__nv_bfloat16*>(smem + 65536);
+    for (int i = threadIdx.x; i < 128 * k; i += 128) {
+        const int r = i / k, c = i - r * k;
+        sa[((c >> 3) * 128 + r) * 8 + (c & 7)] = __float2bfloat16_rn(a[i]);
+    }
+    for (int i = threadIdx.x; i < n * k; i += 128) {
+        const int r = i / k, c = i - r * k;
+        sb[((c >> 3) * n + r) * 8 + (c & 7)] = __float2bfloat16_rn(b[i]);
+    }
+    if (threadIdx.x == 0) { ptx::mbar_init(bar, 1); ptx::fence_barrier_init(); }
+    if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(slot)), 256);
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *slot;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = ptx::idesc_bf16(128, n);
+        for (int ks = 0; ks < k / 16; ++ks) {
+            const uint64_t ad = op_desc(a_base + ks * 2 * kKgBytes, kKgBytes, 128, flags & 1);
+            const uint64_t bd = op_desc(b_base + ks * 2 * (n * 16), n * 16, 128, flags & 1);
+            ptx::umma_bf16(tmem, ad, bd, idesc, ks != 0);
+        }
+        ptx::umma_commit(bar);
+    }
+    ptx::mbar_wait(bar, 0);
+    ptx::tc_fence_after();
+    for (int cb = 0; cb * 16 < n; ++cb) {
+        uint32_t r[16];
+        ptx::tmem_ld16(tmem + (static_cast<uint32_t>(warp * 32) << 16) + cb * 16, r);
+        ptx::tmem_ld_wait();
+        for (int e = 0; e < 16; ++e) d[row * n + cb * 16 + e] = __uint_as_float(r[e]);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 256); }
+    (void)lane;
+}
+
+}  // namespace tc
+
+int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, cudaStream_t st) {
+    static int sm_count = 0;
+    if (sm_count == 0) {
+        int dev = 0;
+        DM_CUDA(cudaGetDevice(&dev));
+        DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    DM_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0 && (reinterpret_cast<uintptr_t>(raw_out) & 15) == 0,
+               DMNERF_EINVAL, "mlp_fwd(bf16): packed image and raw_out must be 16-byte aligned");
+    DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmTotal));
+    const int64_t pairs = (in.n_points + tc::kPair - 1) / tc::kPair;
+    const unsigned grid = static_cast<unsigned>(pairs < sm_count ? pairs : sm_count);
+    tc::mlp_fwd_bf16_kernel<<<grid, tc::kThreads, tc::kSmTotal, st>>>(in, static_cast<const uint8_t*>(packed),
+                                                                     tc::make_image(ins_num), raw_out, g_tc_debug_flags);
+    DM_LAUNCH_CHECK("mlp_fwd_bf16_kernel");
+    return DMNERF_OK;
+}
+
+int64_t bf16_image_bytes(int ins_num) { return tc::make_image(ins_num).total_bytes; }
+
+int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st) {
+    const tc::Image im = tc::make_image(ins_num);
+    tc::Params pr;
+    for (int i = 0; i < kNumParams; ++i) pr.p[i] = params[i];
+    uint8_t* image = static_cast<uint8_t*>(packed);
+    float* scratch = reinterpret_cast<float*>(image + im.scratch_off);
+    tc::compose_kernel<<<(2 * 128 * 256 + 256 + 255) / 256, 256, 0, st>>>(pr, scratch);
+    const int64_t elems = im.bias_off / 2;
+    tc::pack_bf16_kernel<<<static_cast<unsigned>((elems + 255) / 256), 256, 0, st>>>(pr, im, image);
+    tc::pack_bias_kernel<<<(tc::kBiasFloats + 255) / 256, 256, 0, st>>>(pr, im, image);
+    DM_LAUNCH_CHECK("pack_bf16");
+    return DMNERF_OK;
+}
+
 }  // namespace dmnerf
-extern "C" int dmnerf_selftest_umma(const float*, const float*, int, int, float*, void*) { return DMNERF_EUNSUPPORTED; }
+
+using namespace dmnerf;
+
+extern "C" int dmnerf_debug_flags(int flags) {
+    const int old = g_tc_debug_flags;
+    if (flags >= 0) g_tc_debug_flags = flags;
+    return old;
+}
+
+extern "C" int dmnerf_selftest_umma(const float* a, const float* b, int n, int k, float* d, void* stream) {
+    DM_REQUIRE(a && b && d, DMNERF_EINVAL, "selftest_umma: null pointer");
+    DM_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0 && k >= 16 && k <= 256 && k % 16 == 0, DMNERF_EUNSUPPORTED,
+               "selftest_umma: n=%d k=%d (need multiples of 16, <= 256)", n, k);
+    const int smem = 65536 + 131072 + 64;
+    DM_CUDA(cudaFuncSetAttribute(tc::umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    tc::umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(a, b, n, k, d, g_tc_debug_flags);
+    DM_LAUNCH_CHECK("umma_selftest_kernel");
+    return DMNERF_OK;
+}

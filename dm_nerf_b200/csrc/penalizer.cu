@@ -129,8 +129,8 @@ penalizer_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 
 using namespace dmnerf;
 
-static int pen_check(const void* raw, const void* z, const void* depth, const void* rays_d, int s, int c) {
-    DM_REQUIRE(raw && z && depth && rays_d, DMNERF_EINVAL, "penalizer: null pointer");
+static int pen_check(const void* raw, const void* z, const void* depth, const void* rays_d, int s, int c, int64_t n) {
+    DM_REQUIRE(n == 0 || (raw && z && depth && rays_d), DMNERF_EINVAL, "penalizer: null pointer");
     DM_REQUIRE(s >= 1 && s <= 1024 && c >= 6 && c <= 128, DMNERF_EUNSUPPORTED,
                "penalizer: n_samples %d / channels %d unsupported", s, c);
     return DMNERF_OK;
@@ -139,7 +139,7 @@ static int pen_check(const void* raw, const void* z, const void* depth, const vo
 extern "C" int dmnerf_penalizer_fwd(const float* raw, const float* z, const float* depth, const float* rays_d,
                                     int64_t n, int s, int c, float tolerance, float deta_w, float* partials,
                                     float* loss, void* stream) {
-    if (int rc = pen_check(raw, z, depth, rays_d, s, c)) return rc;
+    if (int rc = pen_check(raw, z, depth, rays_d, s, c, n)) return rc;
     DM_REQUIRE(partials && loss, DMNERF_EINVAL, "penalizer_fwd: null output");
     cudaStream_t st = as_stream(stream);
     DM_CUDA(cudaMemsetAsync(partials, 0, 4 * sizeof(float), st));
@@ -159,7 +159,7 @@ extern "C" int dmnerf_penalizer_fwd(const float* raw, const float* z, const floa
 extern "C" int dmnerf_penalizer_bwd(const float* raw, const float* z, const float* depth, const float* rays_d,
                                     int64_t n, int s, int c, float tolerance, float deta_w, const float* partials,
                                     const float* d_loss, float* d_raw, void* stream) {
-    if (int rc = pen_check(raw, z, depth, rays_d, s, c)) return rc;
+    if (int rc = pen_check(raw, z, depth, rays_d, s, c, n)) return rc;
     DM_REQUIRE(partials && d_raw, DMNERF_EINVAL, "penalizer_bwd: null pointer");
     if (n <= 0) return DMNERF_OK;
     const size_t smem = static_cast<size_t>(kPenWarps) * 2 * s * sizeof(float);

@@ -177,6 +177,7 @@ using namespace dmnerf;
 
 static int launch_sample(const float* bins, const float* w_or_cdf, int cdf_given, const float* u, int64_t u_stride,
                          int64_t n, int nb, int ns, float* z_out, int64_t* inds_out, void* stream) {
+    if (n <= 0) return DMNERF_OK;
     DM_REQUIRE(bins && w_or_cdf && z_out, DMNERF_EINVAL, "sample_pdf: null pointer");
     DM_REQUIRE(nb >= 2 && nb <= 1024 && ns >= 2 && ns <= 4096, DMNERF_EUNSUPPORTED,
                "sample_pdf: n_bins %d / n_samples %d unsupported", nb, ns);
@@ -201,6 +202,7 @@ extern "C" int dmnerf_sample_cdf(const float* bins, const float* cdf, const floa
 
 extern "C" int dmnerf_fine_z(const float* z_coarse, const float* weights, const float* u, int64_t u_stride, int64_t n,
                              int sc, int n_imp, float* z_fine, float* z_samples, void* stream) {
+    if (n <= 0) return DMNERF_OK;
     DM_REQUIRE(z_coarse && weights && z_fine, DMNERF_EINVAL, "fine_z: null pointer");
     DM_REQUIRE(sc >= 4 && sc <= 512 && n_imp >= 2 && sc + n_imp <= 1024, DMNERF_EUNSUPPORTED,
                "fine_z: sc %d / n_importance %d unsupported", sc, n_imp);
@@ -217,6 +219,7 @@ extern "C" int dmnerf_fine_z(const float* z_coarse, const float* weights, const 
 
 extern "C" int dmnerf_sort_cat(const float* const* srcs, const int* lens, int parts, int64_t n, float* out,
                                void* stream) {
+    if (n <= 0) return DMNERF_OK;
     DM_REQUIRE(srcs && lens && out, DMNERF_EINVAL, "sort_cat: null pointer");
     DM_REQUIRE(parts >= 1 && parts <= 8, DMNERF_EUNSUPPORTED, "sort_cat: %d parts (max 8)", parts);
     CatParts cp;
@@ -238,6 +241,7 @@ extern "C" int dmnerf_sort_cat(const float* const* srcs, const int* lens, int pa
 }
 
 extern "C" int dmnerf_jitter_z(const float* z, const float* t_rand, int64_t n, int s, float* z_out, void* stream) {
+    if (n <= 0) return DMNERF_OK;
     DM_REQUIRE(z && t_rand && z_out, DMNERF_EINVAL, "jitter_z: null pointer");
     DM_REQUIRE(s >= 1, DMNERF_EINVAL, "jitter_z: bad sample count");
     const int64_t total = n * s;

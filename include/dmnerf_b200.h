@@ -140,6 +140,9 @@ int  dmnerf_label_argmax(const float* ins, int64_t n, int k, uint8_t* labels, vo
 /* ---- self test of the tcgen05 building blocks (used by tests/) ---------------------------------------
  * D[128,n] = A[128,k] * B[n,k]^T in bf16 with fp32 accumulate; a,b fp32 in, d fp32 out. */
 int  dmnerf_selftest_umma(const float* a, const float* b, int n, int k, float* d, void* stream);
+/* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the shared-memory descriptors).
+ * flags < 0 only queries.  Returns the previous value. */
+int  dmnerf_debug_flags(int flags);
 
 #ifdef __cplusplus
 }

@@ -39,3 +39,20 @@ def golden():
     def load(name):
         return dict(np.load(os.path.join(GOLDEN, name + ".npz")))
     return load
+
+
+@pytest.fixture(scope="session")
+def c_oracle():
+    """ctypes handle of oracle/libdmnerf_oracle.so (built on demand with gcc)."""
+    import ctypes as C
+    import subprocess
+    so = os.path.join(ROOT, "oracle", "libdmnerf_oracle.so")
+    if not os.path.exists(so):
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
+    lib = C.CDLL(so)
+    p, i64, i32 = C.c_void_p, C.c_int64, C.c_int
+    lib.oracle_sample_pdf.argtypes = [p, p, p, i64, i64, i32, i32, p, p]
+    lib.oracle_sample_pdf.restype = None
+    lib.oracle_composite.argtypes = [p, p, p, i64, i32, i32, i32, p, p, p, p]
+    lib.oracle_composite.restype = None
+    return lib

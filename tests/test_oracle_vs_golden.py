@@ -152,3 +152,26 @@ def test_train_grads(golden):
             got = v.grad.reshape(-1)[::97].numpy()
             scale = max(float(g[f"{tag}.{name}.norm"]) / np.sqrt(v.numel()), 1e-12)
             assert np.max(np.abs(got - ref)) <= 2e-3 * scale + 1e-9, (tag, name)
+
+
+def test_c_restatement_vs_golden(golden, c_oracle):
+    """The plain-C restatement (fixed sequential summation order) against the reference's vectors."""
+    g = golden("sample_pdf")
+    n = g["bins"].shape[0]
+    z, inds = np.empty((n, 128), np.float32), np.empty((n, 128), np.int64)
+    c_oracle.oracle_sample_pdf(g["bins"].ctypes.data, g["weights"].ctypes.data, g["u"].ctypes.data, 128, n, 63, 128,
+                               z.ctypes.data, inds.ctypes.data)
+    safe = np.abs(g["u"][:, :, None] - g["cdf"][:, None, :]).min(-1) > 2e-6
+    assert safe.mean() > 0.99 and np.array_equal(inds[safe], g["inds_rand"][safe])
+    assert (inds == g["inds_rand"]).mean() > 0.999
+    for tag in ("c64", "f192", "k93"):
+        g = golden(f"composite_{tag}")
+        n, s, c = g["raw"].shape
+        rgb, dep = np.empty((n, 3), np.float32), np.empty((n,), np.float32)
+        w, ins = np.empty((n, s), np.float32), np.empty((n, c - 5), np.float32)
+        c_oracle.oracle_composite(g["raw"].ctypes.data, g["z"].ctypes.data, g["rays_d"].ctypes.data, n, s, c, 1,
+                                  rgb.ctypes.data, dep.ctypes.data, w.ctypes.data, ins.ctypes.data)
+        np.testing.assert_allclose(rgb, g["rgb"], atol=2e-6)
+        np.testing.assert_allclose(dep, g["depth"], atol=2e-5)
+        np.testing.assert_allclose(w, g["weights"], atol=1e-6)
+        np.testing.assert_allclose(ins, g["ins"], atol=2e-6)
