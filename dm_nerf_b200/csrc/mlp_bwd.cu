@@ -158,3 +158,174 @@ __device__ __forceinline__ void wgrad_block(const float* __restrict__ dy, const 
 struct GradPtrs { float* g[kNumParams]; };
 
 }  // namespace dmnerf
+
+namespace dmnerf {
+
+// Shared memory (floats): G[256][64] | G2[256][64] | XS[2][64][68] | WST[2][16][256] | DO[C][64]
+__host__ __device__ inline int bwd_smem_floats(int C) { return 2 * 256 * kTileM + 2 * kSlabFloats + 2 * kChunkKb * 256 + C * kTileM; }
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+mlp_bwd_fp32_kernel(const float* __restrict__ packed, Fp32Image im, const float* __restrict__ acts,
+                    const float* __restrict__ d_raw, int64_t n_points, GradPtrs gp) {
+    extern __shared__ __align__(16) float sm[];
+    float* G = sm;
+    float* G2 = G + 256 * kTileM;
+    float* XS = G2 + 256 * kTileM;
+    float* WST = XS + 2 * kSlabFloats;
+    float* DO = WST + 2 * kChunkKb * 256;
+    const int t = threadIdx.x;
+    const int C = im.ins_num + 5, L = im.ins_num + 1;
+
+    for (int64_t tile = blockIdx.x; tile * kTileM < n_points; tile += gridDim.x) {
+        const int64_t p0 = tile * kTileM;
+        const float* A = acts + tile * static_cast<int64_t>(kActRows) * kTileM;
+        // ---- d(raw) tile, transposed to [C][64]; rows past the end contribute nothing --------------------
+        {
+            const int64_t limit = (n_points - p0) * C;
+            const float* src = d_raw + p0 * C;
+            for (int i = t; i < kTileM * C; i += kBwdThreads) {
+                const int pt = i / C, c = i - pt * C;
+                DO[c * kTileM + pt] = (i < limit) ? __ldg(src + i) : 0.f;
+            }
+        }
+        __syncthreads();
+
+        // ======== instance branch (its gradient stops at ins_feature_linear: h.detach()) ========
+        // ins_linear: dW[c][k] += sum_p DO[4+c][p]*insH[k][p];  dY9[k][p] = sum_c DO[4+c][p]*W[c][k] * [insH>0]
+        {
+            const float* insH = A + kActInsH * kTileM;
+            for (int i = t; i < 128 * kTileM / 4; i += kBwdThreads)      // stage insH in XS (dense [128][64])
+                reinterpret_cast<float4*>(XS)[i] = __ldg(reinterpret_cast<const float4*>(insH) + i);
+            __syncthreads();
+            for (int o = t; o < L * 128; o += kBwdThreads) {
+                const int c = o >> 7, k = o & 127;
+                float a = 0.f;
+                for (int i = 0; i < kTileM; ++i) { const int pp = (i + t) & 63; a = fmaf(DO[(4 + c) * kTileM + pp], XS[k * kTileM + pp], a); }
+                atomicAdd(gp.g[P_INSL_W] + o, a);
+            }
+            if (t < L) {
+                float a = 0.f;
+                for (int i = 0; i < kTileM; ++i) a += DO[(4 + t) * kTileM + i];
+                atomicAdd(gp.g[P_INSL_B] + t, a);
+            }
+            const float* w_ins = packed + im.w_ins;
+            for (int o = t; o < 128 * kTileM; o += kBwdThreads) {
+                const int k = o >> 6, pt = o & 63;
+                float a = 0.f;
+                for (int c = 0; c < L; ++c) a = fmaf(DO[(4 + c) * kTileM + pt], __ldg(w_ins + c * 128 + k), a);
+                G2[o] = XS[o] > 0.f ? a : 0.f;
+            }
+            __syncthreads();
+        }
+        // layer 9 (ins_feature_linears.0): X = insF
+        wgrad_block<16>(G2, A + kActInsF * kTileM, 256, gp.g[P_INS0_W], 256, 0, 256, XS);
+        bias_grad(G2, 128, gp.g[P_INS0_B]);
+        dgrad_layer(G2, 128, packed + im.wg[9], G, WST);                 // G = d(insF), no activation
+        // layer 8 (ins_feature_linear): X = h7; no input gradient (detach)
+        wgrad_block<32>(G, A + (kActH0 + 7 * 256) * kTileM, 256, gp.g[P_INSF_W], 256, 0, 256, XS);
+        bias_grad(G, 256, gp.g[P_INSF_B]);
+        __syncthreads();
+
+        // ======== colour branch ========
+        {
+            const float* rgbH = A + kActRgbH * kTileM;
+            for (int i = t; i < 128 * kTileM / 4; i += kBwdThreads)
+                reinterpret_cast<float4*>(XS)[i] = __ldg(reinterpret_cast<const float4*>(rgbH) + i);
+            __syncthreads();
+            for (int o = t; o < 3 * 128; o += kBwdThreads) {
+                const int c = o >> 7, k = o & 127;
+                float a = 0.f;
+                for (int i = 0; i < kTileM; ++i) { const int pp = (i + t) & 63; a = fmaf(DO[c * kTileM + pp], XS[k * kTileM + pp], a); }
+                atomicAdd(gp.g[P_RGBL_W] + o, a);
+            }
+            if (t < 3) {
+                float a = 0.f;
+                for (int i = 0; i < kTileM; ++i) a += DO[t * kTileM + i];
+                atomicAdd(gp.g[P_RGBL_B] + t, a);
+            }
+            const float* w_rgb = packed + im.w_rgb;
+            for (int o = t; o < 128 * kTileM; o += kBwdThreads) {
+                const int k = o >> 6, pt = o & 63;
+                float a = 0.f;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) a = fmaf(DO[c * kTileM + pt], __ldg(w_rgb + c * 128 + k), a);
+                G2[o] = XS[o] > 0.f ? a : 0.f;
+            }
+            __syncthreads();
+        }
+        // layer 11 (rgb_feature_linears.0): X = [rgbF | dir], torch weight is [128][283]
+        wgrad_block<16>(G2, A + kActRgbF * kTileM, 256, gp.g[P_RGB0_W], 283, 0, 256, XS);
+        wgrad_block<16>(G2, A + kActDir * kTileM, 32, gp.g[P_RGB0_W], 283, 256, 27, XS);
+        bias_grad(G2, 128, gp.g[P_RGB0_B]);
+        dgrad_layer(G2, 128, packed + im.wg[11], G, WST);                // G = d(rgbF)
+        // layer 10 (rgb_feature_linear): X = h7
+        wgrad_block<32>(G, A + (kActH0 + 7 * 256) * kTileM, 256, gp.g[P_RGBF_W], 256, 0, 256, XS);
+        bias_grad(G, 256, gp.g[P_RGBF_B]);
+        dgrad_layer(G, 256, packed + im.wg[10], G2, WST);                // G2 = d(h7) from the colour branch
+        // density head: d(h7)[k][p] += DO[3][p]*w_d[k];  dW_d[k] += sum_p DO[3][p]*h7[k][p]
+        {
+            const float* h7 = A + (kActH0 + 7 * 256) * kTileM;
+            const float* wd = packed + im.w_dens;
+            for (int o = t; o < 256 * kTileM; o += kBwdThreads) {
+                const int k = o >> 6, pt = o & 63;
+                G2[o] = fmaf(DO[3 * kTileM + pt], __ldg(wd + k), G2[o]);
+            }
+            {
+                float a = 0.f;                                           // thread t <-> row k = t
+                for (int i = 0; i < kTileM; ++i) a = fmaf(DO[3 * kTileM + i], __ldg(h7 + t * kTileM + i), a);
+                atomicAdd(gp.g[P_DENS_W] + t, a);
+            }
+            if (t == 0) {
+                float a = 0.f;
+                for (int i = 0; i < kTileM; ++i) a += DO[3 * kTileM + i];
+                atomicAdd(gp.g[P_DENS_B], a);
+            }
+            __syncthreads();
+            relu_mask_256(G2, h7);                                       // dY7
+        }
+
+        // ======== trunk, layers 7..0 ========
+        float* dy = G2;
+        float* dx = G;
+        for (int l = 7; l >= 0; --l) {
+            float* dWl = gp.g[2 * l];
+            if (l == 0) {
+                wgrad_block<32>(dy, A + kActPos * kTileM, 64, dWl, 63, 0, 63, XS);
+            } else if (l == 5) {
+                wgrad_block<32>(dy, A + (kActH0 + 4 * 256) * kTileM, 256, dWl, 319, 0, 256, XS);
+                wgrad_block<32>(dy, A + kActPos * kTileM, 64, dWl, 319, 256, 63, XS);
+            } else {
+                wgrad_block<32>(dy, A + (kActH0 + (l - 1) * 256) * kTileM, 256, dWl, 256, 0, 256, XS);
+            }
+            bias_grad(dy, 256, gp.g[2 * l + 1]);
+            if (l > 0) {
+                dgrad_layer(dy, 256, packed + im.wg[l], dx, WST);
+                relu_mask_256(dx, A + (kActH0 + (l - 1) * 256) * kTileM);
+                float* tmp = dy; dy = dx; dx = tmp;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+int launch_mlp_bwd_fp32(const float* packed, const float* acts, const float* d_raw, int64_t n_points, int ins_num,
+                        float* const* grads, cudaStream_t st) {
+    static int sm_count = 0;
+    if (sm_count == 0) {
+        int dev = 0;
+        DM_CUDA(cudaGetDevice(&dev));
+        DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    GradPtrs gp;
+    for (int i = 0; i < kNumParams; ++i) gp.g[i] = grads[i];
+    const size_t smem = static_cast<size_t>(bwd_smem_floats(ins_num + 5)) * sizeof(float);
+    DM_REQUIRE(smem <= 232448, DMNERF_EUNSUPPORTED, "mlp_bwd: %zu bytes of shared memory needed", smem);
+    DM_CUDA(cudaFuncSetAttribute(mlp_bwd_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t tiles = (n_points + kTileM - 1) / kTileM;
+    const unsigned grid = static_cast<unsigned>(tiles < sm_count ? tiles : sm_count);
+    mlp_bwd_fp32_kernel<<<grid, kBwdThreads, smem, st>>>(packed, fp32_image(ins_num), acts, d_raw, n_points, gp);
+    DM_LAUNCH_CHECK("mlp_bwd_fp32_kernel");
+    return DMNERF_OK;
+}
+
+}  // namespace dmnerf

@@ -45,14 +45,17 @@ constexpr int kBiasFloats = 2704;                 // 9*256 | T9 bias (128) | w_d
 constexpr int kBiasT9 = 9 * 256;
 constexpr int kBiasWd = kBiasT9 + 128;
 constexpr int kBiasBd = kBiasWd + 256;
-constexpr int kThreads = 320;
+constexpr int kEpiWarps = 16;                     // 8 per tile: 4 lane quarters x 2 column halves
+constexpr int kProducerWarp = 16, kMmaWarp = 17;
+constexpr int kThreads = 18 * 32;
 
 // shared memory map (bytes)
 constexpr int kSmA = 0;
 constexpr int kSmRing = 2 * kABytes;                           // 163,840
 constexpr int kSmBias = kSmRing + kStages * kStageBytes;       // 212,992
 constexpr int kSmBar = kSmBias + kBiasFloats * 4;              // 223,808
-constexpr int kSmTotal = kSmBar + 128;                         // barriers + tmem slot
+constexpr int kSmDens = kSmBar + 128;                          // density partials of column-half 1: [2][128] floats
+constexpr int kSmTotal = kSmDens + 2 * kTile * 4;
 
 __host__ __device__ inline int layer_k(int l) { return l == 0 ? 64 : (l == 5 ? 320 : (l == 8 ? 288 : 256)); }
 __host__ __device__ inline int layer_akg0(int l) { return l == 0 ? kExtKg : 0; }
@@ -184,35 +187,42 @@ __device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const
                       ptx::pack_bf16(v[4], v[5], relu), ptx::pack_bf16(v[6], v[7], relu));
 }
 
-// Embedding of a 3-vector with F octaves into EXT k-groups: channel c = [x | f: sin(3) cos(3)].  The first
-// octave uses full-range sincosf; higher octaves follow by angle doubling (error << bf16 resolution).
-template <int F>
+// Embedding of a 3-vector into EXT k-groups [KG0, KG1): channel c = [x | f: sin(3) cos(3)], 8 channels per
+// k-group.  The first needed octave uses full-range sincosf on x*2^f (exact scaling); higher octaves follow by
+// angle doubling (error << bf16 resolution).  Channels outside the range are dead code after unrolling.
+template <int F, int KG0, int KG1>
 __device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3]) {
     constexpr int CH = 3 + 6 * F;
-    constexpr int KG = (CH + 7) / 8;
-    float ch[KG * 8];
+    constexpr int C0 = KG0 * 8, C1 = KG1 * 8;
+    constexpr int F0 = C0 < 3 ? 0 : (C0 - 3) / 6;           // first octave that touches [C0, C1)
+    float ch[(KG1 - KG0) * 8];
 #pragma unroll
-    for (int i = 0; i < KG * 8; ++i) ch[i] = 0.f;
+    for (int i = 0; i < (KG1 - KG0) * 8; ++i) ch[i] = 0.f;
     float s[3], c[3];
 #pragma unroll
-    for (int d = 0; d < 3; ++d) { ch[d] = x[d]; sincosf(x[d], &s[d], &c[d]); }
+    for (int d = 0; d < 3; ++d) {
+        if (C0 == 0) ch[d] = x[d];
+        sincosf(x[d] * static_cast<float>(1 << F0), &s[d], &c[d]);
+    }
 #pragma unroll
-    for (int f = 0; f < F; ++f) {
+    for (int f = F0; f < F; ++f) {
 #pragma unroll
         for (int d = 0; d < 3; ++d) {
-            ch[3 + 6 * f + d] = s[d];
-            ch[3 + 6 * f + 3 + d] = c[d];
+            const int cs = 3 + 6 * f + d, cc = cs + 3;
+            if (cs >= C0 && cs < C1 && cs < CH) ch[cs - C0] = s[d];
+            if (cc >= C0 && cc < C1 && cc < CH) ch[cc - C0] = c[d];
             const float s2 = 2.f * s[d] * c[d];
             const float c2 = (c[d] - s[d]) * (c[d] + s[d]);
             s[d] = s2; c[d] = c2;
         }
     }
 #pragma unroll
-    for (int g = 0; g < KG; ++g) store_kg(a_base, kExtKg + g, row, &ch[g * 8], false);
+    for (int g = KG0; g < KG1; ++g) store_kg(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false);
 }
 
-__device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kgs) {
-    for (int g = 0; g < kgs; ++g) {
+__device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kg0,
+                                           int kg1) {
+    for (int g = kg0; g < kg1; ++g) {
         float v[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] = (src && g * 8 + e < count) ? __ldg(src + g * 8 + e) : 0.f;
@@ -234,10 +244,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
-        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
+        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 2 * kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
         ptx::fence_barrier_init();
     }
-    if (warp == 9) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
+    if (warp == kMmaWarp) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
     {
         const float* gb = reinterpret_cast<const float*>(image + im.bias_off);
         for (int i = threadIdx.x; i < kBiasFloats; i += kThreads) s_bias[i] = gb[i];
@@ -249,7 +259,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 
     const int64_t n_pairs = (in.n_points + kPair - 1) / kPair;
 
-    if (warp == 8) {
+    if (warp == kProducerWarp) {
         // ===== weight producer: walks the chunk stream of every layer for every tile pair =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
@@ -273,7 +283,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == kMmaWarp) {
         // ===== MMA issuer =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0, a_par[2] = {0, 0};
@@ -310,11 +320,12 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             }
         }
     } else {
-        // ===== epilogue / embedding: thread == one point of tile t == one TMEM lane =====
-        const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
+        // ===== epilogue / embedding: 8 warps per tile; thread == (point == TMEM lane, column half) =====
+        const int t = warp >> 3, q = warp & 3, half = (warp >> 2) & 1, row = q * 32 + lane;
         const uint32_t a_base = sm0 + kSmA + t * kABytes;
         const uint32_t t_base = tmem + t * 256 + (static_cast<uint32_t>(q * 32) << 16);
         float* stage_out = reinterpret_cast<float*>(smem + kSmA + t * kABytes);
+        float* dens_part = reinterpret_cast<float*>(smem + kSmDens) + t * kTile;
         uint32_t acc_par = 0;
         for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
             const int64_t tile0 = pair * kPair + t * kTile;
@@ -336,9 +347,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 #pragma unroll
                     for (int c = 0; c < 3; ++c) dir[c] = d[c] * inv;
                 }
-                embed_to_ext<kPosFreqs>(a_base, row, pos);
+                if (half == 0) embed_to_ext<kPosFreqs, 0, 4>(a_base, row, pos);
+                else           embed_to_ext<kPosFreqs, 4, 8>(a_base, row, pos);
             } else {
-                row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, 8);
+                row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, half * 4, half * 4 + 4);
             }
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
@@ -351,7 +363,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 ptx::tc_fence_after();
                 const float* bias = s_bias + l * 256;
 #pragma unroll 1
-                for (int cb = 0; cb < 8; ++cb) {
+                for (int cb = half * 4; cb < half * 4 + 4; ++cb) {
                     uint32_t r[32];
                     ptx::tmem_ld32(t_base + cb * 32, r);
                     ptx::tmem_ld_wait();
@@ -359,7 +371,11 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                     for (int g = 0; g < 4; ++g) {
                         float v[8];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]) + bias[cb * 32 + g * 8 + e];
+                        for (int e = 0; e < 8; e += 2) {
+                            const float2 b2 = *reinterpret_cast<const float2*>(bias + cb * 32 + g * 8 + e);
+                            const float2 s2 = __fadd2_rn(make_float2(__uint_as_float(r[g * 8 + e]), __uint_as_float(r[g * 8 + e + 1])), b2);
+                            v[e] = s2.x; v[e + 1] = s2.y;
+                        }
                         if (l == 7) {
 #pragma unroll
                             for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_bias[kBiasWd + cb * 32 + g * 8 + e], dens);
@@ -369,53 +385,60 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 }
                 if (l == 7) {
                     // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it)
-                    if (in.x == nullptr) embed_to_ext<kDirFreqs>(a_base, row, dir);
-                    else row_to_ext(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 4);
+                    if (half == 0) {
+                        if (in.x == nullptr) embed_to_ext<kDirFreqs, 0, 4>(a_base, row, dir);
+                        else row_to_ext(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 0, 4);
+                    } else {
+                        dens_part[row] = dens;
+                    }
                 }
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(bars.a_ready(t));
             }
-            // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored ----
+            // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (half 0) ----
             ptx::mbar_wait(bars.acc_ready(t), acc_par);
             acc_par ^= 1;
             ptx::tc_fence_after();
-            for (int cb = 0; cb * 16 < im.npad; ++cb) {
-                uint32_t r[16];
-                ptx::tmem_ld16(t_base + cb * 16, r);
-                ptx::tmem_ld_wait();
+            if (half == 0) {
+                dens += dens_part[row];
+                for (int cb = 0; cb * 16 < im.npad; ++cb) {
+                    uint32_t r[16];
+                    ptx::tmem_ld16(t_base + cb * 16, r);
+                    ptx::tmem_ld_wait();
 #pragma unroll
-                for (int e = 0; e < 16; ++e) {
-                    const int col = cb * 16 + e;
-                    if (col < C) {
-                        float v = __uint_as_float(r[e]) + s_bias[kBiasT9 + col];
-                        if (col == 3) v = dens + s_bias[kBiasBd];
-                        stage_out[row * C + col] = v;
+                    for (int e = 0; e < 16; ++e) {
+                        const int col = cb * 16 + e;
+                        if (col < C) {
+                            float v = __uint_as_float(r[e]) + s_bias[kBiasT9 + col];
+                            if (col == 3) v = dens + s_bias[kBiasBd];
+                            stage_out[row * C + col] = v;
+                        }
                     }
                 }
-            }
-            ptx::tc_fence_before();
-            ptx::fence_proxy_async_smem();
-            ptx::named_bar_sync(1 + t, kTile);
-            const int64_t rows_left = in.n_points - tile0;
-            if (rows_left >= kTile) {
-                if (row == 0) {
-                    ptx::bulk_s2g(raw_out + tile0 * C, ptx::smem_u32(stage_out), kTile * C * 4);
-                    ptx::bulk_commit();
-                    ptx::bulk_wait_read0();
+                ptx::tc_fence_before();
+                ptx::fence_proxy_async_smem();
+                ptx::named_bar_sync(1 + t, kTile);
+                const int64_t rows_left = in.n_points - tile0;
+                if (rows_left >= kTile) {
+                    if (row == 0) {
+                        ptx::bulk_s2g(raw_out + tile0 * C, ptx::smem_u32(stage_out), kTile * C * 4);
+                        ptx::bulk_commit();
+                        ptx::bulk_wait_read0();
+                    }
+                } else if (rows_left > 0) {
+                    const int total = static_cast<int>(rows_left) * C;
+                    for (int i = row; i < total; i += kTile) raw_out[tile0 * C + i] = stage_out[i];
                 }
-            } else if (rows_left > 0) {
-                const int total = static_cast<int>(rows_left) * C;
-                for (int i = row; i < total; i += kTile) raw_out[tile0 * C + i] = stage_out[i];
+                // the next write into this region is T0's epilogue of the next pair, which cannot start before all
+                // 256 threads (incl. the bulk-store issuer, after its read-wait) arrived on a_ready again.
+                ptx::named_bar_sync(1 + t, kTile);
             }
-            // the next write into this region is T0's epilogue of the next pair, which cannot start before
-            // all 128 threads (incl. the bulk-store issuer, after its read-wait) arrived on a_ready again.
-            ptx::named_bar_sync(1 + t, kTile);
         }
     }
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 9) {
+    if (warp == kMmaWarp) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc(tmem, 512);
     }
