@@ -3,8 +3,12 @@
 // stratified jitter (networks/render.py:40-47).  One warp per ray, everything in shared memory.
 //
 // CDF summation order (fixed and documented; oracle/dmnerf_oracle_c.c uses the same one, so indices are
-// bit-exact against it): w_j = weights_j + 1e-5; total = ((w_0 + w_1) + w_2) + ... sequential fp32;
-// pdf_j = w_j / total (IEEE division); cdf_0 = 0, cdf_{j+1} = cdf_j + pdf_j sequential fp32.
+// bit-exact against it): w_j = weights_j + 1e-5 (fp32); total = fp32(sum_j double(w_j)), sequential;
+// pdf_j = w_j / total (fp32 IEEE division); cdf_0 = 0, cdf_{j+1} = fp32(sum_{i<=j} double(pdf_i)), one
+// running double accumulator.  The running-double prefix sum IS what ATen's CPU cumsum does for float
+// (acc_type<float,false> = double), and fp32(double sum) equals ATen's cascade `sum` except where that one
+// is not correctly rounded -- so against the torch-CPU golden vectors most rays are bit-identical and the
+// rest differ by <= 1 ulp of the cdf (a sequential fp32 order is off by several ulp).
 // searchsorted(right=True): inds = #{j : cdf_j <= u}.  The lerp uses un-fused mul/add like ATen.
 #include "common.cuh"
 #include <math_constants.h>
@@ -22,15 +26,16 @@ __device__ __forceinline__ float linspace01(int i, int n) {
 
 // Builds cdf[0..nb-1] in shared memory from wv[0..nb-2] (= weights + 1e-5 already stored).
 __device__ __forceinline__ void build_cdf(float* cdf, float* wv, int nb, int lane) {
-    float total = 0.f;
-    for (int j = 0; j < nb - 1; ++j) total = __fadd_rn(total, wv[j]);   // every lane, same order
+    double tot = 0.0;
+    for (int j = 0; j < nb - 1; ++j) tot += static_cast<double>(wv[j]);   // every lane, same order
+    const float total = static_cast<float>(tot);
     __syncwarp();
     for (int j = lane; j < nb - 1; j += 32) wv[j] = __fdiv_rn(wv[j], total);
     __syncwarp();
     if (lane == 0) {
-        float c = 0.f;
+        double c = 0.0;
         cdf[0] = 0.f;
-        for (int j = 0; j < nb - 1; ++j) { c = __fadd_rn(c, wv[j]); cdf[j + 1] = c; }
+        for (int j = 0; j < nb - 1; ++j) { c += static_cast<double>(wv[j]); cdf[j + 1] = static_cast<float>(c); }
     }
     __syncwarp();
 }

@@ -2,9 +2,11 @@
  *
  * torch's CPU sum/cumsum association is implementation-defined (cumsum accumulates in double,
  * sum is a vectorised cascade), so "the reference's CDF bits" differ between torch builds and
- * between CPU and CUDA.  The CUDA sampler therefore fixes one documented order (sequential fp32)
- * and THIS file restates the reference algorithm (networks/helpers.py:123-155) in that order, so
- * the kernel's indices can be checked bit-for-bit.  Compiled with -ffp-contract=off (no FMA).
+ * between CPU and CUDA.  The CUDA sampler therefore fixes one documented order -- running DOUBLE
+ * accumulators rounded to fp32 per element, i.e. what ATen's CPU cumsum does and the correctly
+ * rounded value its cascade sum approximates -- and THIS file restates the reference algorithm
+ * (networks/helpers.py:123-155) in that order, so the kernel's indices can be checked bit-for-bit.
+ * Compiled with -ffp-contract=off (no FMA).
  * Only tests/ and bench.py's cpu_baseline leg may load it. */
 #include <math.h>
 #include <stdint.h>
@@ -15,11 +17,16 @@ void oracle_sample_pdf(const float* bins, const float* weights, const float* u, 
     float cdf[1024], w[1024];
     for (int64_t r = 0; r < n; ++r) {
         const float* b = bins + r * nb;
-        float total = 0.f;
-        for (int j = 0; j < nb - 1; ++j) { w[j] = weights[r * (nb - 1) + j] + 1e-5f; total = total + w[j]; }  /* :125 */
-        float c = 0.f;
+        double tot = 0.0;
+        for (int j = 0; j < nb - 1; ++j) { w[j] = weights[r * (nb - 1) + j] + 1e-5f; tot += (double)w[j]; }   /* :125 */
+        const float total = (float)tot;
+        double c = 0.0;
         cdf[0] = 0.f;                                                                                     /* :128 */
-        for (int j = 0; j < nb - 1; ++j) { c = c + w[j] / total; cdf[j + 1] = c; }                          /* :126-127 */
+        for (int j = 0; j < nb - 1; ++j) {                                                                /* :126-127 */
+            const float pdf = w[j] / total;
+            c += (double)pdf;
+            cdf[j + 1] = (float)c;
+        }
         for (int i = 0; i < ns; ++i) {
             const float uu = u[r * u_stride + i];
             int lo = 0, hi = nb;                                     /* searchsorted(right=True), :139 */

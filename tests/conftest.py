@@ -47,8 +47,7 @@ def c_oracle():
     import ctypes as C
     import subprocess
     so = os.path.join(ROOT, "oracle", "libdmnerf_oracle.so")
-    if not os.path.exists(so):
-        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)   # no-op when up to date
     lib = C.CDLL(so)
     p, i64, i32 = C.c_void_p, C.c_int64, C.c_int
     lib.oracle_sample_pdf.argtypes = [p, p, p, i64, i64, i32, i32, p, p]
