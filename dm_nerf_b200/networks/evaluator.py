@@ -1,0 +1,57 @@
+"""Training losses with the reference's names (networks/evaluator.py:8-74): ``img2mse``, ``mse2psnr`` and the
+Hungarian-matched instance loss ``ins_criterion``.  SURVEY 2 row 10 keeps these in stock torch + scipy: they
+consume the ray path's ``rgb_*`` / ``ins_*`` outputs, are O(N_rays * ins_num^2), and sit outside the hot path.
+The cost matrices are built on the device; only the [valid, ins_num] matrix crosses to the host for
+``scipy.optimize.linear_sum_assignment`` (evaluator.py:45-46), one small D2H copy per call."""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+def img2mse(x, y):
+    return torch.mean((x - y) ** 2)
+
+
+def mse2psnr(x):
+    return -10. * torch.log(x) / math.log(10.)
+
+
+def hungarian(pred_ins, gt_ins, valid_ins_num, ins_num):
+    """evaluator.py:41-74.  pred_ins [N,K] probabilities, gt_ins [N,K] one-hot (first ``valid_ins_num`` columns
+    used).  Returns (cost_ce [K,K], cost_siou [K,K], row order, column order incl. unmatched columns)."""
+    from scipy.optimize import linear_sum_assignment
+    p = pred_ins.t()[None, :, :]                        # [1, K_pred, N]
+    g = gt_ins.t()[:, None, :]                          # [K_gt, 1, N]
+    cost_ce = torch.mean(-g * torch.log(p + 1e-8) - (1 - g) * torch.log(1 - p + 1e-8), dim=-1)
+    tp = torch.sum(p * g, dim=-1)
+    fp = torch.sum(p, dim=-1) - tp
+    fn = torch.sum(g, dim=-1) - tp
+    cost_siou = 1.0 - tp / (tp + fp + fn + 1e-6)
+    with torch.no_grad():
+        scores = (cost_ce + cost_siou)[:valid_ins_num].detach().cpu().numpy()
+        row, col = linear_sum_assignment(scores)
+        if ins_num - valid_ins_num > 0:
+            rest = np.array(sorted(set(range(ins_num)) - set(col.tolist())), dtype=col.dtype)
+            col = np.concatenate([col, rest])
+    return cost_ce, cost_siou, row, col
+
+
+def ins_criterion(pred_ins, gt_labels, ins_num):
+    """evaluator.py:19-37: one-hot the labels present in the batch, match predicted channels to them, then
+    CE on matched pairs + mean activation of unmatched channels + soft-IoU on matched pairs."""
+    valid = torch.unique(gt_labels)
+    n_valid = len(valid)
+    gt_ins = torch.zeros((gt_labels.shape[0], ins_num), device=pred_ins.device, dtype=pred_ins.dtype)
+    gt_ins[..., :n_valid] = F.one_hot(gt_labels.long())[..., valid.long()].to(pred_ins.dtype)
+    cost_ce, cost_siou, row, col = hungarian(pred_ins, gt_ins, n_valid, ins_num)
+    valid_ce = torch.mean(cost_ce[row, col[:n_valid]])
+    if len(col) != n_valid:
+        invalid_ce = torch.mean(pred_ins[:, col[n_valid:]])
+    else:
+        invalid_ce = torch.zeros((), device=pred_ins.device)
+    valid_siou = torch.mean(cost_siou[row, col[:n_valid]])
+    return valid_ce + invalid_ce + valid_siou, valid_ce, invalid_ce, valid_siou
