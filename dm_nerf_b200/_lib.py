@@ -63,9 +63,9 @@ _SIGNATURES = {
     "dmnerf_weights_pack": (_int, [C.POINTER(_p), _int, _int, _p, _p]),
     "dmnerf_mlp_fwd": (_int, [_p, _p, _p, _i64, _int, _p, _int, _int, _p, _p, _p]),
     "dmnerf_mlp_fwd_embedded": (_int, [_p, _i64, _p, _int, _int, _p, _p, _p]),
-    "dmnerf_acts_bytes": (_i64, [_i64, _int]),
-    "dmnerf_mlp_bwd": (_int, [_p, _p, _p, _i64, _int, C.POINTER(_p), _p, _p]),
-    "dmnerf_bwd_workspace_bytes": (_i64, [_i64, _int]),
+    "dmnerf_acts_bytes": (_i64, [_i64, _int, _int]),
+    "dmnerf_mlp_bwd": (_int, [_p, _p, _p, _i64, _int, _int, C.POINTER(_p), _p, _p]),
+    "dmnerf_bwd_workspace_bytes": (_i64, [_i64, _int, _int]),
     "dmnerf_composite_fwd": (_int, [_p, _p, _p, _i64, _int, _int, _int, _p, _p, _p, _p, _p]),
     "dmnerf_composite_bwd": (_int, [_p, _p, _p, _i64, _int, _int, _int, _int, _p, _p, _p, _p, _p, _p]),
     "dmnerf_sample_pdf": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
@@ -80,6 +80,7 @@ _SIGNATURES = {
     "dmnerf_embed": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_label_argmax": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_selftest_umma": (_int, [_p, _p, _int, _int, _p, _p]),
+    "dmnerf_selftest_umma_mn": (_int, [_p, _p, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
 }
 

@@ -29,7 +29,14 @@ int launch_mlp_bwd_fp32(const float* packed, const float* acts, const float* d_r
 // mlp_tc.cu
 int64_t bf16_image_bytes(int ins_num);
 int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st);
-int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, cudaStream_t st);
+int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int tc_debug_flags();
+// mlp_tc_bwd.cu
+int64_t bf16_acts_bytes(int64_t n_points);
+int64_t bf16_bwd_workspace_bytes(int64_t n_points);
+int launch_mlp_bwd_bf16(const void* packed, const void* acts, const float* d_raw, int64_t n_points, int ins_num,
+                        float* const* grads, void* workspace, int debug_flags, cudaStream_t st);
+int launch_selftest_umma_mn(const float* a, const float* b, int n, float* d, int debug_flags, cudaStream_t st);
 
 }  // namespace dmnerf
 
@@ -70,8 +77,11 @@ extern "C" int dmnerf_weights_pack(const float* const* params, int ins_num, int 
     DM_REQUIRE(false, DMNERF_EUNSUPPORTED, "weights_pack: unknown mode %d", mode);
 }
 
-extern "C" int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num) {
+extern "C" int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num, int mode) {
     (void)ins_num;
+    if (n_points < 0) return -1;
+    if (mode == DMNERF_MODE_BF16) return bf16_acts_bytes(n_points);
+    if (mode != DMNERF_MODE_FP32) return -1;
     const int64_t tiles = (n_points + kTileM - 1) / kTileM;
     return tiles * kActRows * kTileM * 4;
 }
@@ -85,9 +95,7 @@ static int run_mlp(const MlpInput& in, const void* packed, int ins_num, int mode
         return launch_mlp_fp32(in, static_cast<const float*>(packed), ins_num, raw_out, static_cast<float*>(acts),
                                as_stream(stream));
     if (mode == DMNERF_MODE_BF16) {
-        DM_REQUIRE(acts == nullptr, DMNERF_EUNSUPPORTED,
-                   "mlp_fwd: the activation stash (training) is only produced in DMNERF_MODE_FP32");
-        return launch_mlp_bf16(in, packed, ins_num, raw_out, as_stream(stream));
+        return launch_mlp_bf16(in, packed, ins_num, raw_out, acts, as_stream(stream));
     }
     DM_REQUIRE(false, DMNERF_EUNSUPPORTED, "mlp_fwd: unknown mode %d", mode);
 }
@@ -110,18 +118,29 @@ extern "C" int dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* pa
     return run_mlp(in, packed, ins_num, mode, raw_out, acts, stream);
 }
 
-extern "C" int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num) {
-    (void)n_points; (void)ins_num;
-    return 0;
+extern "C" int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num, int mode) {
+    (void)ins_num;
+    if (n_points < 0) return -1;
+    if (mode == DMNERF_MODE_BF16) return bf16_bwd_workspace_bytes(n_points);
+    return mode == DMNERF_MODE_FP32 ? 0 : -1;
 }
 
 extern "C" int dmnerf_mlp_bwd(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
-                              int ins_num, float* const* grads, void* workspace, void* stream) {
-    (void)workspace;
+                              int ins_num, int mode, float* const* grads, void* workspace, void* stream) {
     DM_REQUIRE(packed && acts && d_raw && grads, DMNERF_EINVAL, "mlp_bwd: null pointer");
     if (int rc = check_ins(ins_num, "mlp_bwd")) return rc;
     for (int i = 0; i < kNumParams; ++i) DM_REQUIRE(grads[i], DMNERF_EINVAL, "mlp_bwd: grads[%d] is null", i);
     if (n_points <= 0) return DMNERF_OK;
+    if (mode == DMNERF_MODE_BF16)
+        return launch_mlp_bwd_bf16(packed, acts, d_raw, n_points, ins_num, grads, workspace, tc_debug_flags(),
+                                   as_stream(stream));
+    DM_REQUIRE(mode == DMNERF_MODE_FP32, DMNERF_EUNSUPPORTED, "mlp_bwd: unknown mode %d", mode);
     return launch_mlp_bwd_fp32(static_cast<const float*>(packed), static_cast<const float*>(acts), d_raw, n_points,
                                ins_num, grads, as_stream(stream));
+}
+
+extern "C" int dmnerf_selftest_umma_mn(const float* a, const float* b, int n, float* d, void* stream) {
+    DM_REQUIRE(a && b && d, DMNERF_EINVAL, "selftest_umma_mn: null pointer");
+    DM_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0, DMNERF_EUNSUPPORTED, "selftest_umma_mn: n=%d (need a multiple of 16, <= 256)", n);
+    return launch_selftest_umma_mn(a, b, n, d, tc_debug_flags(), as_stream(stream));
 }

@@ -84,6 +84,23 @@ constexpr int kActRgbF = kActInsH + 128;      // 256      rgb_feature_linear out
 constexpr int kActRgbH = kActRgbF + 256;      // 128      relu(rgb_feature_linears.0)
 constexpr int kActRows = kActRgbH + 128;      // 2912
 
+// ---- bf16 stash of the tensor-core TRAINING path (DMNERF_MODE_BF16), per block of 64 points ----------
+// The unit is one k-group slab [64 rows][8 bf16] = 1024 B; a region of F features is F/8 consecutive slabs,
+// i.e. exactly a no-swizzle UMMA operand image: K-major over features for the dgrad chain's masks, MN-major
+// with the 64 points as the reduction dim for wgrad -- so wgrad moves whole regions with ONE 1-D bulk copy.
+//   activations (written by the forward):  POS 8 | DIR 4 | H0..H7 8 x 32 | HID 32           = 300 slabs
+//   gradients   (written by dgrad)      :  G0..G7 8 x 32 | G8 32 | G9 16 (C padded to 128)  = 304 slabs
+// POS channel 63 (the pad) is unused; rows past n_points hold finite garbage in the activations and exact
+// zeros in the gradients, so they add nothing to any weight gradient.
+constexpr int kStBlk = 64;
+constexpr int kStKgBytes = kStBlk * 16;
+constexpr int kStPos = 0, kStDir = 8, kStH0 = 12, kStHid = 12 + 8 * 32, kStActKg = 300;
+constexpr int kStG0 = 0, kStG8 = 8 * 32, kStG9 = 9 * 32, kStGradKg = 304;
+constexpr int64_t kStActBlkBytes = static_cast<int64_t>(kStActKg) * kStKgBytes;    // 307,200
+constexpr int64_t kStGradBlkBytes = static_cast<int64_t>(kStGradKg) * kStKgBytes;  // 311,296
+// blocks are allocated for whole tile PAIRS (256 points) of the persistent kernels
+__host__ __device__ inline int64_t tc_stash_blocks(int64_t n_points) { return ((n_points + 255) / 256) * 4; }
+
 // Input of one MLP launch: either rays (points o + d*z and both embeddings computed in-kernel) or
 // already-embedded rows x[m,90].
 struct MlpInput {

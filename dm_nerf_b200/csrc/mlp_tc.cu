@@ -22,68 +22,13 @@
 // matrices are 128 contiguous bytes; LBO (next k-group) = rows*16 B, SBO (next 8 rows) = 128 B.  An
 // epilogue thread owns one row, so one 16-byte store writes 8 consecutive features of the next
 // layer's A operand and a warp's stores are 512 contiguous bytes (conflict-free).
-#include "mlp_layout.cuh"
-#include "tc_ptx.cuh"
-#include <cuda_bf16.h>
+#include "mlp_tc_common.cuh"
 
 namespace dmnerf {
 
 static int g_tc_debug_flags = 0;   // bit0: swap LBO/SBO in the smem descriptors (bring-up aid)
 
 namespace tc {
-
-constexpr int kTile = 128;
-constexpr int kPair = 2 * kTile;
-constexpr int kLayers = 10;
-constexpr int kChunkK = 32;                       // K columns per streamed weight chunk
-constexpr int kStages = 3;
-constexpr int kStageBytes = kChunkK * 256 * 2;    // 16 KB
-constexpr int kKgBytes = kTile * 16;              // one k-group of the A operand: 128 rows x 16 B
-constexpr int kABytes = 40 * kKgBytes;            // 32 k-groups H + 8 k-groups EXT = 81,920 B per tile
-constexpr int kExtKg = 32;                        // first k-group of the EXT region
-constexpr int kBiasFloats = 2704;                 // 9*256 | T9 bias (128) | w_density (256) | b_density (+pad)
-constexpr int kBiasT9 = 9 * 256;
-constexpr int kBiasWd = kBiasT9 + 128;
-constexpr int kBiasBd = kBiasWd + 256;
-constexpr int kEpiWarps = 16;                     // 8 per tile: 4 lane quarters x 2 column halves
-constexpr int kProducerWarp = 16, kMmaWarp = 17;
-constexpr int kThreads = 18 * 32;
-
-// shared memory map (bytes)
-constexpr int kSmA = 0;
-constexpr int kSmRing = 2 * kABytes;                           // 163,840
-constexpr int kSmBias = kSmRing + kStages * kStageBytes;       // 212,992
-constexpr int kSmBar = kSmBias + kBiasFloats * 4;              // 223,808
-constexpr int kSmDens = kSmBar + 128;                          // density partials of column-half 1: [2][128] floats
-constexpr int kSmTotal = kSmDens + 2 * kTile * 4;
-
-__host__ __device__ inline int layer_k(int l) { return l == 0 ? 64 : (l == 5 ? 320 : (l == 8 ? 288 : 256)); }
-__host__ __device__ inline int layer_akg0(int l) { return l == 0 ? kExtKg : 0; }
-
-struct Image {
-    int64_t chunk_off[kLayers];   // byte offset of the layer's first chunk
-    int n[kLayers];               // MMA N of the layer
-    int64_t bias_off;             // fp32 block (kBiasFloats)
-    int64_t scratch_off;          // fp32 scratch: Wc_rgb[128][256], Wc_ins[128][256], bc[256]
-    int64_t total_bytes;
-    int npad, ins_num;
-};
-
-__host__ __device__ inline Image make_image(int ins_num) {
-    Image im;
-    im.ins_num = ins_num;
-    im.npad = ((ins_num + 5) + 15) & ~15;
-    int64_t off = 0;
-    for (int l = 0; l < kLayers; ++l) {
-        im.n[l] = (l == 9) ? im.npad : 256;
-        im.chunk_off[l] = off;
-        off += static_cast<int64_t>(layer_k(l)) * im.n[l] * 2;
-    }
-    im.bias_off = off;       off += kBiasFloats * 4;
-    im.scratch_off = off;    off += (2 * 128 * 256 + 256) * 4;
-    im.total_bytes = off;
-    return im;
-}
 
 // ---- pack --------------------------------------------------------------------------------------------
 struct Params { const float* p[kNumParams]; };
@@ -149,6 +94,50 @@ __global__ void pack_bf16_kernel(Params pr, Image im, uint8_t* __restrict__ imag
     reinterpret_cast<__nv_bfloat16*>(image)[idx] = __float2bfloat16_rn(logical_weight(pr, scratch, l, n, k, im.ins_num));
 }
 
+// dgrad operand B[n = forward input j][k = forward output i] of dgrad layer d (mlp_tc_common.cuh)
+__device__ inline float dgrad_weight(const Params& pr, const float* scratch, int d, int n, int k, int ins_num) {
+    if (d == 0) {                                       // T9^T: k = raw channel, n = [rgb_hid | ins_hid] feature
+        if (n < 128) return k < 3 ? pr.p[P_RGBL_W][k * 128 + n] : 0.f;
+        return (k >= 4 && k < 5 + ins_num) ? pr.p[P_INSL_W][(k - 4) * 128 + (n - 128)] : 0.f;
+    }
+    if (d == 1) return scratch[k * 256 + n];            // composed rgb rows of T8 (k < 128); ins rows are detached
+    const int l = 9 - d;                                // d = 2 -> T7 ... d = 8 -> T1
+    if (l == 5) return pr.p[10][k * 319 + n];           // hidden columns of the skip layer
+    return pr.p[2 * l][k * 256 + n];
+}
+
+__global__ void pack_dgrad_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+    const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
+    const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t total = (im.f32_off - im.dg_off[0]) / 2;
+    if (idx >= total) return;
+    int d = 0;
+    while (d + 1 < kDgLayers && idx * 2 >= im.dg_off[d + 1] - im.dg_off[0]) ++d;
+    int64_t r = idx - (im.dg_off[d] - im.dg_off[0]) / 2;
+    const int per_chunk = kChunkK * 256;
+    const int c = static_cast<int>(r / per_chunk);
+    r -= static_cast<int64_t>(c) * per_chunk;
+    const int g = static_cast<int>(r / (256 * 8));
+    r -= static_cast<int64_t>(g) * 256 * 8;
+    const int n = static_cast<int>(r >> 3), e = static_cast<int>(r & 7);
+    const int k = c * kChunkK + g * 8 + e;
+    reinterpret_cast<__nv_bfloat16*>(image + im.dg_off[0])[idx] = __float2bfloat16_rn(dgrad_weight(pr, scratch, d, n, k, im.ins_num));
+}
+
+__global__ void pack_f32_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+    float* f = reinterpret_cast<float*>(image + im.f32_off);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= kF32Floats) return;
+    float v;
+    if (i < kF32Insf) v = pr.p[P_RGBF_W][i];
+    else if (i < kF32Rgb0) v = pr.p[P_INSF_W][i - kF32Insf];
+    else if (i < kF32Ins0) { const int r = i - kF32Rgb0; v = pr.p[P_RGB0_W][(r >> 8) * 283 + (r & 255)]; }
+    else if (i < kF32BRgbf) v = pr.p[P_INS0_W][i - kF32Ins0];
+    else if (i < kF32BInsf) v = pr.p[P_RGBF_B][i - kF32BRgbf];
+    else v = pr.p[P_INSF_B][i - kF32BInsf];
+    f[i] = v;
+}
+
 __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
     const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
     float* b = reinterpret_cast<float*>(image + im.bias_off);
@@ -167,31 +156,12 @@ __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ imag
 }
 
 
-// ---- device helpers ---------------------------------------------------------------------------------------
-// mbarrier addresses (8 B each) inside the barrier block
-struct Bars {
-    uint32_t base;
-    __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }
-    __device__ __forceinline__ uint32_t w_empty(int s) const { return base + 8 * (kStages + s); }
-    __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kStages + t); }
-    __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kStages + 2 + t); }
-};
-
-__device__ __forceinline__ uint64_t op_desc(uint32_t addr, uint32_t lbo, uint32_t sbo, int swap) {
-    return swap ? ptx::smem_desc(addr, sbo, lbo) : ptx::smem_desc(addr, lbo, sbo);
-}
-
-// 8 consecutive features of one row -> one 16-byte store into k-group `kg` of the A operand
-__device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const float v[8], bool relu) {
-    ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, ptx::pack_bf16(v[0], v[1], relu), ptx::pack_bf16(v[2], v[3], relu),
-                      ptx::pack_bf16(v[4], v[5], relu), ptx::pack_bf16(v[6], v[7], relu));
-}
-
 // Embedding of a 3-vector into EXT k-groups [KG0, KG1): channel c = [x | f: sin(3) cos(3)], 8 channels per
 // k-group.  The first needed octave uses full-range sincosf on x*2^f (exact scaling); higher octaves follow by
 // angle doubling (error << bf16 resolution).  Channels outside the range are dead code after unrolling.
 template <int F, int KG0, int KG1>
-__device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3]) {
+__device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3], uint8_t* gst = nullptr,
+                                             int gkg0 = 0) {
     constexpr int CH = 3 + 6 * F;
     constexpr int C0 = KG0 * 8, C1 = KG1 * 8;
     constexpr int F0 = C0 < 3 ? 0 : (C0 - 3) / 6;           // first octave that touches [C0, C1)
@@ -217,22 +187,26 @@ __device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const flo
         }
     }
 #pragma unroll
-    for (int g = KG0; g < KG1; ++g) store_kg(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false);
+    for (int g = KG0; g < KG1; ++g) store_kg(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false, gst, gkg0 + g);
 }
 
 __device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kg0,
-                                           int kg1) {
+                                           int kg1, uint8_t* gst = nullptr, int gkg0 = 0) {
     for (int g = kg0; g < kg1; ++g) {
         float v[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] = (src && g * 8 + e < count) ? __ldg(src + g * 8 + e) : 0.f;
-        store_kg(a_base, kExtKg + g, row, v, false);
+        store_kg(a_base, kExtKg + g, row, v, false, gst, gkg0 + g);
     }
 }
 
 // ---- the kernel -------------------------------------------------------------------------------------------------
+// kStash (training): every A operand the backward needs (embeddings, h0..h7, [rgb_hid|ins_hid]) is mirrored
+// to the per-tile bf16 stash (mlp_layout.cuh) by the same 16-byte stores that build the smem operand.
+template <bool kStash>
 __global__ void __launch_bounds__(kThreads, 1)
-mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags) {
+mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags,
+                    uint8_t* __restrict__ stash) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sm0 = ptx::smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -331,6 +305,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             const int64_t tile0 = pair * kPair + t * kTile;
             const int64_t p = tile0 + row;
             const bool valid = p < in.n_points;
+            uint8_t* gst = kStash ? stash + ((pair * 2 + t) * 2 + (row >> 6)) * kStActBlkBytes + (row & 63) * 16 : nullptr;
             float dir[3] = {0.f, 0.f, 0.f};
             if (in.x == nullptr) {
                 float pos[3] = {0.f, 0.f, 0.f};
@@ -347,10 +322,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 #pragma unroll
                     for (int c = 0; c < 3; ++c) dir[c] = d[c] * inv;
                 }
-                if (half == 0) embed_to_ext<kPosFreqs, 0, 4>(a_base, row, pos);
-                else           embed_to_ext<kPosFreqs, 4, 8>(a_base, row, pos);
+                if (half == 0) embed_to_ext<kPosFreqs, 0, 4>(a_base, row, pos, gst, kStPos);
+                else           embed_to_ext<kPosFreqs, 4, 8>(a_base, row, pos, gst, kStPos);
             } else {
-                row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, half * 4, half * 4 + 4);
+                row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, half * 4, half * 4 + 4, gst, kStPos);
             }
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
@@ -380,14 +355,14 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 #pragma unroll
                             for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_bias[kBiasWd + cb * 32 + g * 8 + e], dens);
                         }
-                        store_kg(a_base, cb * 4 + g, row, v, true);
+                        store_kg(a_base, cb * 4 + g, row, v, true, gst, (l == 8 ? kStHid : kStH0 + 32 * l) + cb * 4 + g);
                     }
                 }
                 if (l == 7) {
                     // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it)
                     if (half == 0) {
-                        if (in.x == nullptr) embed_to_ext<kDirFreqs, 0, 4>(a_base, row, dir);
-                        else row_to_ext(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 0, 4);
+                        if (in.x == nullptr) embed_to_ext<kDirFreqs, 0, 4>(a_base, row, dir, gst, kStDir);
+                        else row_to_ext(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 0, 4, gst, kStDir);
                     } else {
                         dens_part[row] = dens;
                     }
@@ -495,7 +470,7 @@ umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, i
 
 }  // namespace tc
 
-int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, cudaStream_t st) {
+int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -504,14 +479,24 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
     }
     DM_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0 && (reinterpret_cast<uintptr_t>(raw_out) & 15) == 0,
                DMNERF_EINVAL, "mlp_fwd(bf16): packed image and raw_out must be 16-byte aligned");
-    DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmTotal));
     const int64_t pairs = (in.n_points + tc::kPair - 1) / tc::kPair;
     const unsigned grid = static_cast<unsigned>(pairs < sm_count ? pairs : sm_count);
-    tc::mlp_fwd_bf16_kernel<<<grid, tc::kThreads, tc::kSmTotal, st>>>(in, static_cast<const uint8_t*>(packed),
-                                                                     tc::make_image(ins_num), raw_out, g_tc_debug_flags);
+    if (stash) {
+        DM_REQUIRE((reinterpret_cast<uintptr_t>(stash) & 15) == 0, DMNERF_EINVAL, "mlp_fwd(bf16): stash must be 16-byte aligned");
+        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmTotal));
+        tc::mlp_fwd_bf16_kernel<true><<<grid, tc::kThreads, tc::kSmTotal, st>>>(
+            in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags,
+            static_cast<uint8_t*>(stash));
+    } else {
+        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmTotal));
+        tc::mlp_fwd_bf16_kernel<false><<<grid, tc::kThreads, tc::kSmTotal, st>>>(
+            in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags, nullptr);
+    }
     DM_LAUNCH_CHECK("mlp_fwd_bf16_kernel");
     return DMNERF_OK;
 }
+
+int tc_debug_flags() { return g_tc_debug_flags; }
 
 int64_t bf16_image_bytes(int ins_num) { return tc::make_image(ins_num).total_bytes; }
 
@@ -525,6 +510,9 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     const int64_t elems = im.bias_off / 2;
     tc::pack_bf16_kernel<<<static_cast<unsigned>((elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_bias_kernel<<<(tc::kBiasFloats + 255) / 256, 256, 0, st>>>(pr, im, image);
+    const int64_t dg_elems = (im.f32_off - im.dg_off[0]) / 2;
+    tc::pack_dgrad_kernel<<<static_cast<unsigned>((dg_elems + 255) / 256), 256, 0, st>>>(pr, im, image);
+    tc::pack_f32_kernel<<<(tc::kF32Floats + 255) / 256, 256, 0, st>>>(pr, im, image);
     DM_LAUNCH_CHECK("pack_bf16");
     return DMNERF_OK;
 }

@@ -1,0 +1,107 @@
+// mlp_tc_common.cuh -- constants, packed-image map and small device helpers shared by the tensor-core MLP
+// kernels: forward (mlp_tc.cu) and training backward (mlp_tc_bwd.cu).
+#pragma once
+#include "mlp_layout.cuh"
+#include "tc_ptx.cuh"
+#include <cuda_bf16.h>
+
+namespace dmnerf {
+namespace tc {
+
+constexpr int kTile = 128;
+constexpr int kPair = 2 * kTile;
+constexpr int kLayers = 10;
+constexpr int kChunkK = 32;                       // K columns per streamed weight chunk
+constexpr int kStages = 3;
+constexpr int kStageBytes = kChunkK * 256 * 2;    // 16 KB
+constexpr int kKgBytes = kTile * 16;              // one k-group of the A operand: 128 rows x 16 B
+constexpr int kABytes = 40 * kKgBytes;            // 32 k-groups H + 8 k-groups EXT = 81,920 B per tile
+constexpr int kExtKg = 32;                        // first k-group of the EXT region
+constexpr int kBiasFloats = 2704;                 // 9*256 | T9 bias (128) | w_density (256) | b_density (+pad)
+constexpr int kBiasT9 = 9 * 256;
+constexpr int kBiasWd = kBiasT9 + 128;
+constexpr int kBiasBd = kBiasWd + 256;
+constexpr int kEpiWarps = 16;                     // 8 per tile: 4 lane quarters x 2 column halves
+constexpr int kProducerWarp = 16, kMmaWarp = 17;
+constexpr int kThreads = 18 * 32;
+
+// shared memory map (bytes)
+constexpr int kSmA = 0;
+constexpr int kSmRing = 2 * kABytes;                           // 163,840
+constexpr int kSmBias = kSmRing + kStages * kStageBytes;       // 212,992
+constexpr int kSmBar = kSmBias + kBiasFloats * 4;              // 223,808
+constexpr int kSmDens = kSmBar + 128;                          // density partials of column-half 1: [2][128] floats
+constexpr int kSmTotal = kSmDens + 2 * kTile * 4;
+
+__host__ __device__ inline int layer_k(int l) { return l == 0 ? 64 : (l == 5 ? 320 : (l == 8 ? 288 : 256)); }
+__host__ __device__ inline int layer_akg0(int l) { return l == 0 ? kExtKg : 0; }
+
+// dgrad chain (training): layer d = 0..8 computes dX = G * W for forward layers T9, T8(rgb rows only: the
+// instance branch reads h.detach()), T7, ..., T1; K = forward outputs feeding a gradient, N = 256 forward inputs.
+constexpr int kDgLayers = 9;
+// fp32 copies kept for the chain rule through the two composed pairs (unpack_grads): floats
+constexpr int kF32Rgbf = 0, kF32Insf = 65536, kF32Rgb0 = 131072, kF32Ins0 = 131072 + 32768,
+              kF32BRgbf = 131072 + 65536, kF32BInsf = kF32BRgbf + 256, kF32Floats = kF32BInsf + 256;
+
+struct Image {
+    int64_t chunk_off[kLayers];   // byte offset of the layer's first chunk
+    int n[kLayers];               // MMA N of the layer
+    int64_t bias_off;             // fp32 block (kBiasFloats)
+    int64_t scratch_off;          // fp32 scratch: Wc_rgb[128][256], Wc_ins[128][256], bc[256]
+    int64_t dg_off[kDgLayers];    // dgrad chunk streams ([k-group][256 rows][8 bf16] per 32-wide K chunk)
+    int dg_k[kDgLayers];
+    int64_t f32_off;              // kF32Floats fp32 copies (rgb/ins feature layers) for unpack_grads
+    int64_t total_bytes;
+    int npad, ins_num, kp9;       // kp9 = C rounded up to 32: K of the first dgrad layer
+};
+
+__host__ __device__ inline Image make_image(int ins_num) {
+    Image im;
+    im.ins_num = ins_num;
+    im.npad = ((ins_num + 5) + 15) & ~15;
+    int64_t off = 0;
+    for (int l = 0; l < kLayers; ++l) {
+        im.n[l] = (l == 9) ? im.npad : 256;
+        im.chunk_off[l] = off;
+        off += static_cast<int64_t>(layer_k(l)) * im.n[l] * 2;
+    }
+    im.bias_off = off;       off += kBiasFloats * 4;
+    im.scratch_off = off;    off += (2 * 128 * 256 + 256) * 4;
+    im.kp9 = ((ins_num + 5) + 31) & ~31;
+    for (int d = 0; d < kDgLayers; ++d) {
+        im.dg_k[d] = d == 0 ? im.kp9 : (d == 1 ? 128 : 256);
+        im.dg_off[d] = off;
+        off += static_cast<int64_t>(im.dg_k[d]) * 256 * 2;
+    }
+    im.f32_off = off;        off += static_cast<int64_t>(kF32Floats) * 4;
+    im.total_bytes = off;
+    return im;
+}
+
+// ---- device helpers ---------------------------------------------------------------------------------------
+// mbarrier addresses (8 B each) inside the barrier block
+struct Bars {
+    uint32_t base;
+    __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }
+    __device__ __forceinline__ uint32_t w_empty(int s) const { return base + 8 * (kStages + s); }
+    __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kStages + t); }
+    __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kStages + 2 + t); }
+};
+
+__device__ __forceinline__ uint64_t op_desc(uint32_t addr, uint32_t lbo, uint32_t sbo, int swap) {
+    return swap ? ptx::smem_desc(addr, sbo, lbo) : ptx::smem_desc(addr, lbo, sbo);
+}
+
+// 8 consecutive features of one row -> one 16-byte store into k-group `kg` of the A operand; when `gst` is
+// given (training; already offset to this thread's row inside its 64-point stash block), the same 16 bytes
+// also go to slab `gkg` of the HBM stash (a warp writes 512 contiguous bytes).
+__device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const float v[8], bool relu,
+                                         uint8_t* gst = nullptr, int gkg = 0) {
+    const uint32_t w0 = ptx::pack_bf16(v[0], v[1], relu), w1 = ptx::pack_bf16(v[2], v[3], relu);
+    const uint32_t w2 = ptx::pack_bf16(v[4], v[5], relu), w3 = ptx::pack_bf16(v[6], v[7], relu);
+    ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, w0, w1, w2, w3);
+    if (gst) *reinterpret_cast<uint4*>(gst + gkg * kStKgBytes) = make_uint4(w0, w1, w2, w3);
+}
+
+}  // namespace tc
+}  // namespace dmnerf

@@ -87,16 +87,16 @@ class DM_NeRF(nn.Module):
     def query_rays(self, rays_o, rays_d, z_vals) -> torch.Tensor:
         """raw[N,S,5+K] for points rays_o + rays_d*z with both embeddings computed in-kernel
         (render.py:49-61 / manipulator.py:108-134 in one launch)."""
-        if self._wants_grad():
-            return ops._MlpFn.apply(rays_o, rays_d, z_vals, None, self.ins_num, self.packed(MODE_FP32),
-                                    *self._ordered_params())
         mode = ops.get_mode()
+        if self._wants_grad():
+            return ops._MlpFn.apply(rays_o, rays_d, z_vals, None, self.ins_num, mode, self.packed(mode),
+                                    *self._ordered_params())
         return ops.mlp_fwd(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)[0]
 
     def forward(self, x):
         """x[..., 90] already embedded (dm_nerf.py:80-106)."""
-        if self._wants_grad():
-            return ops._MlpFn.apply(None, None, None, x, self.ins_num, self.packed(MODE_FP32),
-                                    *self._ordered_params())
         mode = ops.get_mode()
+        if self._wants_grad():
+            return ops._MlpFn.apply(None, None, None, x, self.ins_num, mode, self.packed(mode),
+                                    *self._ordered_params())
         return ops.mlp_fwd_embedded(x, self.packed(mode), self.ins_num, mode)[0]

@@ -21,7 +21,8 @@ launches = 0
 
 
 def set_mode(mode) -> None:
-    """'fp32' (CUDA-core parity mode) or 'bf16' (tcgen05 tensor-core mode) for no-grad MLP queries."""
+    """'fp32' (CUDA-core parity mode) or 'bf16' (tcgen05 tensor-core mode) for MLP queries, forward and
+    (when gradients are enabled) backward."""
     global _default_mode
     _default_mode = _MODE_NAMES[mode] if isinstance(mode, str) else int(mode)
 
@@ -132,7 +133,7 @@ def mlp_fwd(rays_o, rays_d, z, packed, ins_num: int, mode: int, stash: bool = Fa
     raw = torch.empty((n, s, ins_num + 5), dtype=torch.float32, device=z.device)
     acts = None
     if stash:
-        acts = torch.empty(_lib.lib().dmnerf_acts_bytes(n * s, ins_num), dtype=torch.uint8, device=z.device)
+        acts = _aligned_bytes(_lib.lib().dmnerf_acts_bytes(n * s, ins_num, mode), z.device)
     _timed_call(f"dmnerf_mlp_fwd[S={s},mode={mode}]", _lib.lib().dmnerf_mlp_fwd, _ptr(rays_o), _ptr(rays_d), _ptr(z),
                 n, s, _ptr(packed), ins_num, mode, _ptr(raw), _ptr(acts), _stream())
     _count()
@@ -149,19 +150,31 @@ def mlp_fwd_embedded(x, packed, ins_num: int, mode: int, stash: bool = False):
     raw = torch.empty((m, ins_num + 5), dtype=torch.float32, device=x.device)
     acts = None
     if stash:
-        acts = torch.empty(_lib.lib().dmnerf_acts_bytes(m, ins_num), dtype=torch.uint8, device=x.device)
+        acts = _aligned_bytes(_lib.lib().dmnerf_acts_bytes(m, ins_num, mode), x.device)
     check(_lib.lib().dmnerf_mlp_fwd_embedded(_ptr(x2), m, _ptr(packed), ins_num, mode, _ptr(raw), _ptr(acts),
                                              _stream()), "dmnerf_mlp_fwd_embedded")
     _count()
     return raw.reshape(*lead, ins_num + 5), acts
 
 
-def mlp_bwd(packed_fp32, acts, d_raw, n_points: int, ins_num: int, shapes: Sequence[torch.Size]) -> List[torch.Tensor]:
+def _aligned_bytes(nbytes: int, device) -> torch.Tensor:
+    """uint8 buffer whose data pointer is 1024-byte aligned (bulk-copy / UMMA operand images)."""
+    if nbytes < 0:
+        raise RuntimeError(f"dm_nerf_b200: size query failed: {_lib.last_error()}")
+    buf = torch.empty(nbytes + 1024, dtype=torch.uint8, device=device)
+    off = (-buf.data_ptr()) % 1024
+    return buf[off:off + nbytes]
+
+
+def mlp_bwd(packed, acts, d_raw, n_points: int, ins_num: int, shapes: Sequence[torch.Size],
+            mode: int = MODE_FP32) -> List[torch.Tensor]:
     d_raw = _f32(d_raw, "d_raw")
     grads = [torch.zeros(s, dtype=torch.float32, device=d_raw.device) for s in shapes]
-    check(_lib.lib().dmnerf_mlp_bwd(_ptr(packed_fp32), _ptr(acts), _ptr(d_raw), n_points, ins_num, _ptr_array(grads),
-                                    None, _stream()), "dmnerf_mlp_bwd")
-    _count()
+    ws_bytes = _lib.lib().dmnerf_bwd_workspace_bytes(n_points, ins_num, mode)
+    ws = _aligned_bytes(ws_bytes, d_raw.device) if ws_bytes > 0 else None
+    _timed_call(f"dmnerf_mlp_bwd[mode={mode}]", _lib.lib().dmnerf_mlp_bwd, _ptr(packed), _ptr(acts), _ptr(d_raw),
+                n_points, ins_num, mode, _ptr_array(grads), _ptr(ws), _stream())
+    _count(1 if mode == MODE_FP32 else 3)
     return grads
 
 
@@ -170,23 +183,24 @@ class _MlpFn(torch.autograd.Function):
     (the reference detaches z_samples, render.py:68, and rays are data)."""
 
     @staticmethod
-    def forward(ctx, rays_o, rays_d, z, x, ins_num, packed_fp32, *params):
+    def forward(ctx, rays_o, rays_d, z, x, ins_num, mode, packed, *params):
         if x is None:
-            raw, acts = mlp_fwd(rays_o, rays_d, z, packed_fp32, ins_num, MODE_FP32, stash=True)
+            raw, acts = mlp_fwd(rays_o, rays_d, z, packed, ins_num, mode, stash=True)
             ctx.n_points = z.numel()
         else:
-            raw, acts = mlp_fwd_embedded(x, packed_fp32, ins_num, MODE_FP32, stash=True)
+            raw, acts = mlp_fwd_embedded(x, packed, ins_num, mode, stash=True)
             ctx.n_points = x.numel() // 90
-        ctx.save_for_backward(packed_fp32, acts)
-        ctx.ins_num = ins_num
+        ctx.save_for_backward(packed, acts)
+        ctx.ins_num, ctx.mode = ins_num, mode
         ctx.shapes = [p.shape for p in params]
         return raw
 
     @staticmethod
     def backward(ctx, d_raw):
         packed, acts = ctx.saved_tensors
-        grads = mlp_bwd(packed, acts, d_raw.reshape(-1, ctx.ins_num + 5), ctx.n_points, ctx.ins_num, ctx.shapes)
-        return (None, None, None, None, None, None, *grads)
+        grads = mlp_bwd(packed, acts, d_raw.reshape(-1, ctx.ins_num + 5), ctx.n_points, ctx.ins_num, ctx.shapes,
+                        ctx.mode)
+        return (None, None, None, None, None, None, None, *grads)
 
 
 # ---------------------------------------------------------------------------------------------------

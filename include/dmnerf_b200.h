@@ -52,22 +52,27 @@ int  dmnerf_weights_pack(const float* const* params, int ins_num, int mode, void
  * dm_nerf (networks/render.py:49-61, 71-83) and manipulator_nerf (networks/manipulator.py:108-134).
  * rays_o, rays_d [n_rays,3]; z [n_rays,n_samples]; raw_out [n_rays,n_samples,5+ins_num].
  * Points o + d*z, view dirs d/|d| and both embeddings are computed in-kernel.
- * acts (may be NULL): training-mode activation stash of dmnerf_acts_bytes() bytes for the backward. */
+ * acts (may be NULL): training-mode activation stash of dmnerf_acts_bytes(n_points, ins_num, mode) bytes for
+ * the backward (fp32 rows in DMNERF_MODE_FP32; bf16 UMMA operand images per 64-point block in DMNERF_MODE_BF16,
+ * 1024-byte aligned). */
 int  dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
                     const void* packed, int ins_num, int mode, float* raw_out, void* acts, void* stream);
 /* Same network on already-embedded rows x[m,90] (DM_NeRF.forward(x) called directly,
  * tools/mesh_generator.py:45). */
 int  dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int ins_num, int mode,
                              float* raw_out, void* acts, void* stream);
-int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num);
-/* a12: parameter gradients of the MLP given d(raw) [n_points, 5+ins_num].  packed: the
- * DMNERF_MODE_FP32 image of the SAME weights the forward used; acts: the stash that forward wrote.
+int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num, int mode);
+/* a12: parameter gradients of the MLP given d(raw) [n_points, 5+ins_num] (the autograd of
+ * networks/dm_nerf.py:80-106 that total_loss.backward() runs, train_dmsr.py:63).  packed: the image of
+ * the SAME weights and the SAME mode the forward used; acts: the stash that forward wrote.
  * grads: HOST array of DMNERF_NUM_PARAMS device pointers (same order/shapes as params), ACCUMULATED
  * into (caller zeroes).  Honors h.detach() on the instance branch (networks/dm_nerf.py:95): the
- * instance head's gradient stops at ins_feature_linear.  workspace: dmnerf_bwd_workspace_bytes(). */
+ * instance head's gradient stops at ins_feature_linear.  workspace: dmnerf_bwd_workspace_bytes() bytes
+ * (1024-byte aligned; NULL allowed when that is 0).  DMNERF_MODE_BF16 runs the dgrad chain and the
+ * split-K wgrad GEMMs on tcgen05 (csrc/mlp_tc_bwd.cu); DMNERF_MODE_FP32 is the CUDA-core parity path. */
 int  dmnerf_mlp_bwd(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
-                    int ins_num, float* const* grads, void* workspace, void* stream);
-int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num);
+                    int ins_num, int mode, float* const* grads, void* workspace, void* stream);
+int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num, int mode);
 
 /* ---- a5/a8: volume compositing ---------------------------------------------------------------
  * Replaces render_train (networks/render.py:6-28) [flags=DROP_EMPTY] and manipulator_render
@@ -140,7 +145,10 @@ int  dmnerf_label_argmax(const float* ins, int64_t n, int k, uint8_t* labels, vo
 /* ---- self test of the tcgen05 building blocks (used by tests/) ---------------------------------------
  * D[128,n] = A[128,k] * B[n,k]^T in bf16 with fp32 accumulate; a,b fp32 in, d fp32 out. */
 int  dmnerf_selftest_umma(const float* a, const float* b, int n, int k, float* d, void* stream);
-/* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the shared-memory descriptors).
+/* D[128,n] = A[64,128]^T * B[64,n]: both operands MN-major, the 64 rows being the reduction dim -- the operand
+ * form of the wgrad GEMMs.  a,b fp32 in (row-major [64][128], [64][n]), d fp32 out [128][n]. */
+int  dmnerf_selftest_umma_mn(const float* a, const float* b, int n, float* d, void* stream);
+/* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the forward's descriptors; bit1: in wgrad's).
  * flags < 0 only queries.  Returns the previous value. */
 int  dmnerf_debug_flags(int flags);
 

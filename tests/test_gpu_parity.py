@@ -469,3 +469,83 @@ def test_train_step_gradients_golden(golden):
             # end to end the fine depths differ at the cdf-conditioning level (see _z_tol); a 1e-3 shift of a
             # low-weight sample is half a radian at the 2^9 octave, so the embedding-fed columns get 5e-2 of rms
             assert np.max(np.abs(got - ref)) <= 5e-2 * scale + 1e-9, (tag, name, np.max(np.abs(got - ref)), scale)
+
+
+def test_umma_mn_selftest():
+    """D = A^T B with both operands MN-major and the 64 rows as the reduction dim (the wgrad operand form)."""
+    import ctypes as C
+    from dm_nerf_b200 import _lib
+    lib = _lib.lib()
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    gen = torch.Generator().manual_seed(2)
+    for n in (16, 32, 64, 256):
+        a, b = torch.randn(64, 128, generator=gen).to(DEV), torch.randn(64, n, generator=gen).to(DEV)
+        d = torch.zeros(128, n, device=DEV)
+        rc = lib.dmnerf_selftest_umma_mn(C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), n, C.c_void_p(d.data_ptr()), st)
+        assert rc == 0, _lib.last_error()
+        ref = a.bfloat16().float().t() @ b.bfloat16().float()
+        assert float((d - ref).abs().max()) <= 1e-3, n
+
+
+def _bf16_mode():
+    from dm_nerf_b200 import ops
+
+    class _Ctx:
+        def __enter__(self):
+            ops.set_mode("bf16")
+
+        def __exit__(self, *exc):
+            ops.set_mode("fp32")
+    return _Ctx()
+
+
+@pytest.mark.parametrize("k,n,s", [(32, 5, 77), (16, 3, 64), (93, 2, 192), (32, 64, 192)])
+def test_mlp_backward_bf16_vs_oracle_autograd(k, n, s):
+    """Tensor-core training path (bf16 operands, fp32 accumulate): forward with stash, dgrad chain, split-K
+    wgrad, unpack.  Checked per parameter tensor against
+      (a) the rounding-faithful CPU model (oracle/dmnerf_oracle_bf16.py: bf16 rounding where the kernels round):
+          ||g - g_ref|| <= 3e-2 ||g_ref|| and cosine >= 0.9995 (measured 1e-3..2e-2: accumulation order and the
+          few ReLU units that sit within fp32 noise of zero);
+      (b) the fp32 oracle: cosine >= 0.98 -- a bf16 forward flips the mask of every unit whose pre-activation is
+          within bf16 noise of zero, worth ~3 % of gradient norm per layer, so only direction is asserted."""
+    import dmnerf_oracle_bf16 as orb
+    gen = torch.Generator().manual_seed(5)
+    o = (torch.rand(n, 3, generator=gen) - 0.5) * 2
+    d = torch.randn(n, 3, generator=gen)
+    z, _ = torch.sort(torch.rand(n, s, generator=gen) * 11 + 4, -1)
+    g_out = torch.randn(n, s, k + 5, generator=gen)
+    refs = []
+    for fn in (orb.query_field_bf16, orc.query_field):
+        p = {kk: v.requires_grad_(True) for kk, v in orc.init_params(k, 9).items()}
+        out = fn(p, o, d, z)
+        (out * g_out).sum().backward()
+        refs.append((out.detach(), p))
+    m = make_model(k, 9)
+    with _bf16_mode():
+        got = m.query_rays(cu(o), cu(d), cu(z))
+        assert got.requires_grad
+        (got * cu(g_out)).sum().backward()
+    close(got, refs[0][0], 2e-3)
+    close(got, refs[1][0], 6e-2)
+    for name, prm in m.named_parameters():
+        a = prm.grad.detach().cpu().double().reshape(-1)
+        assert torch.isfinite(a).all(), name
+        for (_, p), (rel_tol, cos_tol) in zip(refs, ((3e-2, 0.9995), (1.0, 0.98))):
+            b = p[name].grad.double().reshape(-1)
+            rel = float((a - b).norm() / b.norm().clamp_min(1e-30))
+            cos = float((a @ b) / (a.norm() * b.norm()).clamp_min(1e-30))
+            assert rel <= rel_tol and cos >= cos_tol, f"{name}: rel {rel:.4f} cos {cos:.6f}"
+
+
+def test_ins_branch_is_detached_from_trunk_bf16():
+    k = 32
+    m = make_model(k, 3)
+    gen = torch.Generator().manual_seed(6)
+    o, d = cu(torch.rand(2, 3, generator=gen)), cu(torch.randn(2, 3, generator=gen))
+    z = cu(torch.sort(torch.rand(2, 64, generator=gen) * 11 + 4, -1)[0])
+    with _bf16_mode():
+        raw = m.query_rays(o, d, z)
+        raw[..., 4:].sum().backward()
+    for name, prm in m.named_parameters():
+        touched = float(prm.grad.abs().max()) > 0
+        assert touched == name.startswith("ins_"), name

@@ -24,6 +24,7 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
     k = int(sys.argv[2]) if len(sys.argv) > 2 else 32
     steps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
+    ops.set_mode(sys.argv[4] if len(sys.argv) > 4 else "fp32")
     H, W = 480, 640
     dev = torch.device("cuda")
     np.random.seed(0); torch.manual_seed(0)
@@ -60,7 +61,7 @@ def main():
         l = step()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / steps
-    print(f"train step N={n} K={k}: {dt * 1e3:.2f} ms/step -> {n / dt:.0f} rays/s; loss {float(l0):.4f} -> {float(l):.4f}")
+    print(f"train step N={n} K={k} mode={ops.get_mode()}: {dt * 1e3:.2f} ms/step -> {n / dt:.0f} rays/s; loss {float(l0.detach()):.4f} -> {float(l.detach()):.4f}")
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         step(); torch.cuda.synchronize()
