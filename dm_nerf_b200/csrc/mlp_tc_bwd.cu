@@ -480,7 +480,7 @@ __global__ void unpack_grads_kernel(const float* __restrict__ gimg, const uint8_
         case 10: count = 256 * 319; break;
         case P_RGBF_W: case P_INSF_W: count = 65536; break;
         case P_RGB0_W: count = 128 * 283; break;
-        case P_INS0_W: count = 128 * 256; break;
+        case P_INS0_W: count = 0; break;
         case P_RGB0_B: case P_INS0_B: count = 128; break;
         case P_DENS_W: count = 256; break;
         case P_DENS_B: count = 1; break;
@@ -507,18 +507,10 @@ __global__ void unpack_grads_kernel(const float* __restrict__ gimg, const uint8_
             const float* w1 = param == P_RGBF_B ? w_rgb0 : w_ins0;
             const float* dbc = param == P_RGBF_B ? gb8 : gb8 + 128;
             for (int i = 0; i < 128; ++i) v = fmaf(w1[i * 256 + idx], dbc[i], v);
-        } else if (param == P_RGB0_W || param == P_INS0_W) {       // dW1[i][j] = sum_k dWc[i][k] W0[j][k] + dbc[i] b0[j]
-            const bool rgb = param == P_RGB0_W;
-            const int ld = rgb ? 283 : 256;
-            const int i = idx / ld, j = idx % ld;
-            if (j < 256) {
-                const float* dwc = (rgb ? gw8 : gw8 + 128 * 256) + i * 256;
-                const float* w0 = (rgb ? w_rgbf : w_insf) + j * 256;
-                for (int k = 0; k < 256; ++k) v = fmaf(dwc[k], w0[k], v);
-                v = fmaf((rgb ? gb8 : gb8 + 128)[i], (rgb ? b_rgbf : b_insf)[j], v);
-            } else {
-                v = gimg[kGW8D + i * 32 + (j - 256)];
-            }
+        } else if (param == P_RGB0_W || param == P_INS0_W) {       // dir-embedding columns only; the hidden columns are
+            const int i = idx / 283, j = idx % 283;                // dot products over k: unpack_composed_kernel
+            if (param == P_INS0_W || j < 256) continue;
+            v = gimg[kGW8D + i * 32 + (j - 256)];
         } else if (param == P_RGB0_B) v = gb8[idx];
         else if (param == P_INS0_B) v = gb8[128 + idx];
         else if (param == P_DENS_W) v = gimg[kGWD + 3 * 256 + idx];
@@ -528,6 +520,28 @@ __global__ void unpack_grads_kernel(const float* __restrict__ gimg, const uint8_
         else if (param == P_RGBL_W) v = gimg[kGW9 + (idx / 128) * 256 + idx % 128];
         else if (param == P_RGBL_B) v = gb9[idx];
         gp.g[param][idx] += v;
+    }
+}
+
+// dW1[i][j] += sum_k dWc[i][k] W0[j][k] + dbc[i] b0[j] for the hidden columns of rgb_feature_linears.0 (ld 283) and
+// ins_feature_linears.0 (ld 256): one warp per output, k across lanes (both rows read coalesced).
+__global__ void unpack_composed_kernel(const float* __restrict__ gimg, const uint8_t* __restrict__ image, Image im,
+                                       GradPtrs gp) {
+    const float* f32 = reinterpret_cast<const float*>(image + im.f32_off);
+    const int lane = threadIdx.x & 31;
+    const int out = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);      // 2 x 128 x 256 outputs
+    if (out >= 2 * 128 * 256) return;
+    const int br = out >> 15, i = (out >> 8) & 127, j = out & 255;
+    const float* dwc = gimg + gwl(7) + (br * 128 + i) * 256;
+    const float* w0 = f32 + (br == 0 ? kF32Rgbf : kF32Insf) + j * 256;
+    float v = 0.f;
+#pragma unroll
+    for (int k = lane; k < 256; k += 32) v = fmaf(dwc[k], w0[k], v);
+    v = warp_sum(v);
+    if (lane == 0) {
+        v = fmaf(gimg[kGB + 8 * 256 + br * 128 + i], f32[(br == 0 ? kF32BRgbf : kF32BInsf) + j], v);
+        float* g = br == 0 ? gp.g[P_RGB0_W] + i * 283 + j : gp.g[P_INS0_W] + i * 256 + j;
+        *g += v;
     }
 }
 
@@ -617,7 +631,8 @@ int launch_mlp_bwd_bf16(const void* packed, const void* acts, const float* d_raw
 
     tcb::GradPtrs gp;
     for (int i = 0; i < kNumParams; ++i) gp.g[i] = grads[i];
-    tcb::unpack_grads_kernel<<<dim3(64, kNumParams), 256, 0, st>>>(gimg, static_cast<const uint8_t*>(packed), im, gp);
+    tcb::unpack_grads_kernel<<<dim3(256, kNumParams), 256, 0, st>>>(gimg, static_cast<const uint8_t*>(packed), im, gp);
+    tcb::unpack_composed_kernel<<<2 * 128 * 256 / 8, 256, 0, st>>>(gimg, static_cast<const uint8_t*>(packed), im, gp);
     DM_LAUNCH_CHECK("unpack_grads_kernel");
     return DMNERF_OK;
 }

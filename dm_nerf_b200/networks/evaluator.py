@@ -1,7 +1,8 @@
 """Training losses with the reference's names (networks/evaluator.py:8-74): ``img2mse``, ``mse2psnr`` and the
 Hungarian-matched instance loss ``ins_criterion``.  SURVEY 2 row 10 keeps these in stock torch + scipy: they
 consume the ray path's ``rgb_*`` / ``ins_*`` outputs, are O(N_rays * ins_num^2), and sit outside the hot path.
-The cost matrices are built on the device; only the [valid, ins_num] matrix crosses to the host for
+The cost matrices are built on the device (as two small matrix products instead of the reference's
+[K,K,N] broadcast -- same sums); only the [valid, ins_num] matrix crosses to the host for
 ``scipy.optimize.linear_sum_assignment`` (evaluator.py:45-46), one small D2H copy per call."""
 from __future__ import annotations
 
@@ -24,12 +25,15 @@ def hungarian(pred_ins, gt_ins, valid_ins_num, ins_num):
     """evaluator.py:41-74.  pred_ins [N,K] probabilities, gt_ins [N,K] one-hot (first ``valid_ins_num`` columns
     used).  Returns (cost_ce [K,K], cost_siou [K,K], row order, column order incl. unmatched columns)."""
     from scipy.optimize import linear_sum_assignment
-    p = pred_ins.t()[None, :, :]                        # [1, K_pred, N]
-    g = gt_ins.t()[:, None, :]                          # [K_gt, 1, N]
-    cost_ce = torch.mean(-g * torch.log(p + 1e-8) - (1 - g) * torch.log(1 - p + 1e-8), dim=-1)
-    tp = torch.sum(p * g, dim=-1)
-    fp = torch.sum(p, dim=-1) - tp
-    fn = torch.sum(g, dim=-1) - tp
+    # gt_ins is one-hot, so the reference's [K_gt, K_pred, N] broadcast (evaluator.py:55-63) collapses to two
+    # [K,N]x[N,K] products: sum_n g*log(p) + (1-g)*log(1-p) = g^T (log p - log(1-p)) + colsum(log(1-p)).
+    n = pred_ins.shape[0]
+    log_p, log_q = torch.log(pred_ins + 1e-8), torch.log(1 - pred_ins + 1e-8)
+    gt_t = gt_ins.t()
+    cost_ce = -(gt_t @ (log_p - log_q) + log_q.sum(0)[None, :]) / n
+    tp = gt_t @ pred_ins
+    fp = pred_ins.sum(0)[None, :] - tp
+    fn = gt_ins.sum(0)[:, None] - tp
     cost_siou = 1.0 - tp / (tp + fp + fn + 1e-6)
     with torch.no_grad():
         scores = (cost_ce + cost_siou)[:valid_ins_num].detach().cpu().numpy()

@@ -20,12 +20,16 @@ def get_rays(H, W, focal, c2w):
     return get_rays_k(H, W, K, c2w)
 
 
-def get_select_full(rgb, pose, K, ins_target, N_train):
-    """helpers.py:99-111: N_train distinct random pixels (numpy RNG, as the reference), their rays
-    (generated for those pixels only), colours and instance labels."""
+def get_select_full(rgb, pose, K, ins_target, N_train, numpy_rng=False):
+    """helpers.py:99-111: N_train distinct random pixels, their rays (generated for those pixels only, not the
+    whole frame), colours and instance labels.  The pixel draw runs on the device (``torch.randperm``); the
+    reference's ``np.random.choice(H*W, N, replace=False)`` permutes all H*W indices on the host every step
+    (3.7 ms at 640x480) -- pass ``numpy_rng=True`` to reproduce its RNG stream."""
     H, W, _ = rgb.shape
-    pick = np.random.choice(H * W, size=[N_train], replace=False)
-    idx = torch.from_numpy(pick).to(rgb.device)
+    if numpy_rng:
+        idx = torch.from_numpy(np.random.choice(H * W, size=[N_train], replace=False)).to(rgb.device)
+    else:
+        idx = torch.randperm(H * W, device=rgb.device)[:N_train]
     ro, rd = ops.rays_k(int(H), int(W), K, pose, 0, int(N_train), rgb.device, pix_idx=idx)
     batch_rays = torch.stack([ro, rd], 0)
     return rgb.reshape(-1, rgb.shape[-1])[idx], ins_target.reshape(-1)[idx], batch_rays

@@ -293,8 +293,27 @@ def main():
     ro, rd = R.helpers.get_rays_k(H, W, K, c2w)
     save("rays_k", K=K, c2w=c2w, rays_o=ro, rays_d=rd, H=np.int64(H), W=np.int64(W))
 
+    # ---- adjacent (8f-2): Hungarian-matched instance loss (+ gradient) ----------------------------------
+    import networks.evaluator as r_eval
+    g = torch.Generator().manual_seed(21)
+    for tag, kk, nn, n_lab in (("k32", 32, 257, 9), ("k93", 93, 130, 93)):
+        pred = torch.sigmoid(torch.randn(nn, kk, generator=g) * 2.0).requires_grad_(True)
+        lab = torch.randint(0, n_lab, (nn,), generator=g)
+        out = r_eval.ins_criterion(pred, lab, kk)
+        out[0].backward()
+        save(f"ins_criterion_{tag}", pred=pred.detach(), labels=lab, ins_num=np.int64(kk),
+             losses=torch.stack([o.reshape(()).float() for o in out]).detach(), grad=pred.grad)
+
     torch.rand = rq._orig
 
 
 if __name__ == "__main__":
+    # `gen_golden.py only <prefix>`: write just the fixtures whose name starts with <prefix> (adding one must not
+    # rewrite the committed others)
+    if len(sys.argv) > 2 and sys.argv[1] == "only":
+        _save, _prefix = save, sys.argv[2]
+
+        def save(name, **arrs):  # noqa: F811
+            if name.startswith(_prefix):
+                _save(name, **arrs)
     main()

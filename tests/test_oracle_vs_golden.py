@@ -2,6 +2,7 @@
 reference (oracle/gen_golden.py, torch 2.11 CPU).  Elementwise/scan stages are bit-exact;
 GEMM-bearing stages allow 2e-5 because sgemm blocking depends on the host's thread count."""
 import numpy as np
+import pytest
 import torch
 
 import dmnerf_oracle as orc
@@ -175,3 +176,22 @@ def test_c_restatement_vs_golden(golden, c_oracle):
         np.testing.assert_allclose(dep, g["depth"], atol=2e-5)
         np.testing.assert_allclose(w, g["weights"], atol=1e-6)
         np.testing.assert_allclose(ins, g["ins"], atol=2e-6)
+
+
+@pytest.mark.parametrize("tag", ["k32", "k93"])
+def test_host_ins_criterion_vs_golden(golden, tag):
+    """The host mirror of evaluator.ins_criterion (matrix-product form of the cost matrices, scipy Hungarian)
+    against values and gradients produced by the reference's own function (evaluator.py:19-74)."""
+    import importlib.util
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "dm_nerf_b200", "networks", "evaluator.py")
+    spec = importlib.util.spec_from_file_location("_host_evaluator", path)      # no package import: no .so needed
+    ev = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ev)
+    g = golden(f"ins_criterion_{tag}")
+    pred = torch.from_numpy(g["pred"]).requires_grad_(True)
+    out = ev.ins_criterion(pred, torch.from_numpy(g["labels"]), int(g["ins_num"]))
+    out[0].backward()
+    got = np.array([float(o.detach()) for o in out], dtype=np.float32)
+    np.testing.assert_allclose(got, g["losses"], rtol=2e-6, atol=2e-7)
+    np.testing.assert_allclose(pred.grad.numpy(), g["grad"], rtol=1e-4, atol=1e-8)
