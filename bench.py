@@ -31,6 +31,7 @@ sys.path.insert(0, ROOT)
 H, W, K_INS, SC, NIMP = 480, 640, 32, 64, 128
 NEAR, FAR = 4.0, 15.0
 N_RAYS = H * W
+CPU_SAMPLE_RAYS = 24576                          # ~10-20 s of host work for the cpu_baseline leg
 MACS_PER_POINT = 691840 + 128 * K_INS            # algorithmic, padding not counted
 FLOP_PER_RAY = 2 * MACS_PER_POINT * (SC + SC + NIMP)
 
@@ -96,10 +97,35 @@ def cpu_oracle_rays_per_s(torch, n_rays: int, repeats: int = 1):
     with torch.no_grad():
         for _ in range(repeats):
             t0 = time.perf_counter()
-            orc.dm_nerf(rays, pc, pf, zc, perturb=0.0, n_importance=NIMP)
+            for a in range(0, n_rays, 4096):                       # tester.py:62 chunking (N_test = 4096)
+                orc.dm_nerf(rays[:, a:a + 4096], pc, pf, zc[a:a + 4096], perturb=0.0, n_importance=NIMP)
             dt = time.perf_counter() - t0
             best = dt if best is None else min(best, dt)
     return n_rays / best, cores, best
+
+
+def cpu_oracle_train_rays_per_s(torch, n_rays: int):
+    """One training step of the oracle port on the host cores (forward, MSE + penalizer losses, backward)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import dmnerf_oracle as orc
+    torch.set_num_threads(os.cpu_count() or 1)
+    pc = {k: v.requires_grad_(True) for k, v in orc.init_params(K_INS, 1).items()}
+    pf = {k: v.requires_grad_(True) for k, v in orc.init_params(K_INS, 2).items()}
+    Kmat, c2w = synth_camera(torch, 0)
+    ro, rd = orc.get_rays_k(H, W, Kmat, c2w)
+    sel = torch.linspace(0, N_RAYS - 1, n_rays).long()
+    rays = torch.stack([ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel]], 0)
+    zc = orc.z_val_sample(n_rays, NEAR, FAR, SC)
+    tgt = torch.rand(n_rays, 3)
+    t0 = time.perf_counter()
+    o = orc.dm_nerf(rays, pc, pf, zc, perturb=1.0, n_importance=NIMP, t_rand=torch.rand(n_rays, SC),
+                    u=torch.rand(n_rays, NIMP))
+    loss = ((o["rgb_fine"] - tgt) ** 2).mean() + ((o["rgb_coarse"] - tgt) ** 2).mean()
+    loss = loss + orc.ins_penalizer(o["raw_coarse"], o["z_vals_coarse"], o["depth_coarse"], rays[1], 0.05, 0.05)
+    loss = loss + orc.ins_penalizer(o["raw_fine"], o["z_vals_fine"], o["depth_fine"], rays[1], 0.05, 0.05)
+    loss.backward()
+    dt = time.perf_counter() - t0
+    return n_rays / dt, dt
 
 
 def run_reference(args):
@@ -107,7 +133,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n = 2048
+    n = 8192
     times = []
     for i in range(args.warmup + args.steps):
         rps, cores, dt = cpu_oracle_rays_per_s(torch, n)
@@ -124,6 +150,54 @@ def run_reference(args):
         "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def train_leg(args, torch, dist, dev, rank, world):
+    """Training throughput (BASELINE.json configs[0] and configs[2]): full steps of dm_nerf_b200.train.TrainStep --
+    pixel draw, dm_nerf fwd, MSE + Hungarian instance loss + emptiness penalizer, backward, one all-reduce of the
+    flat gradient, Adam -- data-parallel over ray batches (each rank its own view and rays; weak scaling)."""
+    import numpy as np
+    import dmnerf_oracle as orc
+    from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
+    from dm_nerf_b200.train import TrainStep
+    pe, ve = get_embedder(10, 0)[0], get_embedder(4, 0)[0]
+    out = {}
+    for tag, n, k, near, far in (("C1_study_1024rays_K32", 1024, 32, 4.0, 15.0), ("C3_replica_4096rays_K93", 4096, 93, 0.0, 6.5)):
+        torch.manual_seed(3 + rank); np.random.seed(rank)
+        mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
+        mc.load_state_dict(orc.init_params(k, 1)); mf.load_state_dict(orc.init_params(k, 2))
+        mc, mf = mc.to(dev), mf.to(dev)
+        Kmat, c2w = synth_camera(torch, rank)
+        pose = c2w[:3, :4].to(dev)
+        img = torch.rand(H, W, 3, device=dev)
+        lab = ((torch.arange(H, device=dev)[:, None] // 60) * 8 + (torch.arange(W, device=dev)[None] // 80)) % k
+        targs = SimpleNamespace(N_train=n, near=near, far=far, N_samples=SC, N_importance=NIMP, perturb=1.0, ins_num=k,
+                                tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+        ts = TrainStep(pe, ve, mc, mf, Kmat, targs, penalize=True)
+        for _ in range(max(3, args.warmup)):
+            ts.step(img, pose, lab)
+        steps = max(10, args.steps)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            losses = ts.step(img, pose, lab)
+        b.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([a.elapsed_time(b) / steps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms)
+        macs = 691840 + 128 * k
+        flop_per_ray = 2.0 * (3 * macs - 101248) * (SC + SC + NIMP)            # SURVEY 8(d): fwd + dgrad + wgrad
+        out[tag] = {"value": n * world / (ms / 1000), "unit": "rays/s", "ms_per_step": ms, "rays_per_step_per_gpu": n,
+                    "steps": steps, "loss": float(losses["total"]),
+                    "algorithmic_tflops": flop_per_ray * n * world / (ms / 1000) / 1e12}
+    return {"metric": "rays/sec train (64+128 samples/ray, fwd+bwd+Adam, penalizer on)", "scaling": "weak",
+            "parallelism": f"data-parallel ray batches x{world}, one all-reduce of the flat gradient per step",
+            "configs": out}
 
 
 def run_gpu(args):
@@ -206,6 +280,9 @@ def run_gpu(args):
     e2e_step(); sync()
     ms_e2e = timed(e2e_step, args.steps)
     clocks = sampler.summary()
+    train = None
+    if not args.no_train:
+        train = train_leg(args, torch, dist, dev, rank, world)
 
     peaks = {}
     try:
@@ -231,9 +308,15 @@ def run_gpu(args):
     if rank == 0:
         cpu = None
         try:
-            rps, cores, secs = cpu_oracle_rays_per_s(torch, 2048)
+            rps, cores, secs = cpu_oracle_rays_per_s(torch, CPU_SAMPLE_RAYS)
             cpu = {"value": rps, "unit": "rays/s", "cores": cores, "kind": "port",
-                   "sample": f"2048 of the frame's 307200 rays, one pass ({secs:.1f} s), oracle port torch CPU fp32"}
+                   "sample": f"{CPU_SAMPLE_RAYS} of the frame's 307200 rays in tester.py-style 4096-ray chunks, one pass "
+                             f"({secs:.1f} s), oracle port torch CPU fp32"}
+            if train is not None:
+                t_rps, t_secs = cpu_oracle_train_rays_per_s(torch, 1024)
+                train["cpu_baseline"] = {"value": t_rps, "unit": "rays/s", "cores": cores, "kind": "port",
+                                         "sample": f"one C1 step (1024 rays, K=32: dm_nerf + MSE + penalizer + backward, "
+                                                   f"{t_secs:.1f} s), oracle port torch CPU fp32"}
         except Exception as e:  # pragma: no cover
             cpu = {"value": None, "error": str(e)}
         total_rays = N_RAYS * world
@@ -251,7 +334,7 @@ def run_gpu(args):
             "e2e": {"value": total_rays / (ms_e2e / 1000), "unit": "rays/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "stage_ms_per_step": stage_ms,
+            "stage_ms_per_step": stage_ms, "train": train,
         }))
     if world > 1:
         dist.destroy_process_group()
@@ -265,6 +348,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default=os.environ.get("DMNERF_BENCH_MODE", "auto"), choices=["auto", "bf16", "fp32"])
     ap.add_argument("--chunk", type=int, default=32768)
+    ap.add_argument("--no-train", action="store_true", help="skip the training-throughput leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -1,0 +1,63 @@
+"""One training step of the reference's loop body (train_dmsr.py:24-72 / train_replica.py / train_scannet.py) on
+the CUDA ray path, data-parallel over ray batches: pixel draw -> rays -> dm_nerf (coarse + fine) ->
+MSE + Hungarian instance loss + emptiness penalizer -> backward -> ONE all-reduce of the flat gradient -> Adam
+-> lr decay.  Host orchestration only: every kernel on the ray path is libdmnerf_b200.so's."""
+from __future__ import annotations
+
+from types import SimpleNamespace
+from typing import Dict, Optional
+
+import torch
+
+from . import parallel
+from .networks.evaluator import img2mse, ins_criterion
+from .networks.helpers import get_select_full, z_val_sample
+from .networks.penalizer import ins_penalizer
+from .networks.render import dm_nerf
+
+
+class TrainStep:
+    """``step(image [H,W,3], pose [3,4], labels [H,W]) -> dict of detached loss scalars``.
+
+    args: duck-typed like the reference's (N_train, near, far, N_samples, N_importance, perturb, ins_num, tolerance,
+    deta_w, lrate, lrate_decay); ``penalize`` adds the emptiness loss (train_dmsr.py:53-60)."""
+
+    def __init__(self, position_embedder, view_embedder, model_coarse, model_fine, K, args, penalize: bool = True,
+                 optimizer: Optional[torch.optim.Optimizer] = None):
+        self.pe, self.ve, self.mc, self.mf, self.K = position_embedder, view_embedder, model_coarse, model_fine, K
+        self.args = SimpleNamespace(**vars(args))
+        self.args.is_train, self.args.N_ins = True, None
+        self.penalize = penalize
+        self.params = list(model_coarse.parameters()) + list(model_fine.parameters())
+        self.opt = optimizer or torch.optim.Adam(self.params, lr=args.lrate, betas=(0.9, 0.999))
+        self.z_coarse = z_val_sample(args.N_train, args.near, args.far, args.N_samples)     # train_dmsr.py:22
+        self.flat = None
+        self.iteration = 0
+
+    def step(self, image, pose, labels) -> Dict[str, torch.Tensor]:
+        a = self.args
+        target_c, target_i, rays = get_select_full(image, pose, self.K, labels, a.N_train)
+        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a)
+        rgb_loss = img2mse(info["rgb_coarse"], target_c) + img2mse(info["rgb_fine"], target_c)
+        ins_loss = ins_criterion(info["ins_coarse"], target_i, a.ins_num)[0] + \
+            ins_criterion(info["ins_fine"], target_i, a.ins_num)[0]
+        total = rgb_loss + ins_loss
+        emptiness = None
+        if self.penalize:
+            emptiness = ins_penalizer(info["raw_coarse"], info["z_vals_coarse"], info["depth_coarse"], rays[1], a) + \
+                ins_penalizer(info["raw_fine"], info["z_vals_fine"], info["depth_fine"], rays[1], a)
+            total = total + emptiness
+        self.opt.zero_grad(set_to_none=False)
+        total.backward()
+        if self.flat is None:
+            self.flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=self.params[0].device)
+        parallel.allreduce_grads(self.params, self.flat)
+        self.opt.step()
+        lr = a.lrate * (0.1 ** (self.iteration / (a.lrate_decay * 1000)))                  # train_dmsr.py:68-72
+        for group in self.opt.param_groups:
+            group["lr"] = lr
+        self.iteration += 1
+        out = {"total": total.detach(), "rgb": rgb_loss.detach(), "ins": ins_loss.detach()}
+        if emptiness is not None:
+            out["emptiness"] = emptiness.detach()
+        return out
