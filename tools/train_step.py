@@ -62,6 +62,8 @@ def main():
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / steps
     print(f"train step N={n} K={k} mode={ops.get_mode()}: {dt * 1e3:.2f} ms/step -> {n / dt:.0f} rays/s; loss {float(l0.detach()):.4f} -> {float(l.detach()):.4f}")
+    if os.environ.get("DMNERF_NO_TORCH_PROFILER"):
+        return
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         step(); torch.cuda.synchronize()
