@@ -1,0 +1,72 @@
+// chunk_pipe.cuh -- per-warp bulk-copy pipeline for the warp-per-ray kernels (compositing, penalizer).
+//
+// A ray's raw row is S*C contiguous floats.  Each warp walks its rays in 32-sample chunks (32*C floats =
+// 128*C bytes, a multiple of 16) and keeps STAGES chunks in flight with 1-D bulk async copies (TMA engine,
+// UBLKCP) into its private shared-memory ring, one mbarrier per stage.  Producer and consumer are the same
+// warp, so releasing a stage is just the __syncwarp() that ends the chunk's reads; lane 0 then re-arms it.
+// This replaces scalar __ldg staging (one chunk in flight per warp) and is what lifts these kernels from ~30 %
+// to the HBM roofline: bytes in flight per SM = warps * STAGES * 128*C.
+// Requirements (checked by the launchers): base pointer 16-byte aligned and S*C % 4 == 0.
+#pragma once
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace dmnerf {
+
+template <int STAGES>
+struct ChunkPipe {
+    const float* base;        // raw [n, S, C]
+    uint32_t tile0;           // smem address of this warp's ring (STAGES * chunk_bytes)
+    uint32_t bar0;            // smem address of this warp's STAGES mbarriers
+    float* tile_ptr;          // generic pointer to the ring
+    int64_t ray0, ray_stride, total;
+    int S, C, nchunk, chunk_floats, lane;
+    int64_t issued, consumed;
+    bool reverse;             // walk a ray's chunks last-to-first (backward scans)
+
+    __device__ __forceinline__ void init(const float* raw, float* ring, uint64_t* bars, int64_t first_ray, int64_t stride,
+                                         int64_t n, int S_, int C_, int lane_, bool reverse_ = false) {
+        base = raw; tile_ptr = ring; tile0 = ptx::smem_u32(ring); bar0 = ptx::smem_u32(bars);
+        ray0 = first_ray; ray_stride = stride; S = S_; C = C_; lane = lane_; reverse = reverse_;
+        nchunk = (S + 31) >> 5;
+        chunk_floats = 32 * C;
+        const int64_t my_rays = first_ray < n ? (n - first_ray + stride - 1) / stride : 0;
+        total = my_rays * nchunk;
+        issued = consumed = 0;
+        if (lane == 0) {
+            for (int s = 0; s < STAGES; ++s) ptx::mbar_init(bar0 + 8 * s, 1);
+            ptx::fence_barrier_init();
+        }
+        __syncwarp();
+        for (int s = 0; s < STAGES - 1; ++s) issue();
+    }
+    __device__ __forceinline__ int chunk_of(int64_t k) const {
+        const int c = static_cast<int>(k % nchunk);
+        return reverse ? nchunk - 1 - c : c;
+    }
+    __device__ __forceinline__ void issue() {
+        if (issued < total && lane == 0) {
+            const int64_t ray = ray0 + (issued / nchunk) * ray_stride;
+            const int c0 = chunk_of(issued) * 32;
+            const int cnt = min(32, S - c0);
+            const uint32_t bytes = static_cast<uint32_t>(cnt) * C * 4;
+            const int st = static_cast<int>(issued % STAGES);
+            ptx::mbar_arrive_expect_tx(bar0 + 8 * st, bytes);
+            ptx::bulk_g2s(tile0 + st * chunk_floats * 4, base + (ray * S + c0) * static_cast<int64_t>(C), bytes, bar0 + 8 * st);
+        }
+        ++issued;
+    }
+    // Blocks until the next chunk has landed; returns its tile.  ray / c0 describe it.
+    __device__ __forceinline__ float* acquire(int64_t& ray, int& c0) {
+        issue();                                            // refill the stage released by the previous chunk
+        const int st = static_cast<int>(consumed % STAGES);
+        ptx::mbar_wait(bar0 + 8 * st, static_cast<uint32_t>((consumed / STAGES) & 1));
+        ray = ray0 + (consumed / nchunk) * ray_stride;
+        c0 = chunk_of(consumed) * 32;
+        ++consumed;
+        return tile_ptr + st * chunk_floats;
+    }
+    __device__ __forceinline__ bool done() const { return consumed >= total; }
+};
+
+}  // namespace dmnerf

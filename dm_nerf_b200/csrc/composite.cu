@@ -7,7 +7,7 @@
 // Data movement: each 32-sample chunk of raw (32*C contiguous floats) is staged once into shared
 // memory with fully coalesced loads; lanes then act as samples (scan) and as channels (logit sums).
 // HBM traffic = the algorithmic bytes (raw read once); roofline: HBM.
-#include "common.cuh"
+#include "chunk_pipe.cuh"
 
 namespace dmnerf {
 
@@ -117,6 +117,103 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     for (int q = 0; q < 4; ++q) {
         const int j = lane + 32 * q;
         if (j < Lout) ins[ray * Lout + j] = (flags & DMNERF_COMP_RAW_INS) ? acc[q] : sigmoidf_ref(acc[q]);
+    }
+}
+
+// Forward, bulk-copy staged (the default whenever raw is 16-byte aligned and S*C % 4 == 0): persistent warps,
+// each walking rays gw, gw+W, ... with kCompStages chunks in flight (chunk_pipe.cuh).  Same arithmetic and
+// summation order per ray as composite_fwd_kernel.  Logit sums: lanes are channels for full 32-channel passes;
+// a remainder of <= 4 channels (K=32: the single "empty" class) is summed sample-parallel instead of spending a
+// whole pass on one lane.
+constexpr int kCompStages = 3;
+constexpr int kCompBulkWarps = 4;
+
+__global__ void __launch_bounds__(kCompBulkWarps * 32)
+composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
+                          int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,
+                          float* __restrict__ weights, float* __restrict__ ins) {
+    extern __shared__ __align__(128) float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int per_warp = kCompStages * 32 * C + 32;
+    float* ring = smem + warp * per_warp;
+    float* wbuf = ring + kCompStages * 32 * C;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp) + warp * kCompStages;
+    ChunkPipe<kCompStages> pipe;
+    pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
+              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane);
+    const int L = C - 4;
+    const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
+    const int rem = (L & 31) <= 4 ? (L & 31) : 0;          // channels summed sample-parallel
+    const int Lp = L - rem;                                // channels summed channel-parallel (lanes = channels)
+
+    float carry = 1.0f, a_r = 0.f, a_g = 0.f, a_b = 0.f, a_d = 0.f, norm = 0.f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f}, racc[4] = {0.f, 0.f, 0.f, 0.f};
+    while (!pipe.done()) {
+        int64_t ray; int c0;
+        const float* tile = pipe.acquire(ray, c0);
+        const float* zrow = z + ray * S;
+        if (c0 == 0) {
+            const float dx = rays_d[ray * 3 + 0], dy = rays_d[ray * 3 + 1], dz = rays_d[ray * 3 + 2];
+            norm = sqrtf(dx * dx + dy * dy + dz * dz);
+            carry = 1.0f; a_r = a_g = a_b = a_d = 0.f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[q] = racc[q] = 0.f;
+        }
+        const int cnt = min(32, S - c0);
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        float zc = 0.f, dist = 0.f, sigma = 0.f;
+        if (valid) {
+            zc = zrow[s];
+            dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            sigma = tile[lane * C + 3];
+        }
+        float alpha, trans, w;
+        scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
+        if (valid) {
+            if (weights) weights[ray * S + s] = w;
+            a_r += w * sigmoidf_ref(tile[lane * C + 0]);
+            a_g += w * sigmoidf_ref(tile[lane * C + 1]);
+            a_b += w * sigmoidf_ref(tile[lane * C + 2]);
+            a_d += w * zc;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q < rem) racc[q] += w * tile[lane * C + 4 + Lp + q];
+        }
+        wbuf[lane] = w;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            if (j < Lp) {
+                float a = acc[q];
+                const float* col = tile + 4 + j;
+#pragma unroll 8
+                for (int r = 0; r < cnt; ++r) a += wbuf[r] * col[r * C];
+                acc[q] = a;
+            }
+        }
+        if (c0 + 32 >= S) {                                  // last chunk of this ray: write the outputs
+            a_r = warp_sum(a_r); a_g = warp_sum(a_g); a_b = warp_sum(a_b); a_d = warp_sum(a_d);
+            if (lane == 0) {
+                rgb[ray * 3 + 0] = a_r; rgb[ray * 3 + 1] = a_g; rgb[ray * 3 + 2] = a_b;
+                depth[ray] = a_d;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int j = lane + 32 * q;
+                if (j < Lp && j < Lout) ins[ray * Lout + j] = (flags & DMNERF_COMP_RAW_INS) ? acc[q] : sigmoidf_ref(acc[q]);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (q < rem) {
+                    const float v = warp_sum(racc[q]);
+                    if (lane == 0 && Lp + q < Lout)
+                        ins[ray * Lout + Lp + q] = (flags & DMNERF_COMP_RAW_INS) ? v : sigmoidf_ref(v);
+                }
+            }
+        }
+        __syncwarp();                                        // all reads of this tile done -> stage may be refilled
     }
 }
 
@@ -282,6 +379,24 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
     DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_fwd: n_samples %d outside [1,1024]", s);
     DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "composite_fwd: channels %d outside [6,128]", c);
     if (n == 0) return DMNERF_OK;
+    if ((reinterpret_cast<uintptr_t>(raw) & 15) == 0 && (static_cast<int64_t>(s) * c) % 4 == 0) {
+        static int sm_count = 0;
+        if (sm_count == 0) {
+            int dev = 0;
+            DM_CUDA(cudaGetDevice(&dev));
+            DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+        }
+        const size_t smem = static_cast<size_t>(kCompBulkWarps) * ((kCompStages * 32 * c + 32) * sizeof(float) + kCompStages * 8);
+        int per_sm = static_cast<int>((220 * 1024) / (smem + 1024));
+        per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+        DM_CUDA(cudaFuncSetAttribute(composite_fwd_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int64_t want = (n + kCompBulkWarps - 1) / kCompBulkWarps;
+        const int64_t cap = static_cast<int64_t>(sm_count) * per_sm;
+        composite_fwd_bulk_kernel<<<static_cast<unsigned>(want < cap ? want : cap), kCompBulkWarps * 32, smem, as_stream(stream)>>>(
+            raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins);
+        DM_LAUNCH_CHECK("composite_fwd_bulk_kernel");
+        return DMNERF_OK;
+    }
     const int CP = c | 1;
     const size_t smem = static_cast<size_t>(kCompWarps) * (32 * CP + 32) * sizeof(float);
     DM_CUDA(cudaFuncSetAttribute(composite_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -31,8 +31,6 @@ static int g_tc_debug_flags = 0;   // bit0: swap LBO/SBO in the smem descriptors
 namespace tc {
 
 // ---- pack --------------------------------------------------------------------------------------------
-struct Params { const float* p[kNumParams]; };
-
 // composed weights: Wc[i][k] = sum_j W1[i][j] * W0[j][k]  (W1 = *_feature_linears.0[:, :256], W0 = *_feature_linear)
 // bc[i] = sum_j W1[i][j]*b0[j] + b1[i].  scratch: [0,32768) rgb, [32768,65536) ins, then bc[256].
 __global__ void compose_kernel(Params pr, float* __restrict__ scratch) {
@@ -55,23 +53,6 @@ __global__ void compose_kernel(Params pr, float* __restrict__ scratch) {
         for (int j = 0; j < 256; ++j) a = fmaf(w1[i * ld1 + j], b0[j], a);
         scratch[idx] = a + b1[i];
     }
-}
-
-__device__ inline float logical_weight(const Params& pr, const float* scratch, int l, int n, int k, int ins_num) {
-    if (l == 0) return k < 63 ? pr.p[0][n * 63 + k] : 0.f;
-    if (l == 5) return k < 319 ? pr.p[10][n * 319 + k] : 0.f;
-    if (l <= 7) return pr.p[2 * l][n * 256 + k];
-    if (l == 8) {
-        if (n < 128) {
-            if (k < 256) return scratch[n * 256 + k];
-            return k < 283 ? pr.p[P_RGB0_W][n * 283 + k] : 0.f;
-        }
-        return k < 256 ? scratch[32768 + (n - 128) * 256 + k] : 0.f;
-    }
-    // l == 9: block-diagonal heads.  rows 0..2 rgb (k<128), row 3 density (filled in the epilogue), rows 4.. ins
-    if (n < 3) return k < 128 ? pr.p[P_RGBL_W][n * 128 + k] : 0.f;
-    if (n >= 4 && n < 5 + ins_num) return k >= 128 ? pr.p[P_INSL_W][(n - 4) * 128 + (k - 128)] : 0.f;
-    return 0.f;
 }
 
 // one thread per bf16 element of the chunk stream: layer l, chunk c, k-group g, row n, element e
@@ -156,50 +137,6 @@ __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ imag
 }
 
 
-// Embedding of a 3-vector into EXT k-groups [KG0, KG1): channel c = [x | f: sin(3) cos(3)], 8 channels per
-// k-group.  The first needed octave uses full-range sincosf on x*2^f (exact scaling); higher octaves follow by
-// angle doubling (error << bf16 resolution).  Channels outside the range are dead code after unrolling.
-template <int F, int KG0, int KG1>
-__device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3], uint8_t* gst = nullptr,
-                                             int gkg0 = 0) {
-    constexpr int CH = 3 + 6 * F;
-    constexpr int C0 = KG0 * 8, C1 = KG1 * 8;
-    constexpr int F0 = C0 < 3 ? 0 : (C0 - 3) / 6;           // first octave that touches [C0, C1)
-    float ch[(KG1 - KG0) * 8];
-#pragma unroll
-    for (int i = 0; i < (KG1 - KG0) * 8; ++i) ch[i] = 0.f;
-    float s[3], c[3];
-#pragma unroll
-    for (int d = 0; d < 3; ++d) {
-        if (C0 == 0) ch[d] = x[d];
-        sincosf(x[d] * static_cast<float>(1 << F0), &s[d], &c[d]);
-    }
-#pragma unroll
-    for (int f = F0; f < F; ++f) {
-#pragma unroll
-        for (int d = 0; d < 3; ++d) {
-            const int cs = 3 + 6 * f + d, cc = cs + 3;
-            if (cs >= C0 && cs < C1 && cs < CH) ch[cs - C0] = s[d];
-            if (cc >= C0 && cc < C1 && cc < CH) ch[cc - C0] = c[d];
-            const float s2 = 2.f * s[d] * c[d];
-            const float c2 = (c[d] - s[d]) * (c[d] + s[d]);
-            s[d] = s2; c[d] = c2;
-        }
-    }
-#pragma unroll
-    for (int g = KG0; g < KG1; ++g) store_kg(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false, gst, gkg0 + g);
-}
-
-__device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kg0,
-                                           int kg1, uint8_t* gst = nullptr, int gkg0 = 0) {
-    for (int g = kg0; g < kg1; ++g) {
-        float v[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = (src && g * 8 + e < count) ? __ldg(src + g * 8 + e) : 0.f;
-        store_kg(a_base, kExtKg + g, row, v, false, gst, gkg0 + g);
-    }
-}
-
 // ---- the kernel -------------------------------------------------------------------------------------------------
 // kStash (training): every A operand the backward needs (embeddings, h0..h7, [rgb_hid|ins_hid]) is mirrored
 // to the per-tile bf16 stash (mlp_layout.cuh) by the same 16-byte stores that build the smem operand.
@@ -218,7 +155,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
-        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 2 * kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
+        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 1); ptx::mbar_init(bars.acc_ready(t), 1); }
         ptx::fence_barrier_init();
     }
     if (warp == kMmaWarp) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
@@ -300,6 +237,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
         const uint32_t t_base = tmem + t * 256 + (static_cast<uint32_t>(q * 32) << 16);
         float* stage_out = reinterpret_cast<float*>(smem + kSmA + t * kABytes);
         float* dens_part = reinterpret_cast<float*>(smem + kSmDens) + t * kTile;
+        const bool leader = (warp & 7) == 0 && lane == 0;
         uint32_t acc_par = 0;
         for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
             const int64_t tile0 = pair * kPair + t * kTile;
@@ -329,11 +267,11 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             }
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
-            ptx::mbar_arrive(bars.a_ready(t));
+            tile_arrive(bars.a_ready(t), t, leader);
 
             float dens = 0.f;
             for (int l = 0; l < kLayers - 1; ++l) {
-                ptx::mbar_wait(bars.acc_ready(t), acc_par);
+                tile_wait(bars.acc_ready(t), acc_par, t, leader);
                 acc_par ^= 1;
                 ptx::tc_fence_after();
                 const float* bias = s_bias + l * 256;
@@ -369,10 +307,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 }
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
-                ptx::mbar_arrive(bars.a_ready(t));
+                tile_arrive(bars.a_ready(t), t, leader);
             }
             // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (half 0) ----
-            ptx::mbar_wait(bars.acc_ready(t), acc_par);
+            tile_wait(bars.acc_ready(t), acc_par, t, leader);
             acc_par ^= 1;
             ptx::tc_fence_after();
             if (half == 0) {
@@ -470,7 +408,13 @@ umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, i
 
 }  // namespace tc
 
+int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
+    // debug bit2 selects the pipelined variant (mlp_tc2.cu).  It is correct (same parity tests) but not faster:
+    // its N=128 cells re-read the A operand twice, which makes the SS-mode MMAs shared-memory-bandwidth bound
+    // once the epilogue's stores overlap them (measured 7.06 ms vs 6.92 ms per 32768x192 points); see DESIGN.md.
+    if (g_tc_debug_flags & 4) return launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st);
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -498,6 +442,9 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
 
 int tc_debug_flags() { return g_tc_debug_flags; }
 
+namespace tc2 { int pack_v2(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
+int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+
 int64_t bf16_image_bytes(int ins_num) { return tc::make_image(ins_num).total_bytes; }
 
 int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st) {
@@ -514,7 +461,7 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     tc::pack_dgrad_kernel<<<static_cast<unsigned>((dg_elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_f32_kernel<<<(tc::kF32Floats + 255) / 256, 256, 0, st>>>(pr, im, image);
     DM_LAUNCH_CHECK("pack_bf16");
-    return DMNERF_OK;
+    return tc2::pack_v2(params, ins_num, packed, st);
 }
 
 }  // namespace dmnerf
@@ -535,5 +482,113 @@ extern "C" int dmnerf_selftest_umma(const float* a, const float* b, int n, int k
     DM_CUDA(cudaFuncSetAttribute(tc::umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     tc::umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(a, b, n, k, d, g_tc_debug_flags);
     DM_LAUNCH_CHECK("umma_selftest_kernel");
+    return DMNERF_OK;
+}
+
+// ---- micro-benchmark: TMEM -> register read throughput (tcgen05.ld 32x32b.x32), `warps` warps (multiple of 4)
+// each reading its lane quarter of all 512 columns `iters` times.  out[0] = cycles, out[1] = bytes read per CTA.
+namespace dmnerf { namespace tc {
+__global__ void __launch_bounds__(512, 1)
+tmem_read_bw_kernel(int iters, int batched, long long* __restrict__ out) {
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(&slot), 512);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = slot;
+    const uint32_t base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    const int nw = blockDim.x >> 5, groups = nw >> 2, grp = warp >> 2;
+    const int c_lo = 512 / groups * grp, c_hi = c_lo + 512 / groups;
+    uint32_t sink = 0;
+    __syncthreads();
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+        if (batched) {
+            for (int c = c_lo; c < c_hi; c += 64) {
+                uint32_t r0[32], r1[32];
+                ptx::tmem_ld32(base + c, r0);
+                ptx::tmem_ld32(base + c + 32, r1);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e) sink ^= r0[e] ^ r1[e];
+            }
+        } else {
+            for (int c = c_lo; c < c_hi; c += 32) {
+                uint32_t r[32];
+                ptx::tmem_ld32(base + c, r);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e) sink ^= r[e];
+            }
+        }
+    }
+    __syncthreads();
+    const long long t1 = clock64();
+    if (threadIdx.x == 0 && blockIdx.x == 0) { out[0] = t1 - t0; out[1] = static_cast<long long>(iters) * 512 * 128 * 4; }
+    if (sink == 0x12345678u) out[2] = sink;
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 512); }
+}
+}}  // namespace dmnerf::tc
+
+extern "C" int dmnerf_selftest_tmem_read_bw(int warps, int iters, int batched, long long* out, void* stream) {
+    DM_REQUIRE(out && warps >= 4 && warps <= 16 && warps % 4 == 0, DMNERF_EINVAL, "selftest_tmem_read_bw: warps must be 4, 8, 12 or 16");
+    dmnerf::tc::tmem_read_bw_kernel<<<1, warps * 32, 0, as_stream(stream)>>>(iters, batched, out);
+    DM_LAUNCH_CHECK("tmem_read_bw_kernel");
+    return DMNERF_OK;
+}
+
+// ---- micro-benchmark: back-to-back tcgen05.mma issue rate for M=128, N=n, K=16 (bf16), one CTA.
+// out[0] = cycles for `count` MMAs (committed and waited for).
+namespace dmnerf { namespace tc {
+__global__ void __launch_bounds__(128, 1)
+umma_rate_kernel(int n, int count, long long* __restrict__ out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sm0 = ptx::smem_u32(smem);
+    const int warp = threadIdx.x >> 5;
+    const uint32_t a_base = sm0, b_base = sm0 + 65536, bar = sm0 + 65536 + 131072;
+    volatile uint32_t* slot = reinterpret_cast<volatile uint32_t*>(smem + 65536 + 131072 + 8);
+    for (int i = threadIdx.x; i < (65536 + 131072) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (threadIdx.x == 0) { ptx::mbar_init(bar, 1); ptx::fence_barrier_init(); }
+    if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(slot)), 512);
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *slot;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = ptx::idesc_bf16(128, n);
+        // descriptors precomputed and the issue loop unrolled: measures the tensor pipe, not this thread's
+        // instruction latency (a naive loop with descriptor construction issues only one MMA per ~72 cycles)
+        uint64_t ad[16], bd[16];
+#pragma unroll
+        for (int ks = 0; ks < 16; ++ks) {
+            ad[ks] = ptx::smem_desc(a_base + ks * 2 * kKgBytes, kKgBytes, 128);
+            bd[ks] = ptx::smem_desc(b_base + ks * 2 * (n * 16), n * 16, 128);
+        }
+        const long long t0 = clock64();
+        for (int i = 0; i < count; i += 16) {
+            const uint32_t d = tmem + ((i >> 4) & 1) * 256;
+#pragma unroll
+            for (int ks = 0; ks < 16; ++ks) ptx::umma_bf16(d, ad[ks], bd[ks], idesc, ks != 0);
+        }
+        ptx::umma_commit(bar);
+        ptx::mbar_wait(bar, 0);
+        out[0] = clock64() - t0;
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 512); }
+}
+}}  // namespace dmnerf::tc
+
+extern "C" int dmnerf_selftest_umma_rate(int n, int count, long long* out, void* stream) {
+    DM_REQUIRE(out && n >= 16 && n <= 256 && n % 16 == 0 && count > 0, DMNERF_EINVAL, "selftest_umma_rate: bad arguments");
+    const int smem = 65536 + 131072 + 64;
+    DM_CUDA(cudaFuncSetAttribute(dmnerf::tc::umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    dmnerf::tc::umma_rate_kernel<<<1, 128, smem, as_stream(stream)>>>(n, count, out);
+    DM_LAUNCH_CHECK("umma_rate_kernel");
     return DMNERF_OK;
 }

@@ -4,6 +4,7 @@
 #include "mlp_layout.cuh"
 #include "tc_ptx.cuh"
 #include <cuda_bf16.h>
+#include "mlp_tc2.cuh"
 
 namespace dmnerf {
 namespace tc {
@@ -43,6 +44,8 @@ constexpr int kDgLayers = 9;
 constexpr int kF32Rgbf = 0, kF32Insf = 65536, kF32Rgb0 = 131072, kF32Ins0 = 131072 + 32768,
               kF32BRgbf = 131072 + 65536, kF32BInsf = kF32BRgbf + 256, kF32Floats = kF32BInsf + 256;
 
+static_assert(tc2::kExtKg == kExtKg, "mlp_tc2.cuh out of sync");
+
 struct Image {
     int64_t chunk_off[kLayers];   // byte offset of the layer's first chunk
     int n[kLayers];               // MMA N of the layer
@@ -51,6 +54,9 @@ struct Image {
     int64_t dg_off[kDgLayers];    // dgrad chunk streams ([k-group][256 rows][8 bf16] per 32-wide K chunk)
     int dg_k[kDgLayers];
     int64_t f32_off;              // kF32Floats fp32 copies (rgb/ins feature layers) for unpack_grads
+    int64_t v2_off;               // chunk stream of the pipelined forward (mlp_tc2.cuh), in issue order
+    int64_t v2_sched_off;         // tc2::Chunk[v2_chunks]
+    int v2_chunks;
     int64_t total_bytes;
     int npad, ins_num, kp9;       // kp9 = C rounded up to 32: K of the first dgrad layer
 };
@@ -74,9 +80,35 @@ __host__ __device__ inline Image make_image(int ins_num) {
         off += static_cast<int64_t>(im.dg_k[d]) * 256 * 2;
     }
     im.f32_off = off;        off += static_cast<int64_t>(kF32Floats) * 4;
+    uint32_t v2_bytes = 0;
+    im.v2_chunks = tc2::build_schedule(im.npad, nullptr, &v2_bytes);
+    im.v2_off = off;         off += v2_bytes;
+    im.v2_sched_off = off;   off += static_cast<int64_t>(tc2::kMaxChunks) * sizeof(tc2::Chunk);
     im.total_bytes = off;
     return im;
 }
+
+// ---- pack helpers ----
+struct Params { const float* p[kNumParams]; };
+
+
+__device__ inline float logical_weight(const Params& pr, const float* scratch, int l, int n, int k, int ins_num) {
+    if (l == 0) return k < 63 ? pr.p[0][n * 63 + k] : 0.f;
+    if (l == 5) return k < 319 ? pr.p[10][n * 319 + k] : 0.f;
+    if (l <= 7) return pr.p[2 * l][n * 256 + k];
+    if (l == 8) {
+        if (n < 128) {
+            if (k < 256) return scratch[n * 256 + k];
+            return k < 283 ? pr.p[P_RGB0_W][n * 283 + k] : 0.f;
+        }
+        return k < 256 ? scratch[32768 + (n - 128) * 256 + k] : 0.f;
+    }
+    // l == 9: block-diagonal heads.  rows 0..2 rgb (k<128), row 3 density (filled in the epilogue), rows 4.. ins
+    if (n < 3) return k < 128 ? pr.p[P_RGBL_W][n * 128 + k] : 0.f;
+    if (n >= 4 && n < 5 + ins_num) return k >= 128 ? pr.p[P_INSL_W][(n - 4) * 128 + (k - 128)] : 0.f;
+    return 0.f;
+}
+
 
 // ---- device helpers ---------------------------------------------------------------------------------------
 // mbarrier addresses (8 B each) inside the barrier block
@@ -87,6 +119,19 @@ struct Bars {
     __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kStages + t); }
     __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kStages + 2 + t); }
 };
+
+// Handoffs between a tile's 256 epilogue threads and the MMA issuer.  Only ONE thread per tile touches the
+// mbarrier: polling and arriving are shared-memory-pipe operations, and 16 warps polling (or 256 arrivals per
+// layer) compete with the working warps' LDS/STS/LDTM.  The other threads block on a hardware named barrier
+// (ids 3 + tile), which costs no issue slots.
+__device__ __forceinline__ void tile_wait(uint32_t bar, uint32_t parity, int t, bool leader) {
+    if (leader) ptx::mbar_wait(bar, parity);
+    ptx::named_bar_sync(3 + t, 2 * kTile);
+}
+__device__ __forceinline__ void tile_arrive(uint32_t bar, int t, bool leader) {
+    ptx::named_bar_sync(3 + t, 2 * kTile);
+    if (leader) ptx::mbar_arrive(bar);
+}
 
 __device__ __forceinline__ uint64_t op_desc(uint32_t addr, uint32_t lbo, uint32_t sbo, int swap) {
     return swap ? ptx::smem_desc(addr, sbo, lbo) : ptx::smem_desc(addr, lbo, sbo);
@@ -102,6 +147,51 @@ __device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const
     ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, w0, w1, w2, w3);
     if (gst) *reinterpret_cast<uint4*>(gst + gkg * kStKgBytes) = make_uint4(w0, w1, w2, w3);
 }
+
+// Embedding of a 3-vector into EXT k-groups [KG0, KG1): channel c = [x | f: sin(3) cos(3)], 8 channels per
+// k-group.  The first needed octave uses full-range sincosf on x*2^f (exact scaling); higher octaves follow by
+// angle doubling (error << bf16 resolution).  Channels outside the range are dead code after unrolling.
+template <int F, int KG0, int KG1>
+__device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3], uint8_t* gst = nullptr,
+                                             int gkg0 = 0) {
+    constexpr int CH = 3 + 6 * F;
+    constexpr int C0 = KG0 * 8, C1 = KG1 * 8;
+    constexpr int F0 = C0 < 3 ? 0 : (C0 - 3) / 6;           // first octave that touches [C0, C1)
+    float ch[(KG1 - KG0) * 8];
+#pragma unroll
+    for (int i = 0; i < (KG1 - KG0) * 8; ++i) ch[i] = 0.f;
+    float s[3], c[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        if (C0 == 0) ch[d] = x[d];
+        sincosf(x[d] * static_cast<float>(1 << F0), &s[d], &c[d]);
+    }
+#pragma unroll
+    for (int f = F0; f < F; ++f) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            const int cs = 3 + 6 * f + d, cc = cs + 3;
+            if (cs >= C0 && cs < C1 && cs < CH) ch[cs - C0] = s[d];
+            if (cc >= C0 && cc < C1 && cc < CH) ch[cc - C0] = c[d];
+            const float s2 = 2.f * s[d] * c[d];
+            const float c2 = (c[d] - s[d]) * (c[d] + s[d]);
+            s[d] = s2; c[d] = c2;
+        }
+    }
+#pragma unroll
+    for (int g = KG0; g < KG1; ++g) store_kg(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false, gst, gkg0 + g);
+}
+
+__device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kg0,
+                                           int kg1, uint8_t* gst = nullptr, int gkg0 = 0) {
+    for (int g = kg0; g < kg1; ++g) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = (src && g * 8 + e < count) ? __ldg(src + g * 8 + e) : 0.f;
+        store_kg(a_base, kExtKg + g, row, v, false, gst, gkg0 + g);
+    }
+}
+
 
 }  // namespace tc
 }  // namespace dmnerf

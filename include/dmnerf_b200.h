@@ -148,6 +148,15 @@ int  dmnerf_selftest_umma(const float* a, const float* b, int n, int k, float* d
 /* D[128,n] = A[64,128]^T * B[64,n]: both operands MN-major, the 64 rows being the reduction dim -- the operand
  * form of the wgrad GEMMs.  a,b fp32 in (row-major [64][128], [64][n]), d fp32 out [128][n]. */
 int  dmnerf_selftest_umma_mn(const float* a, const float* b, int n, float* d, void* stream);
+/* Micro-benchmark: `warps` (4..16, multiple of 4) warps of one CTA read all 512 TMEM columns `iters` times with
+ * tcgen05.ld 32x32b.x32 (batched != 0: two loads per wait).  out (device, 3 x int64): cycles, bytes read. */
+int  dmnerf_selftest_tmem_read_bw(int warps, int iters, int batched, long long* out, void* stream);
+/* Micro-benchmark: cycles for `count` back-to-back tcgen05.mma (M=128, N=n, K=16, bf16) issued by one thread. */
+int  dmnerf_selftest_umma_rate(int n, int count, long long* out, void* stream);
+/* Bring-up aid: cycle counters block 0 of the last pipelined-forward launch wrote (8 x int64, HOST pointer;
+ * synchronises the device): MMA issuer total / waiting for weights / waiting for activations, epilogue thread total /
+ * waiting for accumulators, producer waiting for a free ring slot. */
+int  dmnerf_debug_counters(long long* host_out8);
 /* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the forward's descriptors; bit1: in wgrad's).
  * flags < 0 only queries.  Returns the previous value. */
 int  dmnerf_debug_flags(int flags);

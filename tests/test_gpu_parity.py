@@ -549,3 +549,21 @@ def test_ins_branch_is_detached_from_trunk_bf16():
     for name, prm in m.named_parameters():
         touched = float(prm.grad.abs().max()) > 0
         assert touched == name.startswith("ins_"), name
+
+
+def test_mlp_bf16_pipelined_variant_matches_lockstep():
+    """The pipelined forward (mlp_tc2.cu, debug bit 2) computes the same network as the default lockstep kernel;
+    the only numeric difference is the bias entering through the GEMM as a bf16 hi+lo pair."""
+    from dm_nerf_b200 import _lib
+    m = make_model(32, 4)
+    gen = torch.Generator().manual_seed(8)
+    o, d = cu((torch.rand(37, 3, generator=gen) - 0.5) * 2), cu(torch.randn(37, 3, generator=gen))
+    z = cu(torch.sort(torch.rand(37, 192, generator=gen) * 11 + 4, -1)[0])
+    with _bf16_mode(), torch.no_grad():
+        a = m.query_rays(o, d, z)
+        old = _lib.lib().dmnerf_debug_flags(4)
+        try:
+            b = m.query_rays(o, d, z)
+        finally:
+            _lib.lib().dmnerf_debug_flags(old)
+    assert float((a - b).abs().max()) <= 2e-3
