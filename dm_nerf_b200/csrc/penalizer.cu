@@ -56,6 +56,10 @@ penalizer_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
             const int s = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
             const int j = i - s * C;
             if (j < 4) continue;
+            // samples behind the surface band carry zero weight in both terms, and inside the band only the
+            // "empty" channel counts: those logits are never loaded (about half of the bytes for a mid-range depth)
+            const float wb = cb[s];
+            if (wb == 0.f && (j != C - 1 || cm[s] == 0.f)) continue;
             const float p = sigmoidf_ref(__ldg(row + i));
             const float l_not = -logf(1.0f - p + 1e-8f);
             if (j == C - 1) {
@@ -114,7 +118,7 @@ penalizer_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         const int s = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
         const int j = i - s * C;
         float v = 0.f;
-        if (j >= 4) {
+        if (j >= 4 && (cb[s] != 0.f || (j == C - 1 && cm[s] != 0.f))) {
             const float p = sigmoidf_ref(__ldg(row + i));
             const float dp = p * (1.0f - p);
             const float d_not = dp / (1.0f - p + 1e-8f);          // d/dx of -log(1-p+1e-8)

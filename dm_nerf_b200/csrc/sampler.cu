@@ -106,22 +106,36 @@ sample_pdf_kernel(const float* __restrict__ bins, const float* __restrict__ weig
 }
 
 // Coarse tail: mids -> pdf over weights[1:-1] -> n_imp samples -> sort(cat(z_coarse, samples)).
+// The result equals torch.sort(cat) as a sorted multiset.  Both inputs are normally sorted already (z_coarse by
+// construction; the samples because the inverse CDF is monotone and, in det mode, u is ascending), so the merge is
+// done by rank -- out position of z_i = i + #{samples < z_i}, of sample k = k + #{z <= s_k}, one binary search per
+// element -- instead of a 256-wide bitonic network.  Random u: the 128 samples go through a 128-wide bitonic sort
+// first.  Sortedness is CHECKED per ray (an ulp-level inversion at a bin edge is possible in principle); a ray
+// that fails takes the full bitonic sort.
+__device__ __forceinline__ bool warp_sorted(const float* v, int n, int lane) {
+    bool ok = true;
+    for (int i = lane + 1; i < n; i += 32) ok = ok && (v[i - 1] <= v[i]);
+    return __all_sync(0xffffffffu, ok);
+}
+
 __global__ void __launch_bounds__(kSampWarps * 32)
 fine_z_kernel(const float* __restrict__ z_coarse, const float* __restrict__ weights, const float* __restrict__ u,
-              int64_t u_stride, int64_t n, int sc, int n_imp, int P, float* __restrict__ z_fine,
+              int64_t u_stride, int64_t n, int sc, int n_imp, int P, int P2, float* __restrict__ z_fine,
               float* __restrict__ z_samples) {
     extern __shared__ float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t ray = static_cast<int64_t>(blockIdx.x) * kSampWarps + warp;
     if (ray >= n) return;
     const int nb = sc - 1;
-    float* s_sort = smem + warp * (P + 3 * sc);
+    float* s_sort = smem + warp * (P + 3 * sc + P2);
     float* s_bins = s_sort + P;
     float* s_cdf = s_bins + sc;
     float* s_w = s_cdf + sc;
-    for (int j = lane; j < sc; j += 32) s_sort[j] = z_coarse[ray * sc + j];
+    float* s_samp = s_w + sc;
+    float* s_zc = s_sort + (P - sc);                       // coarse depths parked at the tail of the output buffer
+    for (int j = lane; j < sc; j += 32) s_zc[j] = z_coarse[ray * sc + j];
     __syncwarp();
-    for (int j = lane; j < nb; j += 32) s_bins[j] = __fmul_rn(0.5f, __fadd_rn(s_sort[j + 1], s_sort[j]));
+    for (int j = lane; j < nb; j += 32) s_bins[j] = __fmul_rn(0.5f, __fadd_rn(s_zc[j + 1], s_zc[j]));
     for (int j = lane; j < nb - 1; j += 32) s_w[j] = __fadd_rn(weights[ray * sc + 1 + j], 1e-5f);
     __syncwarp();
     build_cdf(s_cdf, s_w, nb, lane);
@@ -129,13 +143,38 @@ fine_z_kernel(const float* __restrict__ z_coarse, const float* __restrict__ weig
         const float uu = u ? u[ray * u_stride + i] : linspace01(i, n_imp);
         int inds;
         const float zz = invert_cdf(s_cdf, s_bins, nb, uu, inds);
-        s_sort[sc + i] = zz;
+        s_samp[i] = zz;
         if (z_samples) z_samples[ray * n_imp + i] = zz;
     }
-    for (int i = sc + n_imp + lane; i < P; i += 32) s_sort[i] = CUDART_INF_F;
+    for (int i = n_imp + lane; i < P2; i += 32) s_samp[i] = CUDART_INF_F;
     __syncwarp();
-    bitonic_sort(s_sort, P, lane);
     const int tot = sc + n_imp;
+    // the cdf is dead from here on: the coarse depths move into its place, freeing the whole output buffer
+    for (int j = lane; j < sc; j += 32) s_cdf[j] = s_zc[j];
+    __syncwarp();
+    const bool coarse_ok = warp_sorted(s_cdf, sc, lane);
+    if (coarse_ok) {
+        if (!warp_sorted(s_samp, n_imp, lane)) bitonic_sort(s_samp, P2, lane);
+        for (int i = lane; i < sc; i += 32) {              // rank of a coarse depth: samples strictly below it
+            const float v = s_cdf[i];
+            int lo = 0, hi = n_imp;
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (s_samp[mid] < v) lo = mid + 1; else hi = mid; }
+            s_sort[i + lo] = v;
+        }
+        for (int k = lane; k < n_imp; k += 32) {           // rank of a sample: coarse depths at or below it
+            const float v = s_samp[k];
+            int lo = 0, hi = sc;
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (s_cdf[mid] <= v) lo = mid + 1; else hi = mid; }
+            s_sort[k + lo] = v;
+        }
+        __syncwarp();
+    } else {
+        for (int j = lane; j < sc; j += 32) s_sort[j] = s_cdf[j];
+        for (int i = lane; i < n_imp; i += 32) s_sort[sc + i] = s_samp[i];
+        for (int i = tot + lane; i < P; i += 32) s_sort[i] = CUDART_INF_F;
+        __syncwarp();
+        bitonic_sort(s_sort, P, lane);
+    }
     for (int i = lane; i < tot; i += 32) z_fine[ray * tot + i] = s_sort[i];
 }
 
@@ -212,12 +251,13 @@ extern "C" int dmnerf_fine_z(const float* z_coarse, const float* weights, const 
     DM_REQUIRE(sc >= 4 && sc <= 512 && n_imp >= 2 && sc + n_imp <= 1024, DMNERF_EUNSUPPORTED,
                "fine_z: sc %d / n_importance %d unsupported", sc, n_imp);
     if (n <= 0) return DMNERF_OK;
-    int P = 1;
+    int P = 1, P2 = 1;
     while (P < sc + n_imp) P <<= 1;
-    const size_t smem = static_cast<size_t>(kSampWarps) * (P + 3 * sc) * sizeof(float);
+    while (P2 < n_imp) P2 <<= 1;
+    const size_t smem = static_cast<size_t>(kSampWarps) * (P + 3 * sc + P2) * sizeof(float);
     const unsigned grid = static_cast<unsigned>((n + kSampWarps - 1) / kSampWarps);
     fine_z_kernel<<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(z_coarse, weights, u, u_stride, n, sc, n_imp, P,
-                                                                     z_fine, z_samples);
+                                                                     P2, z_fine, z_samples);
     DM_LAUNCH_CHECK("fine_z_kernel");
     return DMNERF_OK;
 }

@@ -567,3 +567,20 @@ def test_mlp_bf16_pipelined_variant_matches_lockstep():
         finally:
             _lib.lib().dmnerf_debug_flags(old)
     assert float((a - b).abs().max()) <= 2e-3
+
+
+@pytest.mark.parametrize("sc,n_imp", [(64, 128), (64, 64), (33, 100)])
+def test_fine_z_is_sorted_merge(sc, n_imp):
+    """dmnerf_fine_z == torch.sort(cat(z_coarse, z_samples)) bit for bit (rank merge; det and random uniforms,
+    ties between a coarse depth and a sample, duplicated samples from flat cdf segments)."""
+    from dm_nerf_b200 import ops
+    gen = torch.Generator().manual_seed(12)
+    n = 257
+    zc = torch.sort(torch.rand(n, sc, generator=gen) * 11 + 4, -1)[0]
+    w = torch.rand(n, sc, generator=gen)
+    w[::3, 5:40] = 0.0                                   # long empty stretches: denom < 1e-5 branch, repeated samples
+    w[1::7] = 0.0
+    for u in (None, torch.rand(n, n_imp, generator=gen)):
+        zf, zs = ops.fine_z(cu(zc), cu(w), n_imp, None if u is None else cu(u), want_samples=True)
+        ref = torch.sort(torch.cat([cu(zc), zs], -1), -1)[0]
+        assert torch.equal(zf, ref)
