@@ -20,18 +20,22 @@ struct ChunkPipe {
     uint32_t bar0;            // smem address of this warp's STAGES mbarriers
     float* tile_ptr;          // generic pointer to the ring
     int64_t ray0, ray_stride, total;
-    int S, C, nchunk, chunk_floats, lane;
+    int S, C, nchunk, steps, chunk_floats, lane;
     int64_t issued, consumed;
-    bool reverse;             // walk a ray's chunks last-to-first (backward scans)
+    bool there_and_back;      // per ray: chunks 0..n-1, then n-1..0 (recompute pass + reverse gradient pass)
+    bool stores;              // the consumer bulk-stores tiles back out: wait for those reads before refilling
 
     __device__ __forceinline__ void init(const float* raw, float* ring, uint64_t* bars, int64_t first_ray, int64_t stride,
-                                         int64_t n, int S_, int C_, int lane_, bool reverse_ = false) {
+                                         int64_t n, int S_, int C_, int lane_, bool there_and_back_ = false,
+                                         bool stores_ = false) {
         base = raw; tile_ptr = ring; tile0 = ptx::smem_u32(ring); bar0 = ptx::smem_u32(bars);
-        ray0 = first_ray; ray_stride = stride; S = S_; C = C_; lane = lane_; reverse = reverse_;
+        ray0 = first_ray; ray_stride = stride; S = S_; C = C_; lane = lane_;
+        there_and_back = there_and_back_; stores = stores_;
         nchunk = (S + 31) >> 5;
+        steps = there_and_back ? 2 * nchunk : nchunk;
         chunk_floats = 32 * C;
         const int64_t my_rays = first_ray < n ? (n - first_ray + stride - 1) / stride : 0;
-        total = my_rays * nchunk;
+        total = my_rays * steps;
         issued = consumed = 0;
         if (lane == 0) {
             for (int s = 0; s < STAGES; ++s) ptx::mbar_init(bar0 + 8 * s, 1);
@@ -41,12 +45,13 @@ struct ChunkPipe {
         for (int s = 0; s < STAGES - 1; ++s) issue();
     }
     __device__ __forceinline__ int chunk_of(int64_t k) const {
-        const int c = static_cast<int>(k % nchunk);
-        return reverse ? nchunk - 1 - c : c;
+        const int c = static_cast<int>(k % steps);
+        return c < nchunk ? c : 2 * nchunk - 1 - c;
     }
     __device__ __forceinline__ void issue() {
         if (issued < total && lane == 0) {
-            const int64_t ray = ray0 + (issued / nchunk) * ray_stride;
+            if (stores) ptx::bulk_wait_read0();
+            const int64_t ray = ray0 + (issued / steps) * ray_stride;
             const int c0 = chunk_of(issued) * 32;
             const int cnt = min(32, S - c0);
             const uint32_t bytes = static_cast<uint32_t>(cnt) * C * 4;
@@ -56,15 +61,29 @@ struct ChunkPipe {
         }
         ++issued;
     }
-    // Blocks until the next chunk has landed; returns its tile.  ray / c0 describe it.
-    __device__ __forceinline__ float* acquire(int64_t& ray, int& c0) {
+    // Blocks until the next chunk has landed; returns its tile.  ray / c0 describe it; `back` = second (reverse) pass.
+    // The caller must have ended its reads of the previous tile with __syncwarp() (that stage is refilled here).
+    __device__ __forceinline__ float* acquire(int64_t& ray, int& c0, bool* back = nullptr) {
         issue();                                            // refill the stage released by the previous chunk
         const int st = static_cast<int>(consumed % STAGES);
         ptx::mbar_wait(bar0 + 8 * st, static_cast<uint32_t>((consumed / STAGES) & 1));
-        ray = ray0 + (consumed / nchunk) * ray_stride;
+        ray = ray0 + (consumed / steps) * ray_stride;
         c0 = chunk_of(consumed) * 32;
+        if (back) *back = static_cast<int>(consumed % steps) >= nchunk;
         ++consumed;
         return tile_ptr + st * chunk_floats;
+    }
+    // Bulk-store the (modified) tile just acquired to dst; every lane must have finished writing it.
+    __device__ __forceinline__ void store_tile(float* dst, const float* tile, uint32_t bytes) {
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            ptx::bulk_s2g(dst, ptx::smem_u32(tile), bytes);
+            ptx::bulk_commit();
+        }
+    }
+    __device__ __forceinline__ void finish() {
+        if (stores && lane == 0) ptx::bulk_wait0();
     }
     __device__ __forceinline__ bool done() const { return consumed >= total; }
 };

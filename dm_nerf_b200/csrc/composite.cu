@@ -368,6 +368,157 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     }
 }
 
+// Backward, bulk-copy staged: same phases as composite_bwd_kernel, but a ray's chunks arrive through the per-warp
+// bulk-copy ring twice (forward for the recompute pass, then in reverse for the gradient pass) and every finished
+// d_raw chunk leaves with one bulk store from the tile it was built in.
+__global__ void __launch_bounds__(kCompBulkWarps * 32)
+composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
+                          int64_t n, int S, int C, int flags, int ins_detach, const float* __restrict__ d_rgb,
+                          const float* __restrict__ d_depth, const float* __restrict__ d_weights,
+                          const float* __restrict__ d_ins, float* __restrict__ d_raw) {
+    extern __shared__ __align__(128) float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int per_warp = kCompStages * 32 * C + 32 + 3 * S;
+    float* ring = smem + warp * per_warp;
+    float* wbuf = ring + kCompStages * 32 * C;
+    float* s_alpha = wbuf + 32;
+    float* s_trans = s_alpha + S;
+    float* s_w = s_trans + S;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp + (kCompBulkWarps * per_warp & 1)) + warp * kCompStages;
+    ChunkPipe<kCompStages> pipe;
+    pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
+              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane, true, true);
+    const int L = C - 4;
+    const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
+    const bool need_logits = d_ins != nullptr;
+
+    float carry = 1.0f, norm = 0.f, suffix = 0.f, g_r = 0.f, g_g = 0.f, g_b = 0.f, g_d = 0.f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f}, dA[4] = {0.f, 0.f, 0.f, 0.f};
+    while (!pipe.done()) {
+        int64_t ray; int c0; bool back;
+        float* tile = pipe.acquire(ray, c0, &back);
+        const float* zrow = z + ray * S;
+        const int cnt = min(32, S - c0);
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        if (!back) {
+            // ---- phase A: recompute alpha / T / w and the logit sums
+            if (c0 == 0) {
+                const float dx = rays_d[ray * 3 + 0], dy = rays_d[ray * 3 + 1], dz = rays_d[ray * 3 + 2];
+                norm = sqrtf(dx * dx + dy * dy + dz * dz);
+                carry = 1.0f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[q] = 0.f;
+            }
+            float dist = 0.f, sigma = 0.f;
+            if (valid) {
+                const float zc = zrow[s];
+                dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+                sigma = tile[lane * C + 3];
+            }
+            float alpha, trans, w;
+            scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
+            if (valid) { s_alpha[s] = alpha; s_trans[s] = trans; s_w[s] = w; }
+            wbuf[lane] = w;
+            __syncwarp();
+            if (need_logits) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int j = lane + 32 * q;
+                    if (j < L) {
+                        float a = acc[q];
+                        const float* col = tile + 4 + j;
+#pragma unroll 8
+                        for (int r = 0; r < cnt; ++r) a += wbuf[r] * col[r * C];
+                        acc[q] = a;
+                    }
+                }
+            }
+            if (c0 + 32 >= S) {
+                // ---- phase B: gradient w.r.t. the accumulated logits, per-ray output gradients
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int j = lane + 32 * q;
+                    float g = 0.f;
+                    if (need_logits && j < Lout) {
+                        g = d_ins[ray * Lout + j];
+                        if (!(flags & DMNERF_COMP_RAW_INS)) {
+                            const float p = sigmoidf_ref(acc[q]);
+                            g *= p * (1.0f - p);
+                        }
+                    }
+                    dA[q] = g;
+                }
+                g_r = d_rgb ? d_rgb[ray * 3 + 0] : 0.f;
+                g_g = d_rgb ? d_rgb[ray * 3 + 1] : 0.f;
+                g_b = d_rgb ? d_rgb[ray * 3 + 2] : 0.f;
+                g_d = d_depth ? d_depth[ray] : 0.f;
+                suffix = 0.f;
+            }
+            __syncwarp();
+            continue;
+        }
+        // ---- phase C (reverse): running suffix sum R_s = sum_{r>s} dw_r w_r
+        float dw = 0.f, w = 0.f, alpha = 0.f, trans = 0.f, zc = 0.f, c_r = 0.f, c_g = 0.f, c_b = 0.f;
+        if (valid) {
+            w = s_w[s]; alpha = s_alpha[s]; trans = s_trans[s]; zc = zrow[s];
+            c_r = sigmoidf_ref(tile[lane * C + 0]);
+            c_g = sigmoidf_ref(tile[lane * C + 1]);
+            c_b = sigmoidf_ref(tile[lane * C + 2]);
+            dw = g_r * c_r + g_g * c_g + g_b * c_b + g_d * zc;
+            if (d_weights) dw += d_weights[ray * S + s];
+        }
+        if (!ins_detach && need_logits) {
+            for (int r = 0; r < cnt; ++r) {
+                float part = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int j = lane + 32 * q;
+                    if (j < L) part += dA[q] * tile[r * C + 4 + j];
+                }
+                part = warp_sum(part);
+                if (lane == r) dw += part;
+            }
+        }
+        const float g = valid ? dw * w : 0.f;
+        float incl = g;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const float v = __shfl_down_sync(0xffffffffu, incl, o);
+            if (lane + o < 32) incl += v;
+        }
+        const float after = suffix + (incl - g);
+        suffix += __shfl_sync(0xffffffffu, incl, 0);
+        __syncwarp();
+        if (valid) {
+            const float t = (1.0f - alpha) + 1e-10f;
+            const float dalpha = dw * trans - after / t;
+            const float sigma = tile[lane * C + 3];
+            const float dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            const float dsigma = (sigma > 0.f) ? dalpha * dist * (1.0f - alpha) : 0.f;
+            tile[lane * C + 0] = g_r * w * c_r * (1.0f - c_r);
+            tile[lane * C + 1] = g_g * w * c_g * (1.0f - c_g);
+            tile[lane * C + 2] = g_b * w * c_b * (1.0f - c_b);
+            tile[lane * C + 3] = dsigma;
+        }
+        wbuf[lane] = w;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) {
+                float* col = tile + 4 + j;
+                const float a = dA[q];
+#pragma unroll 8
+                for (int r = 0; r < cnt; ++r) col[r * C] = a * wbuf[r];
+            }
+        }
+        pipe.store_tile(d_raw + (ray * S + c0) * static_cast<int64_t>(C), tile, static_cast<uint32_t>(cnt) * C * 4);
+        __syncwarp();
+    }
+    pipe.finish();
+}
+
 }  // namespace dmnerf
 
 using namespace dmnerf;
@@ -415,6 +566,27 @@ extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const floa
     DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_bwd: n_samples %d outside [1,1024]", s);
     DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "composite_bwd: channels %d outside [6,128]", c);
     if (n == 0) return DMNERF_OK;
+    if ((reinterpret_cast<uintptr_t>(raw) & 15) == 0 && (reinterpret_cast<uintptr_t>(d_raw) & 15) == 0 &&
+        (static_cast<int64_t>(s) * c) % 4 == 0 && s % 4 == 0) {
+        static int sm_count = 0;
+        if (sm_count == 0) {
+            int dev = 0;
+            DM_CUDA(cudaGetDevice(&dev));
+            DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+        }
+        const size_t smem = static_cast<size_t>(kCompBulkWarps) * ((kCompStages * 32 * c + 32 + 3 * s) * sizeof(float) + kCompStages * 8) + 8;
+        if (smem <= 220 * 1024) {
+            int per_sm = static_cast<int>((220 * 1024) / (smem + 1024));
+            per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+            DM_CUDA(cudaFuncSetAttribute(composite_bwd_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            const int64_t want = (n + kCompBulkWarps - 1) / kCompBulkWarps;
+            const int64_t cap = static_cast<int64_t>(sm_count) * per_sm;
+            composite_bwd_bulk_kernel<<<static_cast<unsigned>(want < cap ? want : cap), kCompBulkWarps * 32, smem, as_stream(stream)>>>(
+                raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins, d_raw);
+            DM_LAUNCH_CHECK("composite_bwd_bulk_kernel");
+            return DMNERF_OK;
+        }
+    }
     const int CP = c | 1;
     const size_t smem = static_cast<size_t>(kCompWarps) * (32 * CP + 32 + 3 * s) * sizeof(float);
     DM_REQUIRE(smem <= 227 * 1024, DMNERF_EUNSUPPORTED, "composite_bwd: shared memory %zu too large", smem);
