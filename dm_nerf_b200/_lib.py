@@ -81,6 +81,7 @@ _SIGNATURES = {
     "dmnerf_label_argmax": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_selftest_umma": (_int, [_p, _p, _int, _int, _p, _p]),
     "dmnerf_selftest_umma_mn": (_int, [_p, _p, _int, _p, _p]),
+    "dmnerf_selftest_umma2": (_int, [_p, _p, _int, _int, _p, _p]),
     "dmnerf_selftest_tmem_read_bw": (_int, [_int, _int, _int, _p, _p]),
     "dmnerf_selftest_umma_rate": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_counters": (_int, [_p]),

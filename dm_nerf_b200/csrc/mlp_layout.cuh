@@ -98,8 +98,8 @@ constexpr int kStPos = 0, kStDir = 8, kStH0 = 12, kStHid = 12 + 8 * 32, kStActKg
 constexpr int kStG0 = 0, kStG8 = 8 * 32, kStG9 = 9 * 32, kStGradKg = 304;
 constexpr int64_t kStActBlkBytes = static_cast<int64_t>(kStActKg) * kStKgBytes;    // 307,200
 constexpr int64_t kStGradBlkBytes = static_cast<int64_t>(kStGradKg) * kStKgBytes;  // 311,296
-// blocks are allocated for whole tile PAIRS (256 points) of the persistent kernels
-__host__ __device__ inline int64_t tc_stash_blocks(int64_t n_points) { return ((n_points + 255) / 256) * 4; }
+// blocks are allocated for whole tile QUADS (512 points: two tiles in each CTA of a pair) of the persistent kernels
+__host__ __device__ inline int64_t tc_stash_blocks(int64_t n_points) { return ((n_points + 511) / 512) * 8; }
 
 // Input of one MLP launch: either rays (points o + d*z and both embeddings computed in-kernel) or
 // already-embedded rows x[m,90].

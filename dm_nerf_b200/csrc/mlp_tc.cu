@@ -155,7 +155,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
-        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 1); ptx::mbar_init(bars.acc_ready(t), 1); }
+        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 2 * kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
         ptx::fence_barrier_init();
     }
     if (warp == kMmaWarp) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
@@ -237,7 +237,6 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
         const uint32_t t_base = tmem + t * 256 + (static_cast<uint32_t>(q * 32) << 16);
         float* stage_out = reinterpret_cast<float*>(smem + kSmA + t * kABytes);
         float* dens_part = reinterpret_cast<float*>(smem + kSmDens) + t * kTile;
-        const bool leader = (warp & 7) == 0 && lane == 0;
         uint32_t acc_par = 0;
         for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
             const int64_t tile0 = pair * kPair + t * kTile;
@@ -267,11 +266,11 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             }
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
-            tile_arrive(bars.a_ready(t), t, leader);
+            ptx::mbar_arrive(bars.a_ready(t));
 
             float dens = 0.f;
             for (int l = 0; l < kLayers - 1; ++l) {
-                tile_wait(bars.acc_ready(t), acc_par, t, leader);
+                ptx::mbar_wait(bars.acc_ready(t), acc_par);
                 acc_par ^= 1;
                 ptx::tc_fence_after();
                 const float* bias = s_bias + l * 256;
@@ -307,10 +306,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 }
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
-                tile_arrive(bars.a_ready(t), t, leader);
+                ptx::mbar_arrive(bars.a_ready(t));
             }
             // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (half 0) ----
-            tile_wait(bars.acc_ready(t), acc_par, t, leader);
+            ptx::mbar_wait(bars.acc_ready(t), acc_par);
             acc_par ^= 1;
             ptx::tc_fence_after();
             if (half == 0) {
@@ -409,12 +408,14 @@ umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, i
 }  // namespace tc
 
 int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int launch_mlp_bf16_v3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
     // debug bit2 selects the pipelined variant (mlp_tc2.cu).  It is correct (same parity tests) but not faster:
     // its N=128 cells re-read the A operand twice, which makes the SS-mode MMAs shared-memory-bandwidth bound
     // once the epilogue's stores overlap them (measured 7.06 ms vs 6.92 ms per 32768x192 points); see DESIGN.md.
     if (g_tc_debug_flags & 4) return launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st);
+    if (g_tc_debug_flags & 8) return launch_mlp_bf16_v3(in, packed, ins_num, raw_out, stash, st);
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -443,7 +444,7 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
 int tc_debug_flags() { return g_tc_debug_flags; }
 
 namespace tc2 { int pack_v2(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
-int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+namespace tc3 { int pack_v3(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
 
 int64_t bf16_image_bytes(int ins_num) { return tc::make_image(ins_num).total_bytes; }
 
@@ -461,7 +462,8 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     tc::pack_dgrad_kernel<<<static_cast<unsigned>((dg_elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_f32_kernel<<<(tc::kF32Floats + 255) / 256, 256, 0, st>>>(pr, im, image);
     DM_LAUNCH_CHECK("pack_bf16");
-    return tc2::pack_v2(params, ins_num, packed, st);
+    if (int rc = tc2::pack_v2(params, ins_num, packed, st)) return rc;
+    return tc3::pack_v3(params, ins_num, packed, st);
 }
 
 }  // namespace dmnerf
@@ -590,5 +592,68 @@ extern "C" int dmnerf_selftest_umma_rate(int n, int count, long long* out, void*
     DM_CUDA(cudaFuncSetAttribute(dmnerf::tc::umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dmnerf::tc::umma_rate_kernel<<<1, 128, smem, as_stream(stream)>>>(n, count, out);
     DM_LAUNCH_CHECK("umma_rate_kernel");
+    return DMNERF_OK;
+}
+
+// ---- bring-up self test of the CTA-pair MMA: D[256,n] = A[256,k] * B[n,k]^T, cluster of 2 CTAs; CTA r holds rows
+// [128r, 128r+128) of A and rows [n/2 r, n/2 (r+1)) of B (K-major, no swizzle), and receives rows [128r, ..) of D.
+namespace dmnerf { namespace tc {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+umma2_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, int n, int k, float* __restrict__ d) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sm0 = ptx::smem_u32(smem);
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int warp = threadIdx.x >> 5, row = threadIdx.x;
+    const int nh = n / 2;
+    const uint32_t a_base = sm0, b_base = sm0 + 65536, bar = sm0 + 65536 + 65536;
+    volatile uint32_t* slot = reinterpret_cast<volatile uint32_t*>(smem + 65536 + 65536 + 8);
+    __nv_bfloat16* sa = reinterpret_cast<__nv_bfloat16*>(smem);
+    __nv_bfloat16* sb = reinterpret_cast<__nv_bfloat16*>(smem + 65536);
+    for (int i = threadIdx.x; i < 128 * k; i += 128) {
+        const int r = i / k, c = i - r * k;
+        sa[((c >> 3) * 128 + r) * 8 + (c & 7)] = __float2bfloat16_rn(a[(rank * 128 + r) * k + c]);
+    }
+    for (int i = threadIdx.x; i < nh * k; i += 128) {
+        const int r = i / k, c = i - r * k;
+        sb[((c >> 3) * nh + r) * 8 + (c & 7)] = __float2bfloat16_rn(b[(rank * nh + r) * k + c]);
+    }
+    if (threadIdx.x == 0) { ptx::mbar_init(bar, 1); ptx::fence_barrier_init(); }
+    if (warp == 0) ptx::tmem_alloc2(ptx::smem_u32(const_cast<uint32_t*>(slot)), 256);
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before();
+    ptx::cluster_sync();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *slot;
+    if (rank == 0 && threadIdx.x == 0) {
+        const uint32_t idesc = ptx::idesc_bf16(256, n);
+        for (int ks = 0; ks < k / 16; ++ks) {
+            const uint64_t ad = ptx::smem_desc(a_base + ks * 2 * kKgBytes, kKgBytes, 128);
+            const uint64_t bd = ptx::smem_desc(b_base + ks * 2 * (nh * 16), nh * 16, 128);
+            ptx::umma2_bf16(tmem, ad, bd, idesc, ks != 0);
+        }
+        ptx::umma_commit2(bar, 3);
+    }
+    ptx::mbar_wait(bar, 0);
+    ptx::tc_fence_after();
+    for (int cb = 0; cb * 16 < n; ++cb) {
+        uint32_t r[16];
+        ptx::tmem_ld16(tmem + (static_cast<uint32_t>(warp * 32) << 16) + cb * 16, r);
+        ptx::tmem_ld_wait();
+        for (int e = 0; e < 16; ++e) d[(rank * 128 + row) * n + cb * 16 + e] = __uint_as_float(r[e]);
+    }
+    ptx::tc_fence_before();
+    ptx::cluster_sync();
+    if (warp == 0) { ptx::tc_fence_after(); ptx::tmem_dealloc2(tmem, 256); }
+}
+}}  // namespace dmnerf::tc
+
+extern "C" int dmnerf_selftest_umma2(const float* a, const float* b, int n, int k, float* d, void* stream) {
+    DM_REQUIRE(a && b && d, DMNERF_EINVAL, "selftest_umma2: null pointer");
+    DM_REQUIRE(n >= 32 && n <= 256 && n % 32 == 0 && k >= 16 && k <= 256 && k % 16 == 0, DMNERF_EUNSUPPORTED,
+               "selftest_umma2: n=%d k=%d (n multiple of 32 <= 256, k multiple of 16 <= 256)", n, k);
+    const int smem = 65536 + 65536 + 64;
+    DM_CUDA(cudaFuncSetAttribute(dmnerf::tc::umma2_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    dmnerf::tc::umma2_selftest_kernel<<<2, 128, smem, as_stream(stream)>>>(a, b, n, k, d);
+    DM_LAUNCH_CHECK("umma2_selftest_kernel");
     return DMNERF_OK;
 }

@@ -613,12 +613,14 @@ int launch_mlp_bwd_bf16(const void* packed, const void* acts, const float* d_raw
                (reinterpret_cast<uintptr_t>(packed) & 15) == 0,
                DMNERF_EINVAL, "mlp_bwd(bf16): acts/workspace must be 1024-byte aligned, packed 16-byte aligned");
     const tc::Image im = tc::make_image(ins_num);
-    const int64_t blocks = tc_stash_blocks(n_points);
     uint8_t* gstash = static_cast<uint8_t*>(workspace);
-    float* gimg = reinterpret_cast<float*>(gstash + blocks * kStGradBlkBytes);
+    float* gimg = reinterpret_cast<float*>(gstash + tc_stash_blocks(n_points) * kStGradBlkBytes);
     DM_CUDA(cudaMemsetAsync(gimg, 0, tcb::kGimgFloats * 4, st));
 
-    const int64_t pairs = blocks / 4;
+    // blocks actually written by the forward / dgrad kernels: whole 256-point pairs (the allocation is rounded up
+    // further, to 512-point quads, for the CTA-pair forward)
+    const int64_t pairs = (n_points + 255) / 256;
+    const int64_t blocks = pairs * 4;
     DM_CUDA(cudaFuncSetAttribute(tcb::mlp_dgrad_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::kDgSmTotal));
     tcb::mlp_dgrad_bf16_kernel<<<static_cast<unsigned>(pairs < sm_count ? pairs : sm_count), tc::kThreads, tcb::kDgSmTotal, st>>>(
         d_raw, n_points, static_cast<const uint8_t*>(packed), im, static_cast<const uint8_t*>(acts), gstash);

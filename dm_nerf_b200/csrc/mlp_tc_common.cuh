@@ -5,6 +5,7 @@
 #include "tc_ptx.cuh"
 #include <cuda_bf16.h>
 #include "mlp_tc2.cuh"
+#include "mlp_tc3.cuh"
 
 namespace dmnerf {
 namespace tc {
@@ -57,6 +58,9 @@ struct Image {
     int64_t v2_off;               // chunk stream of the pipelined forward (mlp_tc2.cuh), in issue order
     int64_t v2_sched_off;         // tc2::Chunk[v2_chunks]
     int v2_chunks;
+    int64_t v3_off[2];            // per-CTA-rank chunk streams of the CTA-pair forward (mlp_tc3.cuh)
+    int64_t v3_sched_off;         // tc3::Chunk[v3_chunks] then int layer_start[11]
+    int v3_chunks, npad2;         // npad2 = C rounded up to 32 (N of the pair's head MMA)
     int64_t total_bytes;
     int npad, ins_num, kp9;       // kp9 = C rounded up to 32: K of the first dgrad layer
 };
@@ -84,6 +88,12 @@ __host__ __device__ inline Image make_image(int ins_num) {
     im.v2_chunks = tc2::build_schedule(im.npad, nullptr, &v2_bytes);
     im.v2_off = off;         off += v2_bytes;
     im.v2_sched_off = off;   off += static_cast<int64_t>(tc2::kMaxChunks) * sizeof(tc2::Chunk);
+    im.npad2 = ((ins_num + 5) + 31) & ~31;
+    uint32_t v3_bytes = 0;
+    im.v3_chunks = tc3::build_schedule(im.npad2, nullptr, nullptr, &v3_bytes);
+    im.v3_off[0] = off;      off += v3_bytes;
+    im.v3_off[1] = off;      off += v3_bytes;
+    im.v3_sched_off = off;   off += static_cast<int64_t>(tc3::kMaxChunks) * sizeof(tc3::Chunk) + 16 * sizeof(int);
     im.total_bytes = off;
     return im;
 }
@@ -119,19 +129,6 @@ struct Bars {
     __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kStages + t); }
     __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kStages + 2 + t); }
 };
-
-// Handoffs between a tile's 256 epilogue threads and the MMA issuer.  Only ONE thread per tile touches the
-// mbarrier: polling and arriving are shared-memory-pipe operations, and 16 warps polling (or 256 arrivals per
-// layer) compete with the working warps' LDS/STS/LDTM.  The other threads block on a hardware named barrier
-// (ids 3 + tile), which costs no issue slots.
-__device__ __forceinline__ void tile_wait(uint32_t bar, uint32_t parity, int t, bool leader) {
-    if (leader) ptx::mbar_wait(bar, parity);
-    ptx::named_bar_sync(3 + t, 2 * kTile);
-}
-__device__ __forceinline__ void tile_arrive(uint32_t bar, int t, bool leader) {
-    ptx::named_bar_sync(3 + t, 2 * kTile);
-    if (leader) ptx::mbar_arrive(bar);
-}
 
 __device__ __forceinline__ uint64_t op_desc(uint32_t addr, uint32_t lbo, uint32_t sbo, int swap) {
     return swap ? ptx::smem_desc(addr, sbo, lbo) : ptx::smem_desc(addr, lbo, sbo);

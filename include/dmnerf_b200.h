@@ -148,6 +148,9 @@ int  dmnerf_selftest_umma(const float* a, const float* b, int n, int k, float* d
 /* D[128,n] = A[64,128]^T * B[64,n]: both operands MN-major, the 64 rows being the reduction dim -- the operand
  * form of the wgrad GEMMs.  a,b fp32 in (row-major [64][128], [64][n]), d fp32 out [128][n]. */
 int  dmnerf_selftest_umma_mn(const float* a, const float* b, int n, float* d, void* stream);
+/* CTA-pair form (tcgen05 cta_group::2, cluster of two CTAs): D[256,n] = A[256,k] * B[n,k]^T, each CTA holding its 128
+ * rows of A and its half of B's rows. */
+int  dmnerf_selftest_umma2(const float* a, const float* b, int n, int k, float* d, void* stream);
 /* Micro-benchmark: `warps` (4..16, multiple of 4) warps of one CTA read all 512 TMEM columns `iters` times with
  * tcgen05.ld 32x32b.x32 (batched != 0: two loads per wait).  out (device, 3 x int64): cycles, bytes read. */
 int  dmnerf_selftest_tmem_read_bw(int warps, int iters, int batched, long long* out, void* stream);

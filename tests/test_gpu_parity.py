@@ -551,17 +551,19 @@ def test_ins_branch_is_detached_from_trunk_bf16():
         assert touched == name.startswith("ins_"), name
 
 
-def test_mlp_bf16_pipelined_variant_matches_lockstep():
-    """The pipelined forward (mlp_tc2.cu, debug bit 2) computes the same network as the default lockstep kernel;
-    the only numeric difference is the bias entering through the GEMM as a bf16 hi+lo pair."""
+@pytest.mark.parametrize("flag,n_rays,k", [(4, 37, 32), (8, 37, 32), (8, 1500, 93), (8, 3, 1)])
+def test_mlp_bf16_pipelined_variant_matches_lockstep(flag, n_rays, k):
+    """The pipelined forward (mlp_tc2.cu, debug bit 2) and the CTA-pair forward (mlp_tc3.cu, debug bit 3) compute the
+    same network as the lockstep kernel; the only numeric difference is the bias entering through the GEMM as a
+    bf16 hi+lo pair."""
     from dm_nerf_b200 import _lib
-    m = make_model(32, 4)
+    m = make_model(k, 4)
     gen = torch.Generator().manual_seed(8)
-    o, d = cu((torch.rand(37, 3, generator=gen) - 0.5) * 2), cu(torch.randn(37, 3, generator=gen))
-    z = cu(torch.sort(torch.rand(37, 192, generator=gen) * 11 + 4, -1)[0])
+    o, d = cu((torch.rand(n_rays, 3, generator=gen) - 0.5) * 2), cu(torch.randn(n_rays, 3, generator=gen))
+    z = cu(torch.sort(torch.rand(n_rays, 192, generator=gen) * 11 + 4, -1)[0])
     with _bf16_mode(), torch.no_grad():
         a = m.query_rays(o, d, z)
-        old = _lib.lib().dmnerf_debug_flags(4)
+        old = _lib.lib().dmnerf_debug_flags(flag)
         try:
             b = m.query_rays(o, d, z)
         finally:
@@ -584,3 +586,20 @@ def test_fine_z_is_sorted_merge(sc, n_imp):
         zf, zs = ops.fine_z(cu(zc), cu(w), n_imp, None if u is None else cu(u), want_samples=True)
         ref = torch.sort(torch.cat([cu(zc), zs], -1), -1)[0]
         assert torch.equal(zf, ref)
+
+
+def test_umma2_selftest():
+    """CTA-pair MMA (cta_group::2, M=256 over a cluster of two CTAs, B split along N between them)."""
+    import ctypes as C
+    from dm_nerf_b200 import _lib
+    lib = _lib.lib()
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    gen = torch.Generator().manual_seed(3)
+    for n, k in ((256, 64), (256, 256), (64, 32), (128, 16)):
+        a, b = torch.randn(256, k, generator=gen).to(DEV), torch.randn(n, k, generator=gen).to(DEV)
+        d = torch.zeros(256, n, device=DEV)
+        rc = lib.dmnerf_selftest_umma2(C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), n, k, C.c_void_p(d.data_ptr()), st)
+        assert rc == 0, _lib.last_error()
+        torch.cuda.synchronize()
+        ref = a.bfloat16().float() @ b.bfloat16().float().t()
+        assert float((d - ref).abs().max()) <= 1e-3, (n, k)
