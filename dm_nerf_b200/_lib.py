@@ -85,6 +85,7 @@ _SIGNATURES = {
     "dmnerf_selftest_tmem_read_bw": (_int, [_int, _int, _int, _p, _p]),
     "dmnerf_selftest_umma_rate": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_counters": (_int, [_p]),
+    "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
 }
 

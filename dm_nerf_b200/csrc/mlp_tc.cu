@@ -119,6 +119,20 @@ __global__ void pack_f32_kernel(Params pr, Image im, uint8_t* __restrict__ image
     f[i] = v;
 }
 
+// forward bias blocks: layer l = blockIdx.x, element (g, n, e) of a [2][256][8] K-major B operand; k = 0 holds the
+// bf16 head of the bias and k = 1 the bf16 of the remainder (A = ones in both columns), ~16 mantissa bits in all
+__global__ void pack_fwbias_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+    const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
+    const int l = blockIdx.x;
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(image + im.fwb_off + static_cast<int64_t>(l) * kFwBiasBlkBytes);
+    for (int i = threadIdx.x; i < 2 * 256 * 8; i += blockDim.x) {
+        const int g = i / (256 * 8), n = (i >> 3) & 255, e = i & 7, kin = g * 8 + e;
+        const float b = l < 8 ? pr.p[2 * l + 1][n] : scratch[65536 + n];
+        const float hi = __bfloat162float(__float2bfloat16_rn(b));
+        dst[i] = __float2bfloat16_rn(kin == 0 ? hi : (kin == 1 ? b - hi : 0.f));
+    }
+}
+
 __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
     const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
     float* b = reinterpret_cast<float*>(image + im.bias_off);
@@ -140,29 +154,35 @@ __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ imag
 // ---- the kernel -------------------------------------------------------------------------------------------------
 // kStash (training): every A operand the backward needs (embeddings, h0..h7, [rgb_hid|ins_hid]) is mirrored
 // to the per-tile bf16 stash (mlp_layout.cuh) by the same 16-byte stores that build the smem operand.
+// cycle counters of block 0 when debug bit 4 is set (dmnerf_debug_counters): issuer 0 total, 1 wait w_full, 2 wait
+// a_ready | epilogue warp 0: 3 total, 4 wait acc_ready | producer 5 wait w_empty
+__device__ long long g_dbg1[8];
+
 template <bool kStash>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFwThreads, 1)
 mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags,
                     uint8_t* __restrict__ stash) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sm0 = ptx::smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const Bars bars{sm0 + kSmBar};
-    float* s_bias = reinterpret_cast<float*>(smem + kSmBias);
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kSmBar + 8 * (2 * kStages + 4));
-    const int swap = flags & 1;
+    const FwBars bars{sm0 + kFwSmBar};
+    float* s_misc = reinterpret_cast<float*>(smem + kFwSmMisc);      // [0,128) T9 bias | [128,384) w_density | [384] b_density
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kFwSmBar + 8 * (2 * kFwStages + 4));
     const int C = im.ins_num + 5;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
+        for (int s = 0; s < kFwStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 2); }
         for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 2 * kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
         ptx::fence_barrier_init();
     }
     if (warp == kMmaWarp) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
     {
         const float* gb = reinterpret_cast<const float*>(image + im.bias_off);
-        for (int i = threadIdx.x; i < kBiasFloats; i += kThreads) s_bias[i] = gb[i];
+        for (int i = threadIdx.x; i < 128 + 256 + 1; i += kFwThreads) s_misc[i] = gb[kBiasT9 + i];
+        uint32_t* ones = reinterpret_cast<uint32_t*>(smem + kFwSmOnes);
+        for (int i = threadIdx.x; i < 32; i += kFwThreads) ones[i] = (i & 3) == 0 ? 0x3F803F80u : 0u;
     }
+    ptx::fence_proxy_async_smem();
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -174,61 +194,82 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
         // ===== weight producer: walks the chunk stream of every layer for every tile pair =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
+            long long dbg_w = 0;
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
                 for (int l = 0; l < kLayers; ++l) {
-                    const uint32_t bytes = kChunkK * im.n[l] * 2;
-                    const int chunks = layer_k(l) / kChunkK;
+                    const uint32_t bytes = kFwChunkK * im.n[l] * 2;
+                    const int chunks = layer_k(l) / kFwChunkK;
                     const uint8_t* src = image + im.chunk_off[l];
-                    for (int c = 0; c < chunks; ++c) {
+                    for (int c = 0; c < chunks + (l < 9); ++c) {
+                        const long long w0 = clock64();
                         ptx::mbar_wait(bars.w_empty(stage), phase ^ 1);
-                        ptx::mbar_arrive_expect_tx(bars.w_full(stage), bytes);
-                        ptx::bulk_g2s(sm0 + kSmRing + stage * kStageBytes, src + static_cast<int64_t>(c) * bytes, bytes,
-                                      bars.w_full(stage));
-                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        dbg_w += clock64() - w0;
+                        const uint32_t nb = c < chunks ? bytes : kFwBiasBlkBytes;
+                        ptx::mbar_arrive_expect_tx(bars.w_full(stage), nb);
+                        ptx::bulk_g2s(sm0 + kFwSmRing + stage * kFwStageBytes,
+                                      c < chunks ? src + static_cast<int64_t>(c) * bytes
+                                                 : image + im.fwb_off + static_cast<int64_t>(l) * kFwBiasBlkBytes,
+                                      nb, bars.w_full(stage));
+                        if (++stage == kFwStages) { stage = 0; phase ^= 1; }
                     }
                 }
             }
+            if ((flags & 16) && blockIdx.x == 0) g_dbg1[5] = dbg_w;
             // drain: every stage's last release (tcgen05.commit arrive) must have landed before the CTA exits
-            for (int i = 0; i < kStages; ++i) {
+            for (int i = 0; i < kFwStages; ++i) {
                 ptx::mbar_wait(bars.w_empty(stage), phase ^ 1);
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                if (++stage == kFwStages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == kMmaWarp) {
-        // ===== MMA issuer =====
+    } else if (warp >= kMmaWarp) {
+        // ===== MMA issuers: warp 17 drives tile 0, warp 18 tile 1; both walk the same ring (w_empty counts 2) =====
         if (lane == 0) {
-            int stage = 0; uint32_t phase = 0, a_par[2] = {0, 0};
+            const int t = warp - kMmaWarp;
+            int stage = 0; uint32_t phase = 0, a_par = 0;
+            long long dbg_f = 0, dbg_a = 0;
+            const long long dbg_start = clock64();
+            // descriptors are built by adding 16-byte offsets to precomputed low words (K-major, no swizzle:
+            // LBO = k-group stride, SBO = 128 B)
+            constexpr uint32_t kKg16 = kKgBytes >> 4;
+            const uint64_t desc_hi = static_cast<uint64_t>(0x4008u) << 32;
+            const uint32_t a_lo0 = ((sm0 + kSmA + t * kABytes) >> 4) | (kKg16 << 16);
+            // ones operand: every core matrix of the [128 x 16] A tile is the same 128 bytes (LBO = SBO = 0); both
+            // k-groups then carry ones in columns 0,1, and the bias block is zero in rows k = 8.. so only k = 0,1 count
+            const uint64_t ones_d = (static_cast<uint64_t>(0x4000u) << 32) | ((sm0 + kFwSmOnes) >> 4);
+            const uint32_t ring_lo = (sm0 + kFwSmRing) >> 4;
+            const uint32_t d_tmem = tmem + t * 256;
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
                 for (int l = 0; l < kLayers; ++l) {
-                    const int N = im.n[l];
+                    const uint32_t N = im.n[l];
                     const uint32_t idesc = ptx::idesc_bf16(kTile, N);
-                    const int chunks = layer_k(l) / kChunkK;
-                    const int kg0 = layer_akg0(l);
-                    for (int c = 0; c < chunks; ++c) {
+                    const int chunks = layer_k(l) / kFwChunkK, last = chunks - (l == 9);   // T0..T8: + the bias step
+                    uint32_t a_lo = a_lo0 + layer_akg0(l) * kKg16;
+#pragma unroll 1
+                    for (int c = 0; c <= last; ++c, a_lo += 4 * kKg16) {
+                        const long long w0 = clock64();
                         ptx::mbar_wait(bars.w_full(stage), phase);
-                        ptx::tc_fence_after();
-                        const uint32_t b_base = sm0 + kSmRing + stage * kStageBytes;
-#pragma unroll
-                        for (int t = 0; t < 2; ++t) {
-                            if (c == 0) {
-                                ptx::mbar_wait(bars.a_ready(t), a_par[t]);
-                                a_par[t] ^= 1;
-                                ptx::tc_fence_after();
-                            }
-                            const uint32_t a_base = sm0 + kSmA + t * kABytes;
-#pragma unroll
-                            for (int kk = 0; kk < 2; ++kk) {
-                                const uint64_t ad = op_desc(a_base + (kg0 + c * 4 + kk * 2) * kKgBytes, kKgBytes, 128, swap);
-                                const uint64_t bd = op_desc(b_base + kk * 2 * (N * 16), N * 16, 128, swap);
-                                ptx::umma_bf16(tmem + t * 256, ad, bd, idesc, (c | kk) != 0);
-                            }
-                            if (c == chunks - 1) ptx::umma_commit(bars.acc_ready(t));
+                        dbg_f += clock64() - w0;
+                        if (c == 0) {
+                            const long long w1 = clock64();
+                            ptx::mbar_wait(bars.a_ready(t), a_par);
+                            dbg_a += clock64() - w1;
+                            a_par ^= 1;
                         }
+                        ptx::tc_fence_after();
+                        const uint32_t b_lo = (ring_lo + stage * (kFwStageBytes >> 4)) | (N << 16);
+                        if (c < chunks) {
+                            ptx::umma_bf16(d_tmem, desc_hi | a_lo, desc_hi | b_lo, idesc, c != 0);
+                            ptx::umma_bf16(d_tmem, desc_hi | (a_lo + 2 * kKg16), desc_hi | (b_lo + 2 * N), idesc, 1u);
+                        } else {
+                            ptx::umma_bf16(d_tmem, ones_d, desc_hi | b_lo, idesc, 1u);
+                        }
+                        if (c == last) ptx::umma_commit(bars.acc_ready(t));
                         ptx::umma_commit(bars.w_empty(stage));
-                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        if (++stage == kFwStages) { stage = 0; phase ^= 1; }
                     }
                 }
             }
+            if ((flags & 16) && blockIdx.x == 0 && t == 0) { g_dbg1[0] = clock64() - dbg_start; g_dbg1[1] = dbg_f; g_dbg1[2] = dbg_a; }
         }
     } else {
         // ===== epilogue / embedding: 8 warps per tile; thread == (point == TMEM lane, column half) =====
@@ -236,8 +277,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
         const uint32_t a_base = sm0 + kSmA + t * kABytes;
         const uint32_t t_base = tmem + t * 256 + (static_cast<uint32_t>(q * 32) << 16);
         float* stage_out = reinterpret_cast<float*>(smem + kSmA + t * kABytes);
-        float* dens_part = reinterpret_cast<float*>(smem + kSmDens) + t * kTile;
+        float* dens_part = reinterpret_cast<float*>(smem + kFwSmDens) + t * kTile;
         uint32_t acc_par = 0;
+        long long dbg_acc = 0;
+        const long long dbg_start = clock64();
         for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
             const int64_t tile0 = pair * kPair + t * kTile;
             const int64_t p = tile0 + row;
@@ -270,10 +313,11 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 
             float dens = 0.f;
             for (int l = 0; l < kLayers - 1; ++l) {
+                const long long w0 = clock64();
                 ptx::mbar_wait(bars.acc_ready(t), acc_par);
+                dbg_acc += clock64() - w0;
                 acc_par ^= 1;
                 ptx::tc_fence_after();
-                const float* bias = s_bias + l * 256;
 #pragma unroll 1
                 for (int cb = half * 4; cb < half * 4 + 4; ++cb) {
                     uint32_t r[32];
@@ -283,14 +327,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                     for (int g = 0; g < 4; ++g) {
                         float v[8];
 #pragma unroll
-                        for (int e = 0; e < 8; e += 2) {
-                            const float2 b2 = *reinterpret_cast<const float2*>(bias + cb * 32 + g * 8 + e);
-                            const float2 s2 = __fadd2_rn(make_float2(__uint_as_float(r[g * 8 + e]), __uint_as_float(r[g * 8 + e + 1])), b2);
-                            v[e] = s2.x; v[e + 1] = s2.y;
-                        }
+                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
                         if (l == 7) {
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_bias[kBiasWd + cb * 32 + g * 8 + e], dens);
+                            for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_misc[128 + cb * 32 + g * 8 + e], dens);
                         }
                         store_kg(a_base, cb * 4 + g, row, v, true, gst, (l == 8 ? kStHid : kStH0 + 32 * l) + cb * 4 + g);
                     }
@@ -309,7 +349,9 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 ptx::mbar_arrive(bars.a_ready(t));
             }
             // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (half 0) ----
+            const long long w9 = clock64();
             ptx::mbar_wait(bars.acc_ready(t), acc_par);
+            dbg_acc += clock64() - w9;
             acc_par ^= 1;
             ptx::tc_fence_after();
             if (half == 0) {
@@ -322,8 +364,8 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                     for (int e = 0; e < 16; ++e) {
                         const int col = cb * 16 + e;
                         if (col < C) {
-                            float v = __uint_as_float(r[e]) + s_bias[kBiasT9 + col];
-                            if (col == 3) v = dens + s_bias[kBiasBd];
+                            float v = __uint_as_float(r[e]) + s_misc[col];
+                            if (col == 3) v = dens + s_misc[384];
                             stage_out[row * C + col] = v;
                         }
                     }
@@ -347,6 +389,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 ptx::named_bar_sync(1 + t, kTile);
             }
         }
+        if ((flags & 16) && blockIdx.x == 0 && threadIdx.x == 0) { g_dbg1[3] = clock64() - dbg_start; g_dbg1[4] = dbg_acc; }
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -428,13 +471,13 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
     const unsigned grid = static_cast<unsigned>(pairs < sm_count ? pairs : sm_count);
     if (stash) {
         DM_REQUIRE((reinterpret_cast<uintptr_t>(stash) & 15) == 0, DMNERF_EINVAL, "mlp_fwd(bf16): stash must be 16-byte aligned");
-        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmTotal));
-        tc::mlp_fwd_bf16_kernel<true><<<grid, tc::kThreads, tc::kSmTotal, st>>>(
+        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+        tc::mlp_fwd_bf16_kernel<true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
             in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags,
             static_cast<uint8_t*>(stash));
     } else {
-        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmTotal));
-        tc::mlp_fwd_bf16_kernel<false><<<grid, tc::kThreads, tc::kSmTotal, st>>>(
+        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+        tc::mlp_fwd_bf16_kernel<false><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
             in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags, nullptr);
     }
     DM_LAUNCH_CHECK("mlp_fwd_bf16_kernel");
@@ -442,6 +485,11 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
 }
 
 int tc_debug_flags() { return g_tc_debug_flags; }
+
+int debug_counters_v1(long long* host_out8) {
+    DM_CUDA(cudaMemcpyFromSymbol(host_out8, tc::g_dbg1, 8 * sizeof(long long)));
+    return DMNERF_OK;
+}
 
 namespace tc2 { int pack_v2(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
 namespace tc3 { int pack_v3(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
@@ -458,6 +506,7 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     const int64_t elems = im.bias_off / 2;
     tc::pack_bf16_kernel<<<static_cast<unsigned>((elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_bias_kernel<<<(tc::kBiasFloats + 255) / 256, 256, 0, st>>>(pr, im, image);
+    tc::pack_fwbias_kernel<<<9, 256, 0, st>>>(pr, im, image);
     const int64_t dg_elems = (im.f32_off - im.dg_off[0]) / 2;
     tc::pack_dgrad_kernel<<<static_cast<unsigned>((dg_elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_f32_kernel<<<(tc::kF32Floats + 255) / 256, 256, 0, st>>>(pr, im, image);
@@ -592,6 +641,83 @@ extern "C" int dmnerf_selftest_umma_rate(int n, int count, long long* out, void*
     DM_CUDA(cudaFuncSetAttribute(dmnerf::tc::umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dmnerf::tc::umma_rate_kernel<<<1, 128, smem, as_stream(stream)>>>(n, count, out);
     DM_LAUNCH_CHECK("umma_rate_kernel");
+    return DMNERF_OK;
+}
+
+// ---- micro-benchmark: what the issuing thread pays per ring step besides the MMAs themselves.  Groups of two
+// M=128,N=16,K=16 MMAs (44 clk each in the pipe) plus, by `mode` bit: 1 a tcgen05.commit, 2 an mbarrier wait that
+// succeeds at once, 4 tcgen05.fence::after_thread_sync, 8 a clock64() read.  out[0] = cycles for `count` groups.
+namespace dmnerf { namespace tc {
+__global__ void __launch_bounds__(128, 1)
+issue_cost_kernel(int mode, int count, long long* __restrict__ out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sm0 = ptx::smem_u32(smem);
+    const int warp = threadIdx.x >> 5;
+    const uint32_t a_base = sm0, b_base = sm0 + 8192, bar = sm0 + 16384;
+    volatile uint32_t* slot = reinterpret_cast<volatile uint32_t*>(smem + 16384 + 32);
+    for (int i = threadIdx.x; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (threadIdx.x == 0) { ptx::mbar_init(bar, 1); ptx::mbar_init(bar + 8, 1); ptx::mbar_init(bar + 16, 1); ptx::fence_barrier_init(); }
+    if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(slot)), 512);
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *slot;
+    const uint32_t idesc = ptx::idesc_bf16(128, 16);
+    const uint64_t ad0 = ptx::smem_desc(a_base, kKgBytes, 128), ad1 = ptx::smem_desc(a_base + 2 * kKgBytes, kKgBytes, 128);
+    const uint64_t bd0 = ptx::smem_desc(b_base, 256, 128), bd1 = ptx::smem_desc(b_base + 512, 256, 128);
+    if ((mode & 16) && warp == 0) {
+        // whole warp walks the loop; one elected lane issues
+        long long sink = 0;
+        const long long t0 = clock64();
+#pragma unroll 1
+        for (int i = 0; i < count; ++i) {
+            if (mode & 8) sink += clock64();
+            if (mode & 2) ptx::mbar_wait(bar + 8, 1);
+            if (mode & 4) ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+                ptx::umma_bf16(tmem, ad0, bd0, idesc, (mode & 32) ? 1u : 0u);
+                ptx::umma_bf16(tmem, ad1, bd1, idesc, 1u);
+                if (mode & 64) {
+                    ptx::umma_bf16(tmem + ((mode & 128) ? 256 : 0), ad0, bd0, idesc, 1u);
+                    ptx::umma_bf16(tmem + ((mode & 128) ? 256 : 0), ad1, bd1, idesc, 1u);
+                }
+                if (mode & 1) ptx::umma_commit(bar + 16);
+            }
+            __syncwarp();
+        }
+        if (ptx::elect_one()) ptx::umma_commit(bar);
+        __syncwarp();
+        ptx::mbar_wait(bar, 0);
+        if (threadIdx.x == 0) { out[0] = clock64() - t0; out[1] = sink; }
+    } else if (!(mode & 16) && threadIdx.x == 0) {
+        long long sink = 0;
+        const long long t0 = clock64();
+#pragma unroll 1
+        for (int i = 0; i < count; ++i) {
+            if (mode & 8) sink += clock64();
+            if (mode & 2) ptx::mbar_wait(bar + 8, 1);          // fresh barrier: the "previous" phase counts as complete
+            if (mode & 4) ptx::tc_fence_after();
+            ptx::umma_bf16(tmem, ad0, bd0, idesc, 0u);
+            ptx::umma_bf16(tmem, ad1, bd1, idesc, 1u);
+            if (mode & 1) ptx::umma_commit(bar + 16);
+        }
+        ptx::umma_commit(bar);
+        ptx::mbar_wait(bar, 0);
+        out[0] = clock64() - t0;
+        out[1] = sink;
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 512); }
+}
+}}  // namespace dmnerf::tc
+
+extern "C" int dmnerf_selftest_issue_cost(int mode, int count, long long* out, void* stream) {
+    DM_REQUIRE(out && count > 0, DMNERF_EINVAL, "selftest_issue_cost: bad arguments");
+    const int smem = 16384 + 64;
+    dmnerf::tc::issue_cost_kernel<<<1, 128, smem, as_stream(stream)>>>(mode, count, out);
+    DM_LAUNCH_CHECK("issue_cost_kernel");
     return DMNERF_OK;
 }
 

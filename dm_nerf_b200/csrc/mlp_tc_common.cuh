@@ -35,6 +35,24 @@ constexpr int kSmBar = kSmBias + kBiasFloats * 4;              // 223,808
 constexpr int kSmDens = kSmBar + 128;                          // density partials of column-half 1: [2][128] floats
 constexpr int kSmTotal = kSmDens + 2 * kTile * 4;
 
+// forward kernel (mlp_tc.cu): every layer ends with one more K=16 step against a constant "ones" operand whose B
+// rows hold the bias as a bf16 hi+lo pair (Image::fwb_off), so the epilogue is LDTM -> relu+pack -> STS only.  A ring
+// step costs the issuing thread ~300 clk of control code whatever it issues (tools/issue_cost.py: an mbarrier
+// try_wait that succeeds at once is 88 clk alone), so each tile has its own issuer warp (2 MMAs = 256 clk per step).
+constexpr int kFwChunkK = 32;
+constexpr int kFwStages = 4;
+constexpr int kFwStageBytes = kFwChunkK * 256 * 2;              // 16 KB
+constexpr int kFwBiasBlkBytes = 16 * 256 * 2;                   // [2 k-groups][256][8] bf16 per layer T0..T8
+constexpr int kFwThreads = 19 * 32;                             // 16 epilogue warps | producer | one MMA issuer per tile
+constexpr int kFwSmOnes = 2 * kABytes;                          // 163,840: ONE 8x8 core matrix (128 B), elements 0,1 of each row = 1;
+                                                                //   the ones-operand descriptor has LBO = SBO = 0 (broadcast)
+constexpr int kFwSmRing = kFwSmOnes + 128;                      // 163,968
+constexpr int kFwSmMisc = kFwSmRing + kFwStages * kFwStageBytes;  // 229,504: T9 bias (128) | w_density (256) | b_density
+constexpr int kFwSmBar = kFwSmMisc + 400 * 4;
+constexpr int kFwSmDens = kFwSmBar + 8 * (2 * kFwStages + 4) + 16;
+constexpr int kFwSmTotal = kFwSmDens + 2 * kTile * 4;
+static_assert(kFwSmTotal <= 227 * 1024, "forward shared memory budget");
+
 __host__ __device__ inline int layer_k(int l) { return l == 0 ? 64 : (l == 5 ? 320 : (l == 8 ? 288 : 256)); }
 __host__ __device__ inline int layer_akg0(int l) { return l == 0 ? kExtKg : 0; }
 
@@ -58,6 +76,7 @@ struct Image {
     int64_t v2_off;               // chunk stream of the pipelined forward (mlp_tc2.cuh), in issue order
     int64_t v2_sched_off;         // tc2::Chunk[v2_chunks]
     int v2_chunks;
+    int64_t fwb_off;              // 9 bias blocks of the forward (kFwBiasBlkBytes each)
     int64_t v3_off[2];            // per-CTA-rank chunk streams of the CTA-pair forward (mlp_tc3.cuh)
     int64_t v3_sched_off;         // tc3::Chunk[v3_chunks] then int layer_start[11]
     int v3_chunks, npad2;         // npad2 = C rounded up to 32 (N of the pair's head MMA)
@@ -88,6 +107,7 @@ __host__ __device__ inline Image make_image(int ins_num) {
     im.v2_chunks = tc2::build_schedule(im.npad, nullptr, &v2_bytes);
     im.v2_off = off;         off += v2_bytes;
     im.v2_sched_off = off;   off += static_cast<int64_t>(tc2::kMaxChunks) * sizeof(tc2::Chunk);
+    im.fwb_off = off;        off += 9 * kFwBiasBlkBytes;
     im.npad2 = ((ins_num + 5) + 31) & ~31;
     uint32_t v3_bytes = 0;
     im.v3_chunks = tc3::build_schedule(im.npad2, nullptr, nullptr, &v3_bytes);
@@ -122,6 +142,14 @@ __device__ inline float logical_weight(const Params& pr, const float* scratch, i
 
 // ---- device helpers ---------------------------------------------------------------------------------------
 // mbarrier addresses (8 B each) inside the barrier block
+struct FwBars {
+    uint32_t base;
+    __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }
+    __device__ __forceinline__ uint32_t w_empty(int s) const { return base + 8 * (kFwStages + s); }
+    __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kFwStages + t); }
+    __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kFwStages + 2 + t); }
+};
+
 struct Bars {
     uint32_t base;
     __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }

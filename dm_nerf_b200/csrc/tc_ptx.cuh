@@ -73,6 +73,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
+// One lane of a CONVERGED warp (elect.sync): tcgen05.mma / commit take uniform-register operands, and inside a
+// `threadIdx.x == 0` branch the compiler cannot prove uniformity and wraps every such instruction in an R2UR +
+// BRA.U.ANY waterfall loop (~100 clk each).  Run the issue loop on the whole warp and elect the issuing lane instead.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 // ---- proxies / fences ----------------------------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -160,6 +160,7 @@ int  dmnerf_selftest_umma_rate(int n, int count, long long* out, void* stream);
  * synchronises the device): MMA issuer total / waiting for weights / waiting for activations, epilogue thread total /
  * waiting for accumulators, producer waiting for a free ring slot. */
 int  dmnerf_debug_counters(long long* host_out8);
+int  dmnerf_selftest_issue_cost(int mode, int count, long long* out2_dev, void* stream);
 /* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the forward's descriptors; bit1: in wgrad's).
  * flags < 0 only queries.  Returns the previous value. */
 int  dmnerf_debug_flags(int flags);

@@ -23,7 +23,15 @@ with torch.no_grad():
         a.record(); m.query_rays(o, d, z); b.record(); torch.cuda.synchronize()
         ts.append(a.elapsed_time(b))
 print(f"flags {flag} K {K}: ms {min(ts):.3f} (median {sorted(ts)[2]:.3f})  max|diff vs lockstep| {float((out - ref).abs().max()):.3e}")
-if flag & 8:
+if flag & 16:
+    import ctypes as C
+    buf = (C.c_longlong * 8)()
+    _lib.lib().dmnerf_debug_counters(buf)
+    pairs = (n * s / 256) / 148
+    for nm, v in zip(["issuer total", "issuer wait w_full", "issuer wait a_ready", "epi total", "epi wait acc_ready",
+                      "producer wait w_empty"], buf):
+        print(f"  {nm:24s} {v:12d}  per pair {v / pairs:10.0f}")
+elif flag & 8:
     import ctypes as C
     buf = (C.c_longlong * 8)()
     _lib.lib().dmnerf_debug_counters(buf)
