@@ -47,7 +47,7 @@ __device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
     return r;
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFwThreads, 1)
 mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const uint8_t* __restrict__ image, Image im,
                       const uint8_t* __restrict__ acts, uint8_t* __restrict__ gstash) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -59,14 +59,14 @@ mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const u
     const int C = im.ins_num + 5;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kDgStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
+        for (int s = 0; s < kDgStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 2); }
         for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 2 * kTile); ptx::mbar_init(bars.acc_ready(t), 1); }
         ptx::fence_barrier_init();
     }
     if (warp == kMmaWarp) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
     {
         const float* gb = reinterpret_cast<const float*>(image + im.bias_off) + kBiasWd;
-        for (int i = threadIdx.x; i < 256; i += kThreads) s_wd[i] = gb[i];
+        for (int i = threadIdx.x; i < 256; i += kFwThreads) s_wd[i] = gb[i];
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -95,33 +95,30 @@ mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const u
                 if (++stage == kDgStages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == kMmaWarp) {
+    } else if (warp >= kMmaWarp) {
+        // one issuer warp per tile (see mlp_tc.cu: a ring step costs the issuing thread ~300 clk of control code)
         if (lane == 0) {
-            int stage = 0; uint32_t phase = 0, a_par[2] = {0, 0};
+            const int t = warp - kMmaWarp;
+            int stage = 0; uint32_t phase = 0, a_par = 0;
             const uint32_t idesc = ptx::idesc_bf16(kTile, 256);
+            constexpr uint32_t kKg16 = kKgBytes >> 4;
+            const uint64_t desc_hi = static_cast<uint64_t>(0x4008u) << 32;       // SBO = 128 B, descriptor version 1
+            const uint32_t a_lo0 = ((sm0 + t * kDgABytes) >> 4) | (kKg16 << 16);
+            const uint32_t ring_lo = ((sm0 + kDgSmRing) >> 4) | (256u << 16);
+            const uint32_t d_tmem = tmem + t * 256;
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
                 for (int d = 0; d < kDgLayers; ++d) {
                     const int chunks = im.dg_k[d] / kChunkK;
-                    for (int c = 0; c < chunks; ++c) {
+                    uint32_t a_lo = a_lo0;
+#pragma unroll 1
+                    for (int c = 0; c < chunks; ++c, a_lo += 4 * kKg16) {
                         ptx::mbar_wait(bars.w_full(stage), phase);
+                        if (c == 0) { ptx::mbar_wait(bars.a_ready(t), a_par); a_par ^= 1; }
                         ptx::tc_fence_after();
-                        const uint32_t b_base = sm0 + kDgSmRing + stage * kStageBytes;
-#pragma unroll
-                        for (int t = 0; t < 2; ++t) {
-                            if (c == 0) {
-                                ptx::mbar_wait(bars.a_ready(t), a_par[t]);
-                                a_par[t] ^= 1;
-                                ptx::tc_fence_after();
-                            }
-                            const uint32_t a_base = sm0 + t * kDgABytes;
-#pragma unroll
-                            for (int kk = 0; kk < 2; ++kk) {
-                                const uint64_t ad = ptx::smem_desc(a_base + (c * 4 + kk * 2) * kKgBytes, kKgBytes, 128);
-                                const uint64_t bd = ptx::smem_desc(b_base + kk * 2 * (256 * 16), 256 * 16, 128);
-                                ptx::umma_bf16(tmem + t * 256, ad, bd, idesc, (c | kk) != 0);
-                            }
-                            if (c == chunks - 1) ptx::umma_commit(bars.acc_ready(t));
-                        }
+                        const uint32_t b_lo = ring_lo + stage * (kStageBytes >> 4);
+                        ptx::umma_bf16(d_tmem, desc_hi | a_lo, desc_hi | b_lo, idesc, c != 0);
+                        ptx::umma_bf16(d_tmem, desc_hi | (a_lo + 2 * kKg16), desc_hi | (b_lo + 2 * 256), idesc, 1u);
+                        if (c == chunks - 1) ptx::umma_commit(bars.acc_ready(t));
                         ptx::umma_commit(bars.w_empty(stage));
                         if (++stage == kDgStages) { stage = 0; phase ^= 1; }
                     }
@@ -622,7 +619,7 @@ int launch_mlp_bwd_bf16(const void* packed, const void* acts, const float* d_raw
     const int64_t pairs = (n_points + 255) / 256;
     const int64_t blocks = pairs * 4;
     DM_CUDA(cudaFuncSetAttribute(tcb::mlp_dgrad_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::kDgSmTotal));
-    tcb::mlp_dgrad_bf16_kernel<<<static_cast<unsigned>(pairs < sm_count ? pairs : sm_count), tc::kThreads, tcb::kDgSmTotal, st>>>(
+    tcb::mlp_dgrad_bf16_kernel<<<static_cast<unsigned>(pairs < sm_count ? pairs : sm_count), tc::kFwThreads, tcb::kDgSmTotal, st>>>(
         d_raw, n_points, static_cast<const uint8_t*>(packed), im, static_cast<const uint8_t*>(acts), gstash);
     DM_LAUNCH_CHECK("mlp_dgrad_bf16_kernel");
 
