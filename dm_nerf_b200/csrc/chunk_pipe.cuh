@@ -73,6 +73,12 @@ struct ChunkPipe {
         ++consumed;
         return tile_ptr + st * chunk_floats;
     }
+    // The chunk the NEXT acquire() will return (valid while !done()): lets the consumer start dependent global loads
+    // (e.g. the z values of that chunk) one chunk ahead.
+    __device__ __forceinline__ void peek(int64_t& ray, int& c0) const {
+        ray = ray0 + (consumed / steps) * ray_stride;
+        c0 = chunk_of(consumed) * 32;
+    }
     // Bulk-store the (modified) tile just acquired to dst; every lane must have finished writing it.
     __device__ __forceinline__ void store_tile(float* dst, const float* tile, uint32_t bytes) {
         ptx::fence_proxy_async_smem();

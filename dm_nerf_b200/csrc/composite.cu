@@ -10,6 +10,7 @@
 #include "chunk_pipe.cuh"
 
 namespace dmnerf {
+int tc_debug_flags();
 
 constexpr int kCompWarps = 8;
 
@@ -125,20 +126,22 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 // summation order per ray as composite_fwd_kernel.  Logit sums: lanes are channels for full 32-channel passes;
 // a remainder of <= 4 channels (K=32: the single "empty" class) is summed sample-parallel instead of spending a
 // whole pass on one lane.
-constexpr int kCompStages = 3;
+constexpr int kCompStages = 2;        // ring depth per warp.  Measured (tools/sweep_composite.py): resident warps matter more
+                                      // than depth -- 2 stages x 20 warps/SM beats 3 x 12 by 15-30 %, 4 stages is worse still
 constexpr int kCompBulkWarps = 4;
 
+template <int ST>
 __global__ void __launch_bounds__(kCompBulkWarps * 32)
 composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
                           int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,
                           float* __restrict__ weights, float* __restrict__ ins) {
     extern __shared__ __align__(128) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int per_warp = kCompStages * 32 * C + 32;
+    const int per_warp = ST * 32 * C + 32;
     float* ring = smem + warp * per_warp;
-    float* wbuf = ring + kCompStages * 32 * C;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp) + warp * kCompStages;
-    ChunkPipe<kCompStages> pipe;
+    float* wbuf = ring + ST * 32 * C;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp) + warp * ST;
+    ChunkPipe<ST> pipe;
     pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
               static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane);
     const int L = C - 4;
@@ -148,24 +151,41 @@ composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
 
     float carry = 1.0f, a_r = 0.f, a_g = 0.f, a_b = 0.f, a_d = 0.f, norm = 0.f;
     float acc[4] = {0.f, 0.f, 0.f, 0.f}, racc[4] = {0.f, 0.f, 0.f, 0.f};
+    // z (and the ray direction) do not come through the bulk pipe: they are loaded one chunk ahead so that their
+    // latency hides behind the current chunk's arithmetic instead of sitting between acquire() and the scan
+    float z_pre = 0.f, zn_pre = 0.f, norm_pre = 0.f;
+    auto prefetch = [&]() {
+        int64_t r2; int c2;
+        pipe.peek(r2, c2);
+        const int s2 = c2 + lane;
+        if (s2 < S) {
+            z_pre = __ldg(z + r2 * S + s2);
+            zn_pre = (s2 + 1 < S) ? __ldg(z + r2 * S + s2 + 1) : 0.f;
+        }
+        if (c2 == 0) {
+            const float dx = __ldg(rays_d + r2 * 3 + 0), dy = __ldg(rays_d + r2 * 3 + 1), dz = __ldg(rays_d + r2 * 3 + 2);
+            norm_pre = sqrtf(dx * dx + dy * dy + dz * dz);
+        }
+    };
+    if (!pipe.done()) prefetch();
     while (!pipe.done()) {
         int64_t ray; int c0;
         const float* tile = pipe.acquire(ray, c0);
-        const float* zrow = z + ray * S;
+        const float z_cur = z_pre, zn_cur = zn_pre;
         if (c0 == 0) {
-            const float dx = rays_d[ray * 3 + 0], dy = rays_d[ray * 3 + 1], dz = rays_d[ray * 3 + 2];
-            norm = sqrtf(dx * dx + dy * dy + dz * dz);
+            norm = norm_pre;
             carry = 1.0f; a_r = a_g = a_b = a_d = 0.f;
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[q] = racc[q] = 0.f;
         }
+        if (!pipe.done()) prefetch();
         const int cnt = min(32, S - c0);
         const int s = c0 + lane;
         const bool valid = lane < cnt;
         float zc = 0.f, dist = 0.f, sigma = 0.f;
         if (valid) {
-            zc = zrow[s];
-            dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            zc = z_cur;
+            dist = ((s + 1 < S) ? (zn_cur - zc) : 1e10f) * norm;
             sigma = tile[lane * C + 3];
         }
         float alpha, trans, w;
@@ -371,6 +391,7 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 // Backward, bulk-copy staged: same phases as composite_bwd_kernel, but a ray's chunks arrive through the per-warp
 // bulk-copy ring twice (forward for the recompute pass, then in reverse for the gradient pass) and every finished
 // d_raw chunk leaves with one bulk store from the tile it was built in.
+template <int ST>
 __global__ void __launch_bounds__(kCompBulkWarps * 32)
 composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
                           int64_t n, int S, int C, int flags, int ins_detach, const float* __restrict__ d_rgb,
@@ -378,14 +399,16 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
                           const float* __restrict__ d_ins, float* __restrict__ d_raw) {
     extern __shared__ __align__(128) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int per_warp = kCompStages * 32 * C + 32 + 3 * S;
+    const int per_warp = ST * 32 * C + 32 + 5 * S;
     float* ring = smem + warp * per_warp;
-    float* wbuf = ring + kCompStages * 32 * C;
+    float* wbuf = ring + ST * 32 * C;
     float* s_alpha = wbuf + 32;
     float* s_trans = s_alpha + S;
     float* s_w = s_trans + S;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp + (kCompBulkWarps * per_warp & 1)) + warp * kCompStages;
-    ChunkPipe<kCompStages> pipe;
+    float* s_z = s_w + S;
+    float* s_dist = s_z + S;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp + (kCompBulkWarps * per_warp & 1)) + warp * ST;
+    ChunkPipe<ST> pipe;
     pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
               static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane, true, true);
     const int L = C - 4;
@@ -394,27 +417,52 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
 
     float carry = 1.0f, norm = 0.f, suffix = 0.f, g_r = 0.f, g_g = 0.f, g_b = 0.f, g_d = 0.f;
     float acc[4] = {0.f, 0.f, 0.f, 0.f}, dA[4] = {0.f, 0.f, 0.f, 0.f};
+    // z, the ray direction and the per-ray output gradients do not come through the bulk pipe: z is loaded one
+    // chunk ahead (phase A only; phase C re-reads it from shared memory), the gradients at the start of the ray
+    float z_pre = 0.f, zn_pre = 0.f, norm_pre = 0.f;
+    auto prefetch = [&]() {
+        int64_t r2; int c2;
+        pipe.peek(r2, c2);
+        const int s2 = c2 + lane;
+        if (s2 < S) {
+            z_pre = __ldg(z + r2 * S + s2);
+            zn_pre = (s2 + 1 < S) ? __ldg(z + r2 * S + s2 + 1) : 0.f;
+        }
+        if (c2 == 0) {
+            const float dx = __ldg(rays_d + r2 * 3 + 0), dy = __ldg(rays_d + r2 * 3 + 1), dz = __ldg(rays_d + r2 * 3 + 2);
+            norm_pre = sqrtf(dx * dx + dy * dy + dz * dz);
+        }
+    };
+    if (!pipe.done()) prefetch();
     while (!pipe.done()) {
         int64_t ray; int c0; bool back;
         float* tile = pipe.acquire(ray, c0, &back);
-        const float* zrow = z + ray * S;
         const int cnt = min(32, S - c0);
         const int s = c0 + lane;
         const bool valid = lane < cnt;
         if (!back) {
             // ---- phase A: recompute alpha / T / w and the logit sums
+            const float z_cur = z_pre, zn_cur = zn_pre;
             if (c0 == 0) {
-                const float dx = rays_d[ray * 3 + 0], dy = rays_d[ray * 3 + 1], dz = rays_d[ray * 3 + 2];
-                norm = sqrtf(dx * dx + dy * dy + dz * dz);
+                norm = norm_pre;
                 carry = 1.0f;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) acc[q] = 0.f;
+                for (int q = 0; q < 4; ++q) {
+                    acc[q] = 0.f;
+                    const int j = lane + 32 * q;
+                    dA[q] = (need_logits && j < Lout) ? __ldg(d_ins + ray * Lout + j) : 0.f;
+                }
+                g_r = d_rgb ? __ldg(d_rgb + ray * 3 + 0) : 0.f;
+                g_g = d_rgb ? __ldg(d_rgb + ray * 3 + 1) : 0.f;
+                g_b = d_rgb ? __ldg(d_rgb + ray * 3 + 2) : 0.f;
+                g_d = d_depth ? __ldg(d_depth + ray) : 0.f;
             }
+            if (c0 + 32 < S) prefetch();                 // next chunk is still phase A of this ray
             float dist = 0.f, sigma = 0.f;
             if (valid) {
-                const float zc = zrow[s];
-                dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+                dist = ((s + 1 < S) ? (zn_cur - z_cur) : 1e10f) * norm;
                 sigma = tile[lane * C + 3];
+                s_z[s] = z_cur; s_dist[s] = dist;
             }
             float alpha, trans, w;
             scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
@@ -439,20 +487,11 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int j = lane + 32 * q;
-                    float g = 0.f;
-                    if (need_logits && j < Lout) {
-                        g = d_ins[ray * Lout + j];
-                        if (!(flags & DMNERF_COMP_RAW_INS)) {
-                            const float p = sigmoidf_ref(acc[q]);
-                            g *= p * (1.0f - p);
-                        }
+                    if (need_logits && j < Lout && !(flags & DMNERF_COMP_RAW_INS)) {
+                        const float p = sigmoidf_ref(acc[q]);
+                        dA[q] *= p * (1.0f - p);
                     }
-                    dA[q] = g;
                 }
-                g_r = d_rgb ? d_rgb[ray * 3 + 0] : 0.f;
-                g_g = d_rgb ? d_rgb[ray * 3 + 1] : 0.f;
-                g_b = d_rgb ? d_rgb[ray * 3 + 2] : 0.f;
-                g_d = d_depth ? d_depth[ray] : 0.f;
                 suffix = 0.f;
             }
             __syncwarp();
@@ -461,7 +500,7 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
         // ---- phase C (reverse): running suffix sum R_s = sum_{r>s} dw_r w_r
         float dw = 0.f, w = 0.f, alpha = 0.f, trans = 0.f, zc = 0.f, c_r = 0.f, c_g = 0.f, c_b = 0.f;
         if (valid) {
-            w = s_w[s]; alpha = s_alpha[s]; trans = s_trans[s]; zc = zrow[s];
+            w = s_w[s]; alpha = s_alpha[s]; trans = s_trans[s]; zc = s_z[s];
             c_r = sigmoidf_ref(tile[lane * C + 0]);
             c_g = sigmoidf_ref(tile[lane * C + 1]);
             c_b = sigmoidf_ref(tile[lane * C + 2]);
@@ -494,7 +533,7 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
             const float t = (1.0f - alpha) + 1e-10f;
             const float dalpha = dw * trans - after / t;
             const float sigma = tile[lane * C + 3];
-            const float dist = ((s + 1 < S) ? (zrow[s + 1] - zc) : 1e10f) * norm;
+            const float dist = s_dist[s];
             const float dsigma = (sigma > 0.f) ? dalpha * dist * (1.0f - alpha) : 0.f;
             tile[lane * C + 0] = g_r * w * c_r * (1.0f - c_r);
             tile[lane * C + 1] = g_g * w * c_g * (1.0f - c_g);
@@ -514,6 +553,7 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
             }
         }
         pipe.store_tile(d_raw + (ray * S + c0) * static_cast<int64_t>(C), tile, static_cast<uint32_t>(cnt) * C * 4);
+        if (c0 == 0 && !pipe.done()) prefetch();         // next chunk opens the next ray's phase A
         __syncwarp();
     }
     pipe.finish();
@@ -537,14 +577,25 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
             DM_CUDA(cudaGetDevice(&dev));
             DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
         }
-        const size_t smem = static_cast<size_t>(kCompBulkWarps) * ((kCompStages * 32 * c + 32) * sizeof(float) + kCompStages * 8);
+        // debug bits 8-9 (1..3 -> 2..4 stages) and 10-12 (blocks per SM) override the launch shape for tuning sweeps
+        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * 32 * c + 32) * sizeof(float) + st * 8); };
+        const int dbg = tc_debug_flags();
+        int st = kCompStages;
+        if ((dbg >> 8) & 3) st = ((dbg >> 8) & 3) + 1;
+        const size_t smem = smem_for(st);
         int per_sm = static_cast<int>((220 * 1024) / (smem + 1024));
         per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
-        DM_CUDA(cudaFuncSetAttribute(composite_fwd_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if ((dbg >> 10) & 7) per_sm = (dbg >> 10) & 7;
         const int64_t want = (n + kCompBulkWarps - 1) / kCompBulkWarps;
         const int64_t cap = static_cast<int64_t>(sm_count) * per_sm;
-        composite_fwd_bulk_kernel<<<static_cast<unsigned>(want < cap ? want : cap), kCompBulkWarps * 32, smem, as_stream(stream)>>>(
-            raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins);
+        const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
+        auto launch = [&](auto kern) {
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins);
+        };
+        if (st == 2) launch(composite_fwd_bulk_kernel<2>);
+        else if (st == 3) launch(composite_fwd_bulk_kernel<3>);
+        else launch(composite_fwd_bulk_kernel<4>);
         DM_LAUNCH_CHECK("composite_fwd_bulk_kernel");
         return DMNERF_OK;
     }
@@ -574,15 +625,26 @@ extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const floa
             DM_CUDA(cudaGetDevice(&dev));
             DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
         }
-        const size_t smem = static_cast<size_t>(kCompBulkWarps) * ((kCompStages * 32 * c + 32 + 3 * s) * sizeof(float) + kCompStages * 8) + 8;
+        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * 32 * c + 32 + 5 * s) * sizeof(float) + st * 8) + 8; };
+        const int dbg = tc_debug_flags();
+        int st = kCompStages;
+        if ((dbg >> 8) & 3) st = ((dbg >> 8) & 3) + 1;
+        const size_t smem = smem_for(st);
         if (smem <= 220 * 1024) {
             int per_sm = static_cast<int>((220 * 1024) / (smem + 1024));
             per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
-            DM_CUDA(cudaFuncSetAttribute(composite_bwd_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if ((dbg >> 10) & 7) per_sm = (dbg >> 10) & 7;
             const int64_t want = (n + kCompBulkWarps - 1) / kCompBulkWarps;
             const int64_t cap = static_cast<int64_t>(sm_count) * per_sm;
-            composite_bwd_bulk_kernel<<<static_cast<unsigned>(want < cap ? want : cap), kCompBulkWarps * 32, smem, as_stream(stream)>>>(
-                raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins, d_raw);
+            const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
+            auto launch = [&](auto kern) {
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb,
+                                                                             d_depth, d_weights, d_ins, d_raw);
+            };
+            if (st == 2) launch(composite_bwd_bulk_kernel<2>);
+            else if (st == 3) launch(composite_bwd_bulk_kernel<3>);
+            else launch(composite_bwd_bulk_kernel<4>);
             DM_LAUNCH_CHECK("composite_bwd_bulk_kernel");
             return DMNERF_OK;
         }
