@@ -52,21 +52,41 @@ penalizer_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         const float invC = 1.0f / static_cast<float>(C);
         const float* row = raw + ray * S * static_cast<int64_t>(C);
         const int total = S * C;
-        for (int i = lane; i < total; i += 32) {
-            const int s = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
-            const int j = i - s * C;
-            if (j < 4) continue;
-            // samples behind the surface band carry zero weight in both terms, and inside the band only the
-            // "empty" channel counts: those logits are never loaded (about half of the bytes for a mid-range depth)
-            const float wb = cb[s];
-            if (wb == 0.f && (j != C - 1 || cm[s] == 0.f)) continue;
-            const float p = sigmoidf_ref(__ldg(row + i));
-            const float l_not = -logf(1.0f - p + 1e-8f);
-            if (j == C - 1) {
-                sb += -logf(p + 1e-8f) * cb[s];
-                sm += l_not * cm[s];
-            } else {
-                sb += l_not * cb[s];
+        // four independent elements per lane and trip: their loads are issued before any of the transcendental
+        // chains starts (memory-level parallelism x4; a single dependent load per trip left the kernel latency bound)
+        constexpr int U = 4;
+        for (int base = 0; base < total; base += 32 * U) {
+            float x[U], wb[U], wm[U];
+            bool last[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = base + u * 32 + lane;
+                wb[u] = 0.f; wm[u] = 0.f; x[u] = 0.f; last[u] = false;
+                if (i < total) {
+                    const int s = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
+                    const int j = i - s * C;
+                    // samples behind the surface band carry zero weight in both terms, and inside the band only the
+                    // "empty" channel counts: those logits are never loaded (about half of the bytes for a mid-range depth)
+                    if (j >= 4) {
+                        last[u] = j == C - 1;
+                        wb[u] = cb[s];
+                        wm[u] = last[u] ? cm[s] : 0.f;
+                        if (wb[u] != 0.f || wm[u] != 0.f) x[u] = __ldg(row + i);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (wb[u] != 0.f || wm[u] != 0.f) {
+                    const float p = sigmoidf_ref(x[u]);
+                    const float l_not = -logf(1.0f - p + 1e-8f);
+                    if (last[u]) {
+                        sb += -logf(p + 1e-8f) * wb[u];
+                        sm += l_not * wm[u];
+                    } else {
+                        sb += l_not * wb[u];
+                    }
+                }
             }
         }
     }
@@ -114,18 +134,40 @@ penalizer_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     const float* row = raw + ray * S * static_cast<int64_t>(C);
     float* out = d_raw + ray * S * static_cast<int64_t>(C);
     const int total = S * C;
-    for (int i = lane; i < total; i += 32) {
-        const int s = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
-        const int j = i - s * C;
-        float v = 0.f;
-        if (j >= 4 && (cb[s] != 0.f || (j == C - 1 && cm[s] != 0.f))) {
-            const float p = sigmoidf_ref(__ldg(row + i));
-            const float dp = p * (1.0f - p);
-            const float d_not = dp / (1.0f - p + 1e-8f);          // d/dx of -log(1-p+1e-8)
-            if (j == C - 1) v = cb[s] * (-dp / (p + 1e-8f)) + cm[s] * d_not;
-            else            v = cb[s] * d_not;
+    constexpr int U = 4;
+    for (int base = 0; base < total; base += 32 * U) {
+        float x[U], wb[U], wm[U];
+        bool last[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * 32 + lane;
+            wb[u] = 0.f; wm[u] = 0.f; x[u] = 0.f; last[u] = false;
+            if (i < total) {
+                const int s = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
+                const int j = i - s * C;
+                if (j >= 4) {
+                    last[u] = j == C - 1;
+                    wb[u] = cb[s];
+                    wm[u] = last[u] ? cm[s] : 0.f;
+                    if (wb[u] != 0.f || wm[u] != 0.f) x[u] = __ldg(row + i);
+                }
+            }
         }
-        out[i] = v;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * 32 + lane;
+            if (i < total) {
+                float v = 0.f;
+                if (wb[u] != 0.f || wm[u] != 0.f) {
+                    const float p = sigmoidf_ref(x[u]);
+                    const float dp = p * (1.0f - p);
+                    const float d_not = dp / (1.0f - p + 1e-8f);          // d/dx of -log(1-p+1e-8)
+                    if (last[u]) v = wb[u] * (-dp / (p + 1e-8f)) + wm[u] * d_not;
+                    else         v = wb[u] * d_not;
+                }
+                out[i] = v;
+            }
+        }
     }
 }
 
