@@ -295,12 +295,15 @@ def run_gpu(args):
     rays_per_launch = min(args.chunk, N_RAYS)
     roofline = None
     if n_launch:
+        traffic = ncu_traffic_bytes() if (mode == "bf16" and rays_per_launch == 32768 and K_INS == 32) else None
         # achieved = algorithmic FLOPs per launch / mean launch duration (fine pass: 192 points per ray)
         flops_total = 2.0 * MACS_PER_POINT * (SC + NIMP) * N_RAYS * args.steps
         achieved = flops_total / (ms_kernel / 1000) / 1e12
         peak = peaks.get("bf16_tflops_sustained", 1400.0)
         roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                    "traffic": None, "kernel": name, "launches": n_launch, "ms_per_launch": ms_kernel / n_launch,
+                    "traffic": traffic, "traffic_source": "profiles/r01_render_kernels_metrics.csv (ncu --set full, "
+                    "dram__bytes_read.sum + dram__bytes_write.sum of the fine-pass launch)" if traffic else None,
+                    "kernel": name, "launches": n_launch, "ms_per_launch": ms_kernel / n_launch,
                     "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback",
                     "kernel_share_of_step": ms_kernel / (ms_step * args.steps)}
     stage_ms = {k: round(v[1] / args.steps, 3) for k, v in totals.items()}
@@ -338,6 +341,28 @@ def run_gpu(args):
         }))
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic_bytes():
+    """DRAM bytes per launch of the dominant kernel (fine-pass MLP forward, 32768 rays x 192 points, K=32) from the
+    committed ncu --set full capture of this same workload; None when the summary is absent."""
+    try:
+        rows = {}
+        with open(os.path.join(ROOT, "profiles", "r01_render_kernels_metrics.csv")) as f:
+            for line in f:
+                if line.startswith("#"):
+                    continue
+                parts = line.rstrip("\n").split(",")
+                rows[parts[0]] = parts[1:]
+        names, dur = rows["Kernel Name"][1:], [float(x) for x in rows["gpu__time_duration.sum"][1:]]
+        idx = max((i for i, nm in enumerate(names) if "mlp_fwd_bf16" in nm), key=lambda i: dur[i])
+        scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+        total = 0.0
+        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            total += float(rows[key][1:][idx]) * scale[rows[key][0]]
+        return total
+    except Exception:
+        return None
 
 
 def main():
