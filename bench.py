@@ -142,14 +142,14 @@ def run_reference(args):
     ms = 1000 * sum(times) / len(times)
     val = n / (ms / 1000)
     sample = f"{n} rays of the 640x480 frame per step (oracle port, torch CPU fp32, {cores} threads)"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "rays/sec render (64+128 samples/ray)", "value": val, "unit": "rays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "DM-SR full-image render 640x480, 64+128 samples/ray, K=32 (bounded sample)"},
         "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def train_leg(args, torch, dist, dev, rank, world):
@@ -325,7 +325,7 @@ def run_gpu(args):
         total_rays = N_RAYS * world
         h2d = rays_host.numel() * 4
         d2h = sum(v.numel() * v.element_size() for v in host_out.values())
-        print(json.dumps({
+        emit({
             "metric": "rays/sec render (64+128 samples/ray)", "value": total_rays / (ms_step / 1000), "unit": "rays/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -338,7 +338,7 @@ def run_gpu(args):
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
             "stage_ms_per_step": stage_ms, "train": train,
-        }))
+        })
     if world > 1:
         dist.destroy_process_group()
 
@@ -365,6 +365,28 @@ def ncu_traffic_bytes():
         return None
 
 
+_JSON_FD = None
+
+
+def quiet_stdout():
+    """Send everything libraries write to fd 1 (NCCL prints its version banner there) to stderr; the one JSON line
+    goes to the saved descriptor through emit()."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        os.write(1, line)
+    else:
+        os.write(_JSON_FD, line)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -375,6 +397,8 @@ def main():
     ap.add_argument("--chunk", type=int, default=32768)
     ap.add_argument("--no-train", action="store_true", help="skip the training-throughput leg")
     args = ap.parse_args()
+    if not (args.gpus > 1 and int(os.environ.get("WORLD_SIZE", "1")) == 1 and args.impl != "reference"):
+        quiet_stdout()                                  # (the torchrun relaunch path leaves fd 1 to its children)
     if args.impl == "reference":
         return run_reference(args)
     if args.mode == "auto":
