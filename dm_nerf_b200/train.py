@@ -10,7 +10,7 @@ from typing import Dict, Optional
 import torch
 
 from . import parallel
-from .networks.evaluator import img2mse, ins_criterion
+from .networks.evaluator import img2mse, ins_criterion_multi
 from .networks.helpers import get_select_full, z_val_sample
 from .networks.penalizer import ins_penalizer
 from .networks.render import dm_nerf
@@ -29,7 +29,10 @@ class TrainStep:
         self.args.is_train, self.args.N_ins = True, None
         self.penalize = penalize
         self.params = list(model_coarse.parameters()) + list(model_fine.parameters())
-        self.opt = optimizer or torch.optim.Adam(self.params, lr=args.lrate, betas=(0.9, 0.999))
+        # train_dmsr.py:127-128 builds torch.optim.Adam(params, lr, betas=(0.9, 0.999)); fused=True is the same update
+        # in one launch for all 60 tensors instead of one foreach chain per step (0.6 -> 0.1 ms of host time)
+        self.opt = optimizer or torch.optim.Adam(self.params, lr=args.lrate, betas=(0.9, 0.999),
+                                                 fused=self.params[0].is_cuda)
         self.z_coarse = z_val_sample(args.N_train, args.near, args.far, args.N_samples)     # train_dmsr.py:22
         self.flat = None
         self.iteration = 0
@@ -39,13 +42,15 @@ class TrainStep:
         target_c, target_i, rays = get_select_full(image, pose, self.K, labels, a.N_train)
         info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a)
         rgb_loss = img2mse(info["rgb_coarse"], target_c) + img2mse(info["rgb_fine"], target_c)
-        ins_loss = ins_criterion(info["ins_coarse"], target_i, a.ins_num)[0] + \
-            ins_criterion(info["ins_fine"], target_i, a.ins_num)[0]
-        total = rgb_loss + ins_loss
         emptiness = None
         if self.penalize:
+            # enqueued BEFORE the instance loss so the device has work while the host runs the Hungarian assignment
             emptiness = ins_penalizer(info["raw_coarse"], info["z_vals_coarse"], info["depth_coarse"], rays[1], a) + \
                 ins_penalizer(info["raw_fine"], info["z_vals_fine"], info["depth_fine"], rays[1], a)
+        ins_c, ins_f = ins_criterion_multi([info["ins_coarse"], info["ins_fine"]], target_i, a.ins_num)
+        ins_loss = ins_c[0] + ins_f[0]
+        total = rgb_loss + ins_loss
+        if emptiness is not None:
             total = total + emptiness
         self.opt.zero_grad(set_to_none=False)
         total.backward()

@@ -195,3 +195,13 @@ def test_host_ins_criterion_vs_golden(golden, tag):
     got = np.array([float(o.detach()) for o in out], dtype=np.float32)
     np.testing.assert_allclose(got, g["losses"], rtol=2e-6, atol=2e-7)
     np.testing.assert_allclose(pred.grad.numpy(), g["grad"], rtol=1e-4, atol=1e-8)
+    # the batched form TrainStep uses (shared one-hot, one host round trip) gives the same numbers per prediction
+    pred2 = torch.from_numpy(g["pred"]).requires_grad_(True)
+    pred3 = torch.from_numpy(g["pred"][::-1].copy()).requires_grad_(True)          # a second, different prediction
+    multi = ev.ins_criterion_multi([pred2, pred3], torch.from_numpy(g["labels"]), int(g["ins_num"]))
+    multi[0][0].backward()
+    got2 = np.array([float(o.detach()) for o in multi[0]], dtype=np.float32)
+    np.testing.assert_allclose(got2, g["losses"], rtol=2e-6, atol=2e-7)
+    np.testing.assert_allclose(pred2.grad.numpy(), g["grad"], rtol=1e-4, atol=1e-8)
+    single = ev.ins_criterion(pred3.detach(), torch.from_numpy(g["labels"]), int(g["ins_num"]))
+    np.testing.assert_allclose(float(multi[1][0].detach()), float(single[0]), rtol=2e-6)
