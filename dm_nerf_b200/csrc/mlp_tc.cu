@@ -452,6 +452,7 @@ umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, i
 
 int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16_v3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int launch_mlp_bf16_v4(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
     // debug bit2 selects the pipelined variant (mlp_tc2.cu).  It is correct (same parity tests) but not faster:
@@ -459,6 +460,7 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
     // once the epilogue's stores overlap them (measured 7.06 ms vs 6.92 ms per 32768x192 points); see DESIGN.md.
     if (g_tc_debug_flags & 4) return launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st);
     if (g_tc_debug_flags & 8) return launch_mlp_bf16_v3(in, packed, ins_num, raw_out, stash, st);
+    if (g_tc_debug_flags & 32) return launch_mlp_bf16_v4(in, packed, ins_num, raw_out, stash, st);
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;

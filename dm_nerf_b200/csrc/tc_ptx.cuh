@@ -205,6 +205,14 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Fire-and-forget signal to an mbarrier in another CTA of the cluster: an asynchronous 4-byte store whose completion
+// counts 4 bytes on the remote barrier's tx-count.  Unlike mbarrier.arrive.release.cluster (measured: ~800 clk during
+// which the issuing lane is blocked) the issuing thread does not wait for the round trip.
+__device__ __forceinline__ void st_async_signal(uint32_t cluster_data_addr, uint32_t cluster_bar_addr, uint32_t value) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(cluster_data_addr),
+                 "r"(value), "r"(cluster_bar_addr)
+                 : "memory");
+}
 __device__ __forceinline__ void tmem_alloc2(uint32_t slot_smem, uint32_t cols) {   // whole warp, same warp id in both CTAs
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");

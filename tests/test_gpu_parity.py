@@ -551,10 +551,11 @@ def test_ins_branch_is_detached_from_trunk_bf16():
         assert touched == name.startswith("ins_"), name
 
 
-@pytest.mark.parametrize("flag,n_rays,k", [(4, 37, 32), (8, 37, 32), (8, 1500, 93), (8, 3, 1)])
+@pytest.mark.parametrize("flag,n_rays,k", [(4, 37, 32), (8, 37, 32), (8, 1500, 93), (8, 3, 1),
+                                           (32, 37, 32), (32, 1500, 93), (32, 3, 1)])
 def test_mlp_bf16_pipelined_variant_matches_lockstep(flag, n_rays, k):
-    """The pipelined forward (mlp_tc2.cu, debug bit 2) and the CTA-pair forward (mlp_tc3.cu, debug bit 3) compute the
-    same network as the lockstep kernel; the only numeric difference is the bias entering through the GEMM as a
+    """The pipelined forward (mlp_tc2.cu, debug bit 2) and the CTA-pair forwards (mlp_tc3.cu, debug bit 3; mlp_tc4.cu,
+    debug bit 5) compute the same network as the default kernel; the only numeric difference is the bias entering through the GEMM as a
     bf16 hi+lo pair."""
     from dm_nerf_b200 import _lib
     m = make_model(k, 4)

@@ -31,6 +31,14 @@ if flag & 16:
     for nm, v in zip(["issuer total", "issuer wait w_full", "issuer wait a_ready", "epi total", "epi wait acc_ready",
                       "producer wait w_empty"], buf):
         print(f"  {nm:24s} {v:12d}  per pair {v / pairs:10.0f}")
+elif flag & 32:
+    import ctypes as C
+    buf = (C.c_longlong * 8)()
+    _lib.lib().dmnerf_debug_counters(buf)
+    duos = (n * s / 256) / 74
+    for nm, v in zip(["issuer total", "issuer wait w_full", "epi signalling", "issuer wait a_ready", "epi total",
+                      "epi wait acc_ready", "producer wait w_empty", "epi ldtm+wait"], buf):
+        print(f"  {nm:24s} {v:12d}  per duo {v / duos:10.0f}")
 elif flag & 8:
     import ctypes as C
     buf = (C.c_longlong * 8)()
