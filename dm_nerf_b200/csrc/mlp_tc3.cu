@@ -12,9 +12,10 @@
 //     is LDTM -> relu+pack -> STS.128.
 // Roles per CTA (18 warps): warps 0-7 epilogue of tile X, 8-15 of tile Y, warp 16 weight producer (this CTA's chunk
 // halves), warp 17 = MMA issuer in the leader CTA (rank 0) / "chunk landed" relay in the peer CTA.
-// Barriers (same offsets in both CTAs): w_full[s] local TMA; peer_full[s] (leader only) arrived remotely by the peer's
-// relay; w_empty[s] and acc_ready[t] by multicast tcgen05.commit; a_ready[t] (leader only) one arrival per epilogue
-// warp of tile t from BOTH CTAs (remote arrivals through mapa).
+// Barriers (same offsets in both CTAs): w_full[s] local TMA bytes, plus -- in the leader -- 4 bytes stored asynchronously
+// by the peer's relay when ITS half has landed; w_empty[s] and acc_ready[t] by multicast tcgen05.commit; a_ready[t]
+// (leader only) one pending arrival (the issuer's own expect_tx, re-armed after every wait) + 4 bytes per epilogue warp
+// of tile t from BOTH CTAs (st.async ... mbarrier::complete_tx; a remote mbarrier.arrive blocks the lane ~800 clk).
 #include "mlp_tc_common.cuh"
 
 namespace dmnerf {
@@ -23,14 +24,17 @@ namespace tc3 {
 using namespace tc;
 
 constexpr int kSm3A = 0;                                        // 2 tiles x 40 k-groups x 2048 B
-constexpr int kSm3Ones = 2 * kABytes;                           // 163,840
-constexpr int kSm3Ring = kSm3Ones + 2 * kKgBytes;               // 167,936
-constexpr int kSm3Recs = kSm3Ring + kStagesV3 * kSlotBytes;     // 217,088: uint4 per chunk (issuer), then Chunk table
+constexpr int kSm3Ones = 2 * kABytes;                           // 163,840: one 128-byte core matrix (descriptor LBO = SBO = 0)
+constexpr int kSm3Ring = kSm3Ones + 128;
+constexpr int kSm3Recs = kSm3Ring + kStagesV3 * kSlotBytes;     // uint4 per chunk (issuer), then Chunk table
 constexpr int kSm3Sched = kSm3Recs + kMaxChunks * 16;
 constexpr int kSm3Misc = kSm3Sched + kMaxChunks * 12 + 64;      // layer_start[11] | T9 bias (128) | w_density (256) | b_density
 constexpr int kSm3Dens = kSm3Misc + (16 + 128 + 256 + 4) * 4;
-constexpr int kSm3Bar = kSm3Dens + 2 * kTile * 4;
+constexpr int kSm3Sig = kSm3Dens + 2 * kTile * 4;               // landing slots of the async-store signals: [2 CTAs][16 warps] + ring
+constexpr int kSm3Gen = kSm3Sig + (2 * kEpiWarps + kStagesV3 + 1) * 4;   // per ring stage: how many of its uses have been consumed
+constexpr int kSm3Bar = kSm3Gen + (kStagesV3 + 1) * 4;
 constexpr int kSm3Total = kSm3Bar + 8 * (3 * kStagesV3 + 4) + 16;
+constexpr int kSigBytes3 = kEpiWarps * 4;                       // 8 warps per tile x 2 CTAs x 4 bytes complete one a_ready phase
 static_assert(sizeof(Chunk) == 12, "schedule entry size");
 static_assert(kSm3Total <= 227 * 1024, "shared memory budget");
 
@@ -87,6 +91,12 @@ int pack_v3(const float* const* params, int ins_num, void* packed, cudaStream_t 
 // 2 wait peer_full, 3 wait a_ready | epilogue warp 0: 4 total, 5 wait acc_ready | producer: 6 wait w_empty
 __device__ long long g_dbg3[8];
 
+// One issuer warp per tile (true) or one for both (false).  Two issuers need the ring-order guard below (an mbarrier
+// parity wait cannot tell "this use of the stage" from "the use before the previous one"; without the guard the
+// second issuer runs through a stage that has not been loaded yet and the launch faults).  Measured: 7.0 ms with one
+// issuer, 7.7 ms with two (the guard + spills cost more than the parallel issue gains), so one it is.
+constexpr bool kTwoIssuers = false;
+
 struct Bars3 {
     uint32_t base;
     __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }
@@ -96,15 +106,18 @@ struct Bars3 {
     __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (3 * kStagesV3 + 2 + t); }
 };
 
-__device__ __forceinline__ void warp_arrive_leader(uint32_t bar_local, int lane) {
+// "this warp's share of tile t's operand is in shared memory": a 4-byte asynchronous store onto the tx-count of the
+// leader's a_ready[t] (armed by the issuer with expect_tx), not a remote mbarrier.arrive -- that one blocks the
+// issuing lane for ~800 clk (measured in mlp_tc4).
+__device__ __forceinline__ void warp_signal_leader(uint32_t sig_remote, uint32_t bar_remote, int lane) {
     ptx::fence_proxy_async_smem();
     ptx::tc_fence_before();
     __syncwarp();
-    if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(bar_local, 0));
+    if (lane == 0) ptx::st_async_signal(sig_remote, bar_remote, 1u);
 }
 
 template <bool kStash>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwThreads, 1)
 mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out,
                        uint8_t* __restrict__ stash) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -122,20 +135,20 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
     const int n_chunks = im.v3_chunks;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStagesV3; ++s) {
-            ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); ptx::mbar_init(bars.peer_full(s), 1);
-        }
-        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 16); ptx::mbar_init(bars.acc_ready(t), 1); }
+        for (int s = 0; s < kStagesV3; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
+        for (int t = 0; t < 2; ++t) { ptx::mbar_init(bars.a_ready(t), 1); ptx::mbar_init(bars.acc_ready(t), 1); }
         ptx::fence_barrier_init();
+        for (int t = 0; t < 2; ++t) ptx::mbar_arrive_expect_tx(bars.a_ready(t), kSigBytes3);      // arm phase 0 (used in the leader)
+        for (int i = 0; i < kStagesV3; ++i) reinterpret_cast<volatile uint32_t*>(smem + kSm3Gen)[i] = 0;
     }
     if (warp == kMmaWarp) ptx::tmem_alloc2(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
     {
         const Chunk* gc = reinterpret_cast<const Chunk*>(image + im.v3_sched_off);
         const uint32_t* gs = reinterpret_cast<const uint32_t*>(gc);
         uint32_t* ss = reinterpret_cast<uint32_t*>(smem + kSm3Sched);
-        for (int i = threadIdx.x; i < n_chunks * 3; i += kThreads) ss[i] = gs[i];
+        for (int i = threadIdx.x; i < n_chunks * 3; i += kFwThreads) ss[i] = gs[i];
         uint4* rr = reinterpret_cast<uint4*>(smem + kSm3Recs);
-        for (int i = threadIdx.x; i < n_chunks; i += kThreads) {
+        for (int i = threadIdx.x; i < n_chunks; i += kFwThreads) {
             const Chunk ck = gc[i];
             rr[i] = make_uint4(static_cast<uint32_t>(ck.a_kg) * (kKgBytes >> 4),
                                ck.flags | (static_cast<uint32_t>(ck.ksteps) << 8) | (static_cast<uint32_t>(ck.rows) << 16),
@@ -143,11 +156,11 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
         }
         const int* gls = reinterpret_cast<const int*>(image + im.v3_sched_off + kMaxChunks * sizeof(Chunk));
         int* sls = reinterpret_cast<int*>(smem + kSm3Misc);
-        for (int i = threadIdx.x; i < 11; i += kThreads) sls[i] = gls[i];
+        for (int i = threadIdx.x; i < 11; i += kFwThreads) sls[i] = gls[i];
         const float* gb = reinterpret_cast<const float*>(image + im.bias_off);
-        for (int i = threadIdx.x; i < 128 + 256 + 1; i += kThreads) s_misc[i] = gb[kBiasT9 + i];
+        for (int i = threadIdx.x; i < 128 + 256 + 1; i += kFwThreads) s_misc[i] = gb[kBiasT9 + i];
         uint32_t* ones = reinterpret_cast<uint32_t*>(smem + kSm3Ones);
-        for (int i = threadIdx.x; i < 2 * kKgBytes / 4; i += kThreads) ones[i] = (i < kKgBytes / 4 && (i & 3) == 0) ? 0x3F803F80u : 0u;
+        for (int i = threadIdx.x; i < 32; i += kFwThreads) ones[i] = (i & 3) == 0 ? 0x3F803F80u : 0u;
     }
     ptx::fence_proxy_async_smem();
     ptx::tc_fence_before();
@@ -171,7 +184,8 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
                             const long long w0 = clock64();
                             ptx::mbar_wait(bars.w_empty(stage), phase ^ 1);
                             dbg_w += clock64() - w0;
-                            ptx::mbar_arrive_expect_tx(bars.w_full(stage), bytes);
+                            // the leader's barrier also counts the peer's 4-byte "my half has landed" store
+                            ptx::mbar_arrive_expect_tx(bars.w_full(stage), bytes + (rank == 0 ? 4u : 0u));
                             ptx::bulk_g2s(sm0 + kSm3Ring + stage * kSlotBytes, src + ck.off, bytes, bars.w_full(stage));
                             if (++stage == kStagesV3) { stage = 0; phase ^= 1; }
                         }
@@ -184,62 +198,89 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
                 if (++stage == kStagesV3) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == kMmaWarp) {
+    } else if (warp >= kMmaWarp) {
         if (lane == 0 && rank == 0) {
-            // ===== MMA issuer (leader CTA): pair MMAs, tiles X and Y alternating layer by layer =====
-            uint32_t stage = 0, phase = 0, a_par[2] = {0, 0};
-            long long dbg_f = 0, dbg_p = 0, dbg_a = 0;
+            // ===== MMA issuers (leader CTA): warp 17 drives tile X, warp 18 tile Y.  The ring carries, per layer, the
+            // chunks of X's pass and then the chunks of Y's pass; each issuer consumes only its own slots. =====
+            if (!kTwoIssuers && warp != kMmaWarp) goto issuers_done;
+            {
+            const int t_first = kTwoIssuers ? warp - kMmaWarp : 0, t_last = kTwoIssuers ? t_first : 1;
+            uint32_t a_par2[2] = {0, 0};
+            long long dbg_f = 0, dbg_a = 0;
             const long long dbg_start = clock64();
             const uint32_t lbo_a = static_cast<uint32_t>(kKgBytes >> 4) << 16;
-            const uint32_t a_base_lo[2] = {((sm0 + kSm3A) >> 4) | lbo_a, ((sm0 + kSm3A + kABytes) >> 4) | lbo_a};
-            const uint32_t ones_lo = ((sm0 + kSm3Ones) >> 4) | lbo_a;
+            const uint64_t ones_d = (static_cast<uint64_t>(0x4000u) << 32) | ((sm0 + kSm3Ones) >> 4);
             const uint32_t ring_lo = (sm0 + kSm3Ring) >> 4;
             const uint64_t desc_hi = static_cast<uint64_t>(0x4008u) << 32;       // SBO = 128 B, descriptor version 1
+            volatile uint32_t* gen = reinterpret_cast<volatile uint32_t*>(smem + kSm3Gen);
+            uint32_t g = 0;                                                       // ring slots handed out so far
             for (int64_t quad = cluster_id; quad < n_quads; quad += n_clusters) {
                 for (int l = 0; l < kLayers; ++l) {
-#pragma unroll
-                    for (int t = 0; t < 2; ++t) {
+                    const int c0 = layer_start[l], c1 = layer_start[l + 1];
+                    const uint32_t g_layer = g;
+                    g += 2 * (c1 - c0);
+                  for (int t = t_first; t <= t_last; ++t) {
+                    const uint32_t a_base_lo = ((sm0 + kSm3A + t * kABytes) >> 4) | lbo_a;
+                    const uint32_t d = tmem + t * 256;
+                    uint32_t& a_par = a_par2[t];
+                    const uint32_t gi = g_layer + t * (c1 - c0);
+                    uint32_t stage = gi % kStagesV3, use = gi / kStagesV3, phase = use & 1u;
 #pragma unroll 1
-                        for (int c = layer_start[l]; c < layer_start[l + 1]; ++c) {
-                            const uint4 r = recs[c];
-                            const long long w0 = clock64();
-                            ptx::mbar_wait(bars.w_full(stage), phase);
-                            const long long w1 = clock64();
-                            ptx::mbar_wait(bars.peer_full(stage), phase);
-                            const long long w2 = clock64();
-                            if (r.y & kFirst) { ptx::mbar_wait(bars.a_ready(t), a_par[t]); a_par[t] ^= 1; }
-                            dbg_f += w1 - w0; dbg_p += w2 - w1; dbg_a += clock64() - w2;
-                            ptx::tc_fence_after();
-                            const uint32_t nh = r.y >> 16, ksteps = (r.y >> 8) & 15;
-                            const uint32_t a_lo = (r.y & kOnes) ? ones_lo : a_base_lo[t] + r.x;
-                            const uint32_t b_lo = ring_lo + stage * (kSlotBytes >> 4) + (nh << 16);
-                            const uint32_t d = tmem + t * 256;
-                            ptx::umma2_bf16(d, desc_hi | a_lo, desc_hi | b_lo, r.z, (r.y & kFirst) ? 0u : 1u);
-                            if (ksteps > 1) {
-                                ptx::umma2_bf16(d, desc_hi | (a_lo + 2 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 2), r.z, 1u);
-                                if (ksteps > 2) {
-                                    ptx::umma2_bf16(d, desc_hi | (a_lo + 4 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 4), r.z, 1u);
-                                    ptx::umma2_bf16(d, desc_hi | (a_lo + 6 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 6), r.z, 1u);
-                                }
+                    for (int c = c0; c < c1; ++c) {
+                        const uint4 r = recs[c];
+                        const long long w0 = clock64();
+                        if (kTwoIssuers) {
+                            // a parity wait can only tell "this use" from "the previous use": the other issuer may still
+                            // be waiting for the previous use of this stage, so queue up behind it first
+                            uint32_t spins = 0;
+                            while (gen[stage] != use) {
+                                if (++spins > (1u << 24)) { printf("dmnerf: ring order timeout (stage %u use %u)\n", stage, use); __trap(); }
                             }
-                            if (r.y & kLast) ptx::umma_commit2(bars.acc_ready(t), 3);
-                            ptx::umma_commit2(bars.w_empty(stage), 3);
-                            if (++stage == kStagesV3) { stage = 0; phase ^= 1; }
                         }
+                        ptx::mbar_wait(bars.w_full(stage), phase);
+                        if (kTwoIssuers) gen[stage] = use + 1;
+                        const long long w1 = clock64();
+                        if (r.y & kFirst) {
+                            ptx::mbar_wait(bars.a_ready(t), a_par);
+                            a_par ^= 1;
+                            ptx::mbar_arrive_expect_tx(bars.a_ready(t), kSigBytes3);    // arm the next phase
+                        }
+                        dbg_f += w1 - w0; dbg_a += clock64() - w1;
+                        ptx::tc_fence_after();
+                        const uint32_t nh = r.y >> 16, ksteps = (r.y >> 8) & 15;
+                        const uint32_t b_lo = ring_lo + stage * (kSlotBytes >> 4) + (nh << 16);
+                        if (r.y & kOnes) {
+                            ptx::umma2_bf16(d, ones_d, desc_hi | b_lo, r.z, 1u);
+                        } else {
+                            const uint32_t a_lo = a_base_lo + r.x;
+                            ptx::umma2_bf16(d, desc_hi | a_lo, desc_hi | b_lo, r.z, (r.y & kFirst) ? 0u : 1u);
+                            ptx::umma2_bf16(d, desc_hi | (a_lo + 2 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 2), r.z, 1u);
+                            if (ksteps > 2) {
+                                ptx::umma2_bf16(d, desc_hi | (a_lo + 4 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 4), r.z, 1u);
+                                ptx::umma2_bf16(d, desc_hi | (a_lo + 6 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 6), r.z, 1u);
+                            }
+                        }
+                        if (r.y & kLast) ptx::umma_commit2(bars.acc_ready(t), 3);
+                        ptx::umma_commit2(bars.w_empty(stage), 3);
+                        if (++stage == kStagesV3) { stage = 0; phase ^= 1; ++use; }
                     }
+                  }
                 }
             }
-            if (blockIdx.x == 0) { g_dbg3[0] = clock64() - dbg_start; g_dbg3[1] = dbg_f; g_dbg3[2] = dbg_p; g_dbg3[3] = dbg_a; }
-        } else if (lane == 0) {
-            // ===== relay (peer CTA): tell the leader's issuer that this CTA's half of a chunk has landed =====
+            if (blockIdx.x == 0 && t_first == 0) { g_dbg3[0] = clock64() - dbg_start; g_dbg3[1] = dbg_f; g_dbg3[2] = 0; g_dbg3[3] = dbg_a; }
+            }
+            issuers_done:;
+        } else if (lane == 0 && warp == kMmaWarp) {
+            // ===== relay (peer CTA): "my half of this chunk has landed" -> 4 bytes on the leader's w_full tx-count =====
             uint32_t stage = 0, phase = 0;
-            const uint32_t remote0 = ptx::mapa(bars.peer_full(0), 0);
+            const uint32_t remote_bar0 = ptx::mapa(bars.w_full(0), 0);
+            const uint32_t remote_sig0 = ptx::mapa(sm0 + kSm3Sig + 2 * kEpiWarps * 4, 0);
             for (int64_t quad = cluster_id; quad < n_quads; quad += n_clusters) {
                 for (int l = 0; l < kLayers; ++l) {
                     const int cnt = 2 * (layer_start[l + 1] - layer_start[l]);
                     for (int c = 0; c < cnt; ++c) {
                         ptx::mbar_wait(bars.w_full(stage), phase);
-                        ptx::mbar_arrive_cluster(remote0 + 8 * stage);
+                        ptx::st_async_signal(remote_sig0 + 4 * stage, remote_bar0 + 8 * stage, 1u);
                         if (++stage == kStagesV3) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -253,6 +294,8 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
         float* stage_out = reinterpret_cast<float*>(smem + kSm3A + t * kABytes);
         float* dens_part = reinterpret_cast<float*>(smem + kSm3Dens) + t * kTile;
         const float* s_wd = s_misc + 128;
+        const uint32_t sig_remote = ptx::mapa(sm0 + kSm3Sig + (rank * kEpiWarps + warp) * 4, 0);
+        const uint32_t bar_remote = ptx::mapa(bars.a_ready(t), 0);
         uint32_t acc_par = 0;
         long long dbg_acc = 0;
         const long long dbg_start = clock64();
@@ -283,7 +326,7 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
             } else {
                 row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, half * 4, half * 4 + 4, gst, kStPos);
             }
-            warp_arrive_leader(bars.a_ready(t), lane);
+            warp_signal_leader(sig_remote, bar_remote, lane);
 
             float dens = 0.f;
             for (int l = 0; l < kLayers - 1; ++l) {
@@ -322,7 +365,7 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
                     }
                     if (half == 1) dens_part[row] = dens;
                 }
-                warp_arrive_leader(bars.a_ready(t), lane);
+                warp_signal_leader(sig_remote, bar_remote, lane);
             }
             // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (half 0 warps) ----
             const long long w9 = clock64();
@@ -393,11 +436,11 @@ int launch_mlp_bf16_v3(const MlpInput& in, const void* packed, int ins_num, floa
     if (stash) {
         DM_REQUIRE((reinterpret_cast<uintptr_t>(stash) & 15) == 0, DMNERF_EINVAL, "mlp_fwd(bf16): stash must be 16-byte aligned");
         DM_CUDA(cudaFuncSetAttribute(tc3::mlp_fwd_bf16_v3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc3::kSm3Total));
-        tc3::mlp_fwd_bf16_v3_kernel<true><<<grid, tc::kThreads, tc3::kSm3Total, st>>>(
+        tc3::mlp_fwd_bf16_v3_kernel<true><<<grid, tc::kFwThreads, tc3::kSm3Total, st>>>(
             in, static_cast<const uint8_t*>(packed), im, raw_out, static_cast<uint8_t*>(stash));
     } else {
         DM_CUDA(cudaFuncSetAttribute(tc3::mlp_fwd_bf16_v3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc3::kSm3Total));
-        tc3::mlp_fwd_bf16_v3_kernel<false><<<grid, tc::kThreads, tc3::kSm3Total, st>>>(
+        tc3::mlp_fwd_bf16_v3_kernel<false><<<grid, tc::kFwThreads, tc3::kSm3Total, st>>>(
             in, static_cast<const uint8_t*>(packed), im, raw_out, nullptr);
     }
     DM_LAUNCH_CHECK("mlp_fwd_bf16_v3_kernel");
