@@ -77,6 +77,7 @@ _SIGNATURES = {
     "dmnerf_penalizer_bwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _p, _p, _p, _p]),
     "dmnerf_exchange": (_int, [_p, _p, _p, _p, _int, _int, _i64, _int, _int, _p, _p, _p]),
     "dmnerf_rays_k": (_int, [_int, _int, C.POINTER(_f), C.POINTER(_f), _i64, _p, _i64, _p, _p, _p]),
+    "dmnerf_rays_k_dev": (_int, [_int, _int, _p, _p, _i64, _p, _i64, _p, _p, _p]),
     "dmnerf_embed": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_label_argmax": (_int, [_p, _i64, _int, _p, _p]),
     "dmnerf_selftest_umma": (_int, [_p, _p, _int, _int, _p, _p]),
@@ -85,6 +86,7 @@ _SIGNATURES = {
     "dmnerf_selftest_tmem_read_bw": (_int, [_int, _int, _int, _p, _p]),
     "dmnerf_selftest_umma_rate": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_counters": (_int, [_p]),
+    "dmnerf_hungarian": (_int, [_p, _int, _i64, _int, _p, _int, _p, _p]),
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
 }

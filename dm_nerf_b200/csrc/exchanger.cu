@@ -130,6 +130,28 @@ __global__ void rays_k_kernel(Camera cam, int W, int64_t pix0, const int64_t* __
     }
 }
 
+// Same rays with the camera read from DEVICE memory (K [3,3] row-major, c2w [>=3, 4] row-major): nothing about the
+// view is baked into the launch, so a captured training step can be replayed for any image / pose.
+__global__ void rays_k_dev_kernel(const float* __restrict__ K, const float* __restrict__ c2w, int W, int64_t pix0,
+                                  const int64_t* __restrict__ pix_idx, int64_t n, float* __restrict__ rays_o,
+                                  float* __restrict__ rays_d) {
+    const int64_t q = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const int64_t pix = pix_idx ? pix_idx[q] : pix0 + q;
+    const float i = static_cast<float>(pix % W), j = static_cast<float>(pix / W);
+    const float d0 = __fdiv_rn(__fsub_rn(i, __ldg(K + 2)), __ldg(K + 0));
+    const float d1 = __fdiv_rn(__fsub_rn(j, __ldg(K + 5)), __ldg(K + 4));
+    const float d2 = __ldg(K + 8);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float v = __fmul_rn(d0, __ldg(c2w + c * 4 + 0));
+        v = __fadd_rn(v, __fmul_rn(d1, __ldg(c2w + c * 4 + 1)));
+        v = __fadd_rn(v, __fmul_rn(d2, __ldg(c2w + c * 4 + 2)));
+        rays_d[q * 3 + c] = v;
+        rays_o[q * 3 + c] = __ldg(c2w + c * 4 + 3);
+    }
+}
+
 // Standalone positional embedding (Embedder.embed, networks/dm_nerf.py:37-38): out[n, 3+6F].
 __global__ void embed_kernel(const float* __restrict__ x, int64_t n, int F, float* __restrict__ out) {
     const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -208,5 +230,17 @@ extern "C" int dmnerf_rays_k(int H, int W, const float* K, const float* c2w, int
     rays_k_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, as_stream(stream)>>>(cam, W, pix0, pix_idx, n,
                                                                                        rays_o, rays_d);
     DM_LAUNCH_CHECK("rays_k_kernel");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_rays_k_dev(int H, int W, const float* K_dev, const float* c2w_dev, int64_t pix0, const int64_t* pix_idx,
+                                 int64_t n, float* rays_o, float* rays_d, void* stream) {
+    DM_REQUIRE(K_dev && c2w_dev && rays_o && rays_d, DMNERF_EINVAL, "rays_k_dev: null pointer");
+    DM_REQUIRE(H > 0 && W > 0 && (pix_idx || (pix0 >= 0 && pix0 + n <= static_cast<int64_t>(H) * W)), DMNERF_EINVAL,
+               "rays_k_dev: pixel range [%lld,+%lld) outside %dx%d", (long long)pix0, (long long)n, H, W);
+    if (n <= 0) return DMNERF_OK;
+    rays_k_dev_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, as_stream(stream)>>>(K_dev, c2w_dev, W, pix0, pix_idx, n,
+                                                                                           rays_o, rays_d);
+    DM_LAUNCH_CHECK("rays_k_dev_kernel");
     return DMNERF_OK;
 }

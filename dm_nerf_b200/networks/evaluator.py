@@ -85,6 +85,43 @@ def ins_criterion_multi(preds, gt_labels, ins_num):
     return out
 
 
+def ins_criterion_device(preds, gt_labels, ins_num, max_label=None):
+    """``ins_criterion`` for a list of predictions with NO host round trip: static shapes only, the
+    assignment solved by ``dmnerf_hungarian`` on the device, so the whole training step can be enqueued (or captured
+    in a CUDA graph) without a synchronisation.  Labels must lie in ``[0, max_label)`` (default ``ins_num``).
+    Differences to the host path: none in the arithmetic of the three loss terms; ``torch.unique`` (data-dependent
+    shape) is replaced by a presence mask + prefix sum, and the means over the matched / unmatched sets become masked
+    sums divided by device-side counts."""
+    from .. import ops
+    dev, dt = preds[0].device, preds[0].dtype
+    n = gt_labels.shape[0]
+    nl = int(max_label) if max_label is not None else int(ins_num)
+    lab = gt_labels.long()
+    present = torch.zeros(nl, device=dev, dtype=dt).scatter_(0, lab, 1.0)           # 1 for every label in the batch
+    rank = torch.cumsum(present, 0).long() - 1                                       # compact index = position in unique()
+    n_valid = present.sum()
+    slot = rank[lab]                                                                 # [N] row of the one-hot
+    gt_ins = torch.zeros((n, ins_num), device=dev, dtype=dt).scatter_(1, slot[:, None], 1.0)
+    gt_t, gt_count = gt_ins.t(), gt_ins.sum(0)
+    costs = [_ins_costs(p, gt_t, gt_count, n) for p in preds]
+    with torch.no_grad():
+        scores = torch.stack([ce + siou for ce, siou in costs])
+        col = ops.hungarian(scores, n_valid.to(torch.int32)).long()                  # [B, K]
+    ar = torch.arange(ins_num, device=dev)
+    row_mask = (ar < n_valid).to(dt)                                                 # rows / leading col entries that are matches
+    n_inv = ins_num - n_valid
+    out = []
+    for i, (p, (ce, siou)) in enumerate(zip(preds, costs)):
+        c = col[i]
+        valid_ce = (ce[ar, c] * row_mask).sum() / n_valid
+        valid_siou = (siou[ar, c] * row_mask).sum() / n_valid
+        # mean over [N, unmatched columns]; 0 when every channel is matched (evaluator.py:31-34)
+        inv_sum = (p.sum(0)[c] * (1.0 - row_mask)).sum()
+        invalid_ce = torch.where(n_inv > 0, inv_sum / (n * torch.clamp(n_inv, min=1.0)), torch.zeros((), device=dev, dtype=dt))
+        out.append((valid_ce + invalid_ce + valid_siou, valid_ce, invalid_ce, valid_siou))
+    return out
+
+
 def ins_criterion(pred_ins, gt_labels, ins_num):
     """evaluator.py:19-37: one-hot the labels present in the batch, match predicted channels to them, then
     CE on matched pairs + mean activation of unmatched channels + soft-IoU on matched pairs."""

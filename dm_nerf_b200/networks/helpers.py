@@ -30,7 +30,10 @@ def get_select_full(rgb, pose, K, ins_target, N_train, numpy_rng=False):
         idx = torch.from_numpy(np.random.choice(H * W, size=[N_train], replace=False)).to(rgb.device)
     else:
         idx = torch.randperm(H * W, device=rgb.device)[:N_train]
-    ro, rd = ops.rays_k(int(H), int(W), K, pose, 0, int(N_train), rgb.device, pix_idx=idx)
+    if torch.is_tensor(K) and K.is_cuda and torch.is_tensor(pose) and pose.is_cuda:
+        ro, rd = ops.rays_k_dev(int(H), int(W), K, pose, int(N_train), idx)          # camera stays on the device
+    else:
+        ro, rd = ops.rays_k(int(H), int(W), K, pose, 0, int(N_train), rgb.device, pix_idx=idx)
     batch_rays = torch.stack([ro, rd], 0)
     return rgb.reshape(-1, rgb.shape[-1])[idx], ins_target.reshape(-1)[idx], batch_rays
 

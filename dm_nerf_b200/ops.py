@@ -223,6 +223,20 @@ def composite_fwd(raw, z, rays_d, flags: int, want_weights: bool = True):
     return rgb, weights, depth, ins
 
 
+def hungarian(scores, n_valid):
+    """Device-side scipy.optimize.linear_sum_assignment (evaluator.py:45-52).  scores [B, R, K] fp32 (rows beyond
+    ``n_valid`` ignored), n_valid: int32 device scalar.  Returns int32 [B, K]: the matched column of each valid row,
+    then the unmatched columns ascending.  Nothing is copied to the host."""
+    scores = _f32(scores, "scores")
+    b, r, k = scores.shape
+    if n_valid.dtype != torch.int32 or not n_valid.is_cuda:
+        raise RuntimeError("hungarian: n_valid must be an int32 CUDA tensor")
+    col = torch.empty((b, k), dtype=torch.int32, device=scores.device)
+    check(_lib.lib().dmnerf_hungarian(_ptr(scores), b, r * k, k, _ptr(n_valid), k, _ptr(col), _stream()), "dmnerf_hungarian")
+    _count()
+    return col
+
+
 def composite_bwd(raw, z, rays_d, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins):
     n, s, c = raw.shape
     d_raw = torch.empty_like(raw)
@@ -403,6 +417,22 @@ def rays_k(H: int, W: int, K, c2w, pix0: int, n: int, device, pix_idx: Optional[
         pix_idx = pix_idx.to(device=device, dtype=torch.int64).contiguous()
     check(_lib.lib().dmnerf_rays_k(H, W, kf, cf, pix0, _ptr(pix_idx), n, _ptr(ro), _ptr(rd), _stream()),
           "dmnerf_rays_k")
+    _count()
+    return ro, rd
+
+
+def rays_k_dev(H: int, W: int, K, c2w, n: int, pix_idx: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``rays_k`` with the intrinsics and the pose as CUDA tensors (no host copy, nothing view-specific in the launch)."""
+    K = _f32(K, "K")
+    c2w = _f32(c2w, "c2w")
+    if K.numel() < 9 or c2w.numel() < 12 or c2w.shape[-1] != 4:
+        raise RuntimeError("rays_k_dev: K must be [3,3] and c2w [>=3,4]")
+    dev = K.device
+    ro = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    rd = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    pix_idx = pix_idx.to(device=dev, dtype=torch.int64).contiguous()
+    check(_lib.lib().dmnerf_rays_k_dev(H, W, _ptr(K), _ptr(c2w), 0, _ptr(pix_idx), n, _ptr(ro), _ptr(rd), _stream()),
+          "dmnerf_rays_k_dev")
     _count()
     return ro, rd
 

@@ -137,10 +137,22 @@ int  dmnerf_exchange(float* ori_raw, const float* tar_raw, const float* ori_acc,
 int  dmnerf_rays_k(int H, int W, const float* K_host, const float* c2w_host, int64_t pix0,
                    const int64_t* pix_idx /* device, may be NULL: then pixels pix0..pix0+n-1 */, int64_t n,
                    float* rays_o, float* rays_d, void* stream);
+/* Same as dmnerf_rays_k with K [3,3] and c2w [>=3,4] (row-major fp32) in DEVICE memory: no camera value is baked into
+ * the launch, so a captured training step replays for any view (train_dmsr.py:30-36 draws a new image per step). */
+int  dmnerf_rays_k_dev(int H, int W, const float* K_dev, const float* c2w_dev, int64_t pix0,
+                       const int64_t* pix_idx, int64_t n, float* rays_o, float* rays_d, void* stream);
 /* Standalone Embedder.embed (networks/dm_nerf.py:37-38): x [n,3] -> out [n, 3+6*n_freqs]. */
 int  dmnerf_embed(const float* x, int64_t n, int n_freqs, float* out, void* stream);
 /* Per-ray label image: argmax over sigmoid'ed instance map (first max wins), uint8 out. */
 int  dmnerf_label_argmax(const float* ins, int64_t n, int k, uint8_t* labels, void* stream);
+
+/* Linear-sum assignment on the device (replaces scipy.optimize.linear_sum_assignment at networks/evaluator.py:45-46
+ * plus the unmatched-column bookkeeping of :47-52).  scores: n_mats matrices, matrix m at scores + m*mat_stride,
+ * row-major with leading dimension ld; rows 0 .. *n_valid-1 (n_valid: DEVICE int, <= n_cols) are assigned to distinct
+ * columns of 0 .. n_cols-1 (n_cols <= 128) minimising the summed score.  col_out [n_mats, n_cols] int32: the column
+ * of each assigned row, then the unmatched columns in ascending order.  No host synchronisation. */
+int  dmnerf_hungarian(const float* scores, int n_mats, int64_t mat_stride, int ld, const int* n_valid, int n_cols,
+                      int* col_out, void* stream);
 
 /* ---- self test of the tcgen05 building blocks (used by tests/) ---------------------------------------
  * D[128,n] = A[128,k] * B[n,k]^T in bf16 with fp32 accumulate; a,b fp32 in, d fp32 out. */

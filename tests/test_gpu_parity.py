@@ -604,3 +604,80 @@ def test_umma2_selftest():
         torch.cuda.synchronize()
         ref = a.bfloat16().float() @ b.bfloat16().float().t()
         assert float((d - ref).abs().max()) <= 1e-3, (n, k)
+
+
+@pytest.mark.parametrize("k,n_valid", [(32, 32), (32, 7), (93, 41), (123, 123), (5, 1), (16, 0)])
+def test_hungarian_vs_scipy(k, n_valid):
+    """dmnerf_hungarian against scipy.optimize.linear_sum_assignment (the call the reference makes, evaluator.py:45-46)
+    on random score matrices: same assignment, and the unmatched columns follow in ascending order."""
+    from scipy.optimize import linear_sum_assignment
+    from dm_nerf_b200 import ops
+    gen = torch.Generator().manual_seed(100 + k + n_valid)
+    scores = torch.rand(3, k, k, generator=gen) * 4 - 1
+    scores[2] = torch.rand(k, 1, generator=gen) + torch.rand(1, k, generator=gen) * 0.5 + 0.01 * scores[2]   # near-degenerate
+    col = ops.hungarian(cu(scores), torch.tensor(n_valid, dtype=torch.int32, device=DEV)).cpu().numpy()
+    for b in range(3):
+        s = scores[b, :n_valid].double().numpy()
+        row, ref = linear_sum_assignment(s) if n_valid else (np.zeros(0, int), np.zeros(0, int))
+        got = col[b]
+        assert sorted(got.tolist()) == list(range(k))
+        assert abs(s[np.arange(n_valid), got[:n_valid]].sum() - s[row, ref].sum()) <= 1e-9
+        assert got[:n_valid].tolist() == ref.tolist()
+        rest = sorted(set(range(k)) - set(ref.tolist()))
+        assert got[n_valid:].tolist() == rest
+
+
+@pytest.mark.parametrize("tag", ["k32", "k93"])
+def test_ins_criterion_device_vs_golden(golden, tag):
+    """The sync-free instance loss (device Hungarian, static shapes) against the values and gradients produced by the
+    reference's own ins_criterion (evaluator.py:19-74)."""
+    from dm_nerf_b200.networks import evaluator as ev
+    g = golden(f"ins_criterion_{tag}")
+    pred = cu(torch.from_numpy(g["pred"])).requires_grad_(True)
+    pred_b = cu(torch.from_numpy(g["pred"][::-1].copy())).requires_grad_(True)
+    labels = cu(torch.from_numpy(g["labels"]))
+    out = ev.ins_criterion_device([pred, pred_b], labels, int(g["ins_num"]), max_label=int(g["labels"].max()) + 1)
+    out[0][0].backward()
+    got = np.array([float(o.detach()) for o in out[0]], dtype=np.float32)
+    np.testing.assert_allclose(got, g["losses"], rtol=5e-6, atol=5e-7)
+    np.testing.assert_allclose(pred.grad.cpu().numpy(), g["grad"], rtol=1e-4, atol=1e-8)
+    host = ev.ins_criterion(pred_b.detach(), labels, int(g["ins_num"]))
+    np.testing.assert_allclose(float(out[1][0].detach()), float(host[0]), rtol=5e-6)
+
+
+def test_train_step_cuda_graph_replay():
+    """TrainStep(graph=True): the captured step (pixel draw, both passes, losses, device Hungarian, backward, Adam)
+    replays with new inputs; every replay moves the weights, the loss stays finite, the step counter drives the
+    learning-rate scalar, and the packed-weight caches do not go stale (a query after training uses the new weights)."""
+    from types import SimpleNamespace
+    from dm_nerf_b200.networks.dm_nerf import DM_NeRF
+    from dm_nerf_b200.train import TrainStep
+    k, n, H, W = 8, 256, 48, 64
+    mc, mf = make_model(k, 1), make_model(k, 2)
+    pe, ve = embedders()
+    Kmat = torch.tensor([[60.0, 0, W / 2], [0, -60.0, H / 2], [0, 0, -1]])
+    args = SimpleNamespace(N_train=n, near=4.0, far=15.0, N_samples=64, N_importance=128, perturb=1.0, ins_num=k,
+                           tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+    gen = torch.Generator().manual_seed(5)
+    lab = cu((torch.arange(H)[:, None] // 12 * 2 + torch.arange(W)[None] // 32) % k)
+    with _bf16_mode():
+        ts = TrainStep(pe, ve, mc, mf, Kmat, args, penalize=True, graph=True)
+        prev = mc.mlps[0].weight.detach().clone()
+        for it in range(4):
+            img = cu(torch.rand(H, W, 3, generator=gen))
+            pose = torch.eye(4)[:3, :4].clone(); pose[2, 3] = 6.0 + it
+            out = ts.step(img, cu(pose), lab)
+            total = float(out["total"])
+            assert np.isfinite(total)
+            cur = mc.mlps[0].weight.detach().clone()
+            assert float((cur - prev).abs().max()) > 0
+            prev = cur
+        assert ts.iteration == 3 + 4                     # three warm-up steps before the capture, then one per call
+        o, d = cu(torch.rand(5, 3, generator=gen)), cu(torch.randn(5, 3, generator=gen))
+        z = cu(torch.sort(torch.rand(5, 64, generator=gen) * 11 + 4, -1)[0])
+        with torch.no_grad():
+            got = mc.query_rays(o, d, z)
+            fresh = DM_NeRF(8, 256, 63, 27, [4], k).to(DEV)
+            fresh.load_state_dict(mc.state_dict())
+            ref = fresh.query_rays(o, d, z)
+    assert torch.equal(got, ref)
