@@ -169,7 +169,11 @@ def _aligned_bytes(nbytes: int, device) -> torch.Tensor:
 def mlp_bwd(packed, acts, d_raw, n_points: int, ins_num: int, shapes: Sequence[torch.Size],
             mode: int = MODE_FP32) -> List[torch.Tensor]:
     d_raw = _f32(d_raw, "d_raw")
-    grads = [torch.zeros(s, dtype=torch.float32, device=d_raw.device) for s in shapes]
+    # one zeroed buffer for the 30 gradients (the kernels accumulate into it): 1 fill instead of 30
+    sizes = [int(torch.Size(s).numel()) for s in shapes]
+    padded = [(n + 3) & ~3 for n in sizes]                                    # every gradient starts 16-byte aligned
+    flat = torch.zeros(sum(padded), dtype=torch.float32, device=d_raw.device)
+    grads = [g[:n].view(s) for g, n, s in zip(flat.split(padded), sizes, shapes)]
     ws_bytes = _lib.lib().dmnerf_bwd_workspace_bytes(n_points, ins_num, mode)
     ws = _aligned_bytes(ws_bytes, d_raw.device) if ws_bytes > 0 else None
     _timed_call(f"dmnerf_mlp_bwd[mode={mode}]", _lib.lib().dmnerf_mlp_bwd, _ptr(packed), _ptr(acts), _ptr(d_raw),

@@ -106,7 +106,7 @@ class TrainStep:
         total = rgb_loss + ins_loss
         if emptiness is not None:
             total = total + emptiness
-        self.opt.zero_grad(set_to_none=False)
+        self.opt.zero_grad(set_to_none=True)          # backward then installs the fresh gradient tensors: no fills, no adds
         total.backward()
         if self.flat is None:
             self.flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=self.params[0].device)
