@@ -86,7 +86,7 @@ constexpr int kActRows = kActRgbH + 128;      // 2912
 
 // ---- bf16 stash of the tensor-core TRAINING path (DMNERF_MODE_BF16), per block of 64 points ----------
 // The unit is one k-group slab [64 rows][8 bf16] = 1024 B; a region of F features is F/8 consecutive slabs,
-// i.e. exactly a no-swizzle UMMA operand image: K-major over features for the dgrad chain's masks, MN-major
+// i.e. exactly a no-swizzle UMMA operand image: MN-major
 // with the 64 points as the reduction dim for wgrad -- so wgrad moves whole regions with ONE 1-D bulk copy.
 //   activations (written by the forward):  POS 8 | DIR 4 | H0..H7 8 x 32 | HID 32           = 300 slabs
 //   gradients   (written by dgrad)      :  G0..G7 8 x 32 | G8 32 | G9 16 (C padded to 128)  = 304 slabs
@@ -100,6 +100,17 @@ constexpr int64_t kStActBlkBytes = static_cast<int64_t>(kStActKg) * kStKgBytes; 
 constexpr int64_t kStGradBlkBytes = static_cast<int64_t>(kStGradKg) * kStKgBytes;  // 311,296
 // blocks are allocated for whole tile QUADS (512 points: two tiles in each CTA of a pair) of the persistent kernels
 __host__ __device__ inline int64_t tc_stash_blocks(int64_t n_points) { return ((n_points + 511) / 512) * 8; }
+// ReLU sign masks (1 bit per activation), appended to the activation stash after its last block: the dgrad chain only
+// needs to know WHICH of h0..h7 / hid were positive, so it reads 288 B per point here instead of 4.6 KB of bf16
+// activations.  Per 64-point block: [9 layers a: h0..h7, hid][2 column halves][4 words c][64 rows] uint32; word c of
+// (a, half) covers features half*128 + c*32 .. +31 of layer a for one point: bit k (k = 0..15) is the feature
+// c*32 + (k>>2)*8 + 2*(k&3), bit 16+k the feature after it (the order the epilogues' packed bf16 pairs come in).
+constexpr int kStMaskLayers = 9;
+constexpr int64_t kStMaskBlkBytes = static_cast<int64_t>(kStMaskLayers) * 2 * 4 * kStBlk * 4;   // 18,432
+__host__ __device__ inline int64_t tc_mask_offset(int64_t n_points) { return tc_stash_blocks(n_points) * kStActBlkBytes; }
+__host__ __device__ inline int64_t tc_mask_word(int64_t blk, int a, int half, int c, int row64) {
+    return ((((blk * kStMaskLayers + a) * 2 + half) * 4 + c) * kStBlk + row64) * 4;
+}
 
 // Input of one MLP launch: either rays (points o + d*z and both embeddings computed in-kernel) or
 // already-embedded rows x[m,90].

@@ -285,7 +285,9 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             const int64_t tile0 = pair * kPair + t * kTile;
             const int64_t p = tile0 + row;
             const bool valid = p < in.n_points;
-            uint8_t* gst = kStash ? stash + ((pair * 2 + t) * 2 + (row >> 6)) * kStActBlkBytes + (row & 63) * 16 : nullptr;
+            const int64_t sblk = (pair * 2 + t) * 2 + (row >> 6);
+            uint8_t* gst = kStash ? stash + sblk * kStActBlkBytes + (row & 63) * 16 : nullptr;
+            uint8_t* mst = kStash ? stash + tc_mask_offset(in.n_points) : nullptr;
             float dir[3] = {0.f, 0.f, 0.f};
             if (in.x == nullptr) {
                 float pos[3] = {0.f, 0.f, 0.f};
@@ -323,6 +325,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                     uint32_t r[32];
                     ptx::tmem_ld32(t_base + cb * 32, r);
                     ptx::tmem_ld_wait();
+                    uint32_t mword = 0;
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         float v[8];
@@ -332,8 +335,13 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 #pragma unroll
                             for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_misc[128 + cb * 32 + g * 8 + e], dens);
                         }
-                        store_kg(a_base, cb * 4 + g, row, v, true, gst, (l == 8 ? kStHid : kStH0 + 32 * l) + cb * 4 + g);
+                        if constexpr (kStash)
+                            mword = store_kg_mask(a_base, cb * 4 + g, row, v, gst, (l == 8 ? kStHid : kStH0 + 32 * l) + cb * 4 + g, g, mword);
+                        else
+                            store_kg(a_base, cb * 4 + g, row, v, true);
                     }
+                    // one coalesced 128-byte line of sign masks per warp and 32 columns (read by the dgrad chain)
+                    if constexpr (kStash) *reinterpret_cast<uint32_t*>(mst + tc_mask_word(sblk, l, half, cb & 3, row & 63)) = mword;
                 }
                 if (l == 7) {
                     // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it)
@@ -453,14 +461,19 @@ umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, i
 int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16_v3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16_v4(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int launch_masks_from_acts(void* acts, int64_t n_points, cudaStream_t st);
 
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
     // debug bit2 selects the pipelined variant (mlp_tc2.cu).  It is correct (same parity tests) but not faster:
     // its N=128 cells re-read the A operand twice, which makes the SS-mode MMAs shared-memory-bandwidth bound
     // once the epilogue's stores overlap them (measured 7.06 ms vs 6.92 ms per 32768x192 points); see DESIGN.md.
-    if (g_tc_debug_flags & 4) return launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st);
-    if (g_tc_debug_flags & 8) return launch_mlp_bf16_v3(in, packed, ins_num, raw_out, stash, st);
-    if (g_tc_debug_flags & 32) return launch_mlp_bf16_v4(in, packed, ins_num, raw_out, stash, st);
+    if (g_tc_debug_flags & (4 | 8 | 32)) {
+        const int rc = (g_tc_debug_flags & 4)   ? launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st)
+                       : (g_tc_debug_flags & 8) ? launch_mlp_bf16_v3(in, packed, ins_num, raw_out, stash, st)
+                                                : launch_mlp_bf16_v4(in, packed, ins_num, raw_out, stash, st);
+        // the variants stash the activations only; the dgrad chain's sign masks are derived from them here
+        return (rc == DMNERF_OK && stash) ? launch_masks_from_acts(stash, in.n_points, st) : rc;
+    }
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;

@@ -6,7 +6,7 @@
 //   1. mlp_dgrad_bf16_kernel  the gradient chain d(raw) -> G8 -> G7 ... -> G0 (G_l = dL/d pre-activation of
 //      forward layer T_l).  Same persistent structure as the forward: tile pairs in lockstep, transposed
 //      weights streamed through a bulk-copy ring, fp32 accumulators in TMEM, the epilogue applies the ReLU
-//      mask read from the stashed activation and writes the next operand to smem AND to the gradient stash.
+//      mask read from the forward's 1-bit sign-mask stash and writes the next operand to smem AND to the gradient stash.
 //      Detach points: the instance rows of T8 are left out of the chain (h.detach(), dm_nerf.py:95); nothing
 //      flows into the embeddings (rays / z are data).  The density head is a rank-1 term in T8's epilogue.
 //   2. mlp_wgrad_bf16_kernel  dW_l = G_l^T A_l as split-K GEMMs over points: each CTA owns a contiguous range of
@@ -40,12 +40,6 @@ struct DBars {
     __device__ __forceinline__ uint32_t a_ready(int t) const { return base + 8 * (2 * kDgStages + t); }
     __device__ __forceinline__ uint32_t acc_ready(int t) const { return base + 8 * (2 * kDgStages + 2 + t); }
 };
-
-__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
-    uint4 r;
-    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
 
 __global__ void __launch_bounds__(kFwThreads, 1)
 mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const uint8_t* __restrict__ image, Image im,
@@ -136,7 +130,7 @@ mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const u
             const int64_t p = pair * kPair + t * kTile + row;
             const bool valid = p < n_points;
             const int64_t blk = (pair * 2 + t) * 2 + (row >> 6);
-            const uint8_t* act_row = acts + blk * kStActBlkBytes + (row & 63) * 16;
+            const uint8_t* masks = acts + tc_mask_offset(n_points);
             uint8_t* g_row = gstash + blk * kStGradBlkBytes + (row & 63) * 16;
             const float* dr = d_raw + p * C;
             const float dsig = valid ? __ldg(dr + 3) : 0.f;
@@ -155,12 +149,13 @@ mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const u
             ptx::mbar_arrive(bars.a_ready(t));
 
             for (int d = 0; d < kDgLayers; ++d) {
-                const int mkg0 = d == 0 ? kStHid : kStH0 + 32 * (8 - d);     // activation whose ReLU gates this gradient
+                const int ma = d == 0 ? 8 : 8 - d;                           // activation whose ReLU gates this gradient
                 const int okg0 = d == 0 ? kStG8 : kStG0 + 32 * (8 - d);      // where the masked gradient is stashed
                 const int cb0 = half * 4;
-                uint4 mk[4];
+                // 128 sign bits (the forward's mask stash): four coalesced 4-byte loads, in flight during the wait
+                uint32_t mk[4];
 #pragma unroll
-                for (int g = 0; g < 4; ++g) mk[g] = ldg_nc_v4(act_row + (mkg0 + cb0 * 4 + g) * kStKgBytes);
+                for (int c = 0; c < 4; ++c) mk[c] = __ldg(reinterpret_cast<const uint32_t*>(masks + tc_mask_word(blk, ma, half, c, row & 63)));
                 ptx::mbar_wait(bars.acc_ready(t), acc_par);
                 acc_par ^= 1;
                 ptx::tc_fence_after();
@@ -168,24 +163,17 @@ mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const u
                 for (int cb = cb0; cb < cb0 + 4; ++cb) {
                     uint32_t r[32];
                     ptx::tmem_ld32(t_base + cb * 32, r);
-                    uint4 cur[4];
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) cur[g] = mk[g];
-                    if (cb + 1 < cb0 + 4) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) mk[g] = ldg_nc_v4(act_row + (mkg0 + (cb + 1) * 4 + g) * kStKgBytes);
-                    }
+                    const int c = cb - cb0;
+                    const uint32_t mword = c == 0 ? mk[0] : (c == 1 ? mk[1] : (c == 2 ? mk[2] : mk[3]));
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
-                        const uint32_t mw[4] = {cur[g].x, cur[g].y, cur[g].z, cur[g].w};
                         float v[8];
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
                             float x = __uint_as_float(r[g * 8 + e]);
                             if (d == 1) x = fmaf(dsig, s_wd[cb * 32 + g * 8 + e], x);           // density head: d(sigma) * w_density
-                            const uint32_t bits = (e & 1) ? (mw[e >> 1] >> 16) : (mw[e >> 1] & 0xFFFFu);
-                            v[e] = bits != 0 ? x : 0.f;
+                            v[e] = (mword >> ((e & 1) * 16 + g * 4 + (e >> 1))) & 1u ? x : 0.f;
                         }
                         const uint32_t w0 = ptx::pack_bf16(v[0], v[1], false), w1 = ptx::pack_bf16(v[2], v[3], false);
                         const uint32_t w2 = ptx::pack_bf16(v[4], v[5], false), w3 = ptx::pack_bf16(v[6], v[7], false);
@@ -618,7 +606,42 @@ umma_mn_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b
 
 }  // namespace tcb
 
-int64_t bf16_acts_bytes(int64_t n_points) { return tc_stash_blocks(n_points) * kStActBlkBytes; }
+int64_t bf16_acts_bytes(int64_t n_points) { return tc_stash_blocks(n_points) * (kStActBlkBytes + kStMaskBlkBytes); }
+
+// Sign masks from an activation stash whose forward did not write them (the parked forward variants): one thread per
+// mask word.  The default forward kernel writes the masks itself.
+namespace tcb {
+__global__ void masks_from_acts_kernel(uint8_t* __restrict__ acts, int64_t n_points, int64_t n_blocks) {
+    const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= n_blocks * kStMaskLayers * 2 * 4 * kStBlk) return;
+    const int row = static_cast<int>(idx % kStBlk);
+    int64_t r = idx / kStBlk;
+    const int c = static_cast<int>(r % 4); r /= 4;
+    const int half = static_cast<int>(r % 2); r /= 2;
+    const int a = static_cast<int>(r % kStMaskLayers);
+    const int64_t blk = r / kStMaskLayers;
+    const int kg0 = (a == 8 ? kStHid : kStH0 + 32 * a) + (half * 4 + c) * 4;
+    uint32_t m = 0;
+    for (int g = 0; g < 4; ++g) {
+        const uint4 w = *reinterpret_cast<const uint4*>(acts + blk * kStActBlkBytes + static_cast<int64_t>(kg0 + g) * kStKgBytes + row * 16);
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+        for (int j = 0; j < 4; ++j) {
+            const int k = g * 4 + j;
+            if (ww[j] & 0xFFFFu) m |= 1u << k;
+            if (ww[j] >> 16) m |= 1u << (16 + k);
+        }
+    }
+    *reinterpret_cast<uint32_t*>(acts + tc_mask_offset(n_points) + tc_mask_word(blk, a, half, c, row)) = m;
+}
+}  // namespace tcb
+
+int launch_masks_from_acts(void* acts, int64_t n_points, cudaStream_t st) {
+    const int64_t blocks = ((n_points + 255) / 256) * 4;
+    const int64_t words = blocks * kStMaskLayers * 2 * 4 * kStBlk;
+    tcb::masks_from_acts_kernel<<<static_cast<unsigned>((words + 255) / 256), 256, 0, st>>>(static_cast<uint8_t*>(acts), n_points, blocks);
+    DM_LAUNCH_CHECK("masks_from_acts_kernel");
+    return DMNERF_OK;
+}
 
 int64_t bf16_bwd_workspace_bytes(int64_t n_points) {
     return tc_stash_blocks(n_points) * kStGradBlkBytes + tcb::kGimgFloats * 4;

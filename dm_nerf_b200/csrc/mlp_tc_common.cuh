@@ -173,6 +173,23 @@ __device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const
     if (gst) *reinterpret_cast<uint4*>(gst + gkg * kStKgBytes) = make_uint4(w0, w1, w2, w3);
 }
 
+// same, and folds the 8 "is positive" flags of the ReLU outputs into the mask word m (mlp_layout.cuh: word j of
+// k-group g -> bits g*4+j and 16+g*4+j).  After cvt.rn.relu a bf16 half is in [0, 0x7FFF], so adding 0x7FFF sets its
+// top bit exactly when it is non-zero and never carries into the other half.
+__device__ __forceinline__ uint32_t store_kg_mask(uint32_t a_base, int kg, int row, const float v[8], uint8_t* gst, int gkg,
+                                                  int g, uint32_t m) {
+    const uint32_t w[4] = {ptx::pack_bf16(v[0], v[1], true), ptx::pack_bf16(v[2], v[3], true),
+                           ptx::pack_bf16(v[4], v[5], true), ptx::pack_bf16(v[6], v[7], true)};
+    ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4*>(gst + gkg * kStKgBytes) = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k = g * 4 + j;
+        m |= ((w[j] + 0x7FFF7FFFu) >> (15 - k)) & (0x00010001u << k);
+    }
+    return m;
+}
+
 // Embedding of a 3-vector into EXT k-groups [KG0, KG1): channel c = [x | f: sin(3) cos(3)], 8 channels per
 // k-group.  The first needed octave uses full-range sincosf on x*2^f (exact scaling); higher octaves follow by
 // angle doubling (error << bf16 resolution).  Channels outside the range are dead code after unrolling.
