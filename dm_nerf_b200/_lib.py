@@ -89,6 +89,7 @@ _SIGNATURES = {
     "dmnerf_hungarian": (_int, [_p, _int, _i64, _int, _p, _int, _p, _p]),
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
+    "dmnerf_reserve_sms": (_int, [_int]),
 }
 
 EXPORTS = tuple(_SIGNATURES)

@@ -28,24 +28,32 @@ __global__ void __launch_bounds__(32)
 hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, const int* __restrict__ n_valid_ptr, int nc,
                  int* __restrict__ col_out) {
     extern __shared__ float s_cost[];            // [nr][nc] staged once: the path search reads one row per step
-    __shared__ double s_u[kHungMaxN], s_v[kHungMaxN], s_spc[kHungMaxN];      // duals, shortest path costs
+    // The path search keeps everything a lane needs about ITS columns (shortest path cost, dual v, owner row, visited
+    // bit) in registers: a step is two shared-memory loads (u[i], the cost row), three dependent double adds per
+    // column and the warp arg-min.  Shared memory holds what is indexed by data: u, the matching, the path, and a
+    // copy of the path costs published once per augmentation for the dual update.
+    __shared__ double s_u[kHungMaxN], s_spc[kHungMaxN];
     __shared__ int s_col4row[kHungMaxN], s_row4col[kHungMaxN], s_path[kHungMaxN], s_sr_list[kHungMaxN];
-    __shared__ unsigned char s_sc[kHungMaxN];    // columns already on the alternating tree
     const int lane = threadIdx.x;
     const float* cost = scores + static_cast<int64_t>(blockIdx.x) * mat_stride;
     int* out = col_out + static_cast<int64_t>(blockIdx.x) * nc;
     int nr = *n_valid_ptr;
     nr = nr < 0 ? 0 : (nr > nc ? nc : nr);
 
-    for (int j = lane; j < kHungMaxN; j += 32) { s_v[j] = 0.0; s_row4col[j] = -1; s_u[j] = 0.0; s_col4row[j] = -1; }
+    for (int j = lane; j < kHungMaxN; j += 32) { s_row4col[j] = -1; s_u[j] = 0.0; s_col4row[j] = -1; }
     for (int i = 0; i < nr; ++i)
         for (int j = lane; j < nc; j += 32) s_cost[i * nc + j] = __ldg(cost + static_cast<int64_t>(i) * ld + j);
     __syncwarp();
 
     const double kInf = __longlong_as_double(0x7ff0000000000000LL);
+    double v[kHungCols], spc[kHungCols];
+    int r4c[kHungCols];
+#pragma unroll
+    for (int k = 0; k < kHungCols; ++k) { v[k] = 0.0; r4c[k] = -1; }
     for (int cur = 0; cur < nr; ++cur) {
-        for (int j = lane; j < kHungMaxN; j += 32) { s_spc[j] = kInf; s_sc[j] = 0; }
-        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < kHungCols; ++k) spc[k] = kInf;
+        unsigned vis = 0;                                    // bit k: column lane + 32k is on the alternating tree
         int n_sr = 0, sink = -1, i = cur;
         double min_val = 0.0;
         while (sink < 0) {
@@ -53,17 +61,18 @@ hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, c
             ++n_sr;
             const double ui = s_u[i];
             const float* crow = s_cost + i * nc;
+            float cv[kHungCols];
+#pragma unroll
+            for (int k = 0; k < kHungCols; ++k) cv[k] = lane + 32 * k < nc ? crow[lane + 32 * k] : 0.f;
             // relax every unvisited column from row i; lane-local minimum (an unassigned column wins a tie)
             double best = kInf; int best_j = -1, best_r4c = -1;
 #pragma unroll
             for (int k = 0; k < kHungCols; ++k) {
                 const int j = lane + 32 * k;
-                if (j < nc && !s_sc[j]) {
-                    const double r = min_val + static_cast<double>(crow[j]) - ui - s_v[j];
-                    double cur_spc = s_spc[j];
-                    if (r < cur_spc) { cur_spc = r; s_spc[j] = r; s_path[j] = i; }
-                    const int r4 = s_row4col[j];
-                    if (cur_spc < best || (cur_spc == best && r4 < 0 && best_r4c >= 0)) { best = cur_spc; best_j = j; best_r4c = r4; }
+                if (j < nc && !((vis >> k) & 1u)) {
+                    const double r = min_val + static_cast<double>(cv[k]) - ui - v[k];
+                    if (r < spc[k]) { spc[k] = r; s_path[j] = i; }
+                    if (spc[k] < best || (spc[k] == best && r4c[k] < 0 && best_r4c >= 0)) { best = spc[k]; best_j = j; best_r4c = r4c[k]; }
                 }
             }
             // warp arg-min by three hardware reductions: high word, low word of the order-preserving key, then
@@ -78,21 +87,24 @@ hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, c
             const unsigned long long mkey = (static_cast<unsigned long long>(mhi) << 32) | mlo;
             if (sel == 0xffffffffu || mkey == dkey(kInf)) { sink = -2; break; }     // infeasible (cannot happen for finite costs)
             const int j = static_cast<int>((sel >> 8) & 255u);
-            const int r4c = static_cast<int>(sel & 255u) - 1;
+            const int owner = static_cast<int>(sel & 255u) - 1;
             min_val = __longlong_as_double(static_cast<long long>((mkey >> 63) ? (mkey & 0x7fffffffffffffffULL) : ~mkey));
-            s_sc[j] = 1;                                     // every lane stores the same byte
-            __syncwarp();
-            if (r4c < 0) sink = j; else i = r4c;
+            if (lane == (j & 31)) vis |= 1u << (j >> 5);
+            if (owner < 0) sink = j; else i = owner;
         }
         if (sink < 0) break;
-        // dual update (uses the matching BEFORE augmentation)
+        // dual update (uses the matching BEFORE augmentation); the path costs are published for the row duals
+#pragma unroll
+        for (int k = 0; k < kHungCols; ++k) s_spc[lane + 32 * k] = spc[k];
+        __syncwarp();
         for (int t = 1 + lane; t < n_sr; t += 32) {                        // rows of the tree other than cur
             const int r = s_sr_list[t];
             s_u[r] += min_val - s_spc[s_col4row[r]];
         }
         if (lane == 0) s_u[cur] += min_val;
-        for (int j = lane; j < nc; j += 32)
-            if (s_sc[j]) s_v[j] -= min_val - s_spc[j];
+#pragma unroll
+        for (int k = 0; k < kHungCols; ++k)
+            if ((vis >> k) & 1u) v[k] -= min_val - spc[k];
         __syncwarp();
         // augment along the path sink -> cur
         if (lane == 0) {
@@ -107,6 +119,8 @@ hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, c
             }
         }
         __syncwarp();
+#pragma unroll
+        for (int k = 0; k < kHungCols; ++k) r4c[k] = s_row4col[lane + 32 * k];
     }
     // output: matched columns of rows 0..nr-1, then the unmatched columns ascending
     for (int r = lane; r < nr; r += 32) out[r] = s_col4row[r];

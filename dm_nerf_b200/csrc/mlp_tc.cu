@@ -26,6 +26,7 @@
 
 namespace dmnerf {
 
+static int g_reserved_sms = 0;     // SMs the persistent MLP kernels leave free (dmnerf_reserve_sms)
 static int g_tc_debug_flags = 0;   // bit0: swap LBO/SBO in the smem descriptors (bring-up aid)
 
 namespace tc {
@@ -462,6 +463,7 @@ int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, floa
 int launch_mlp_bf16_v3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16_v4(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_masks_from_acts(void* acts, int64_t n_points, cudaStream_t st);
+int persistent_ctas(int sm_count);
 
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
     // debug bit2 selects the pipelined variant (mlp_tc2.cu).  It is correct (same parity tests) but not faster:
@@ -483,7 +485,8 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
     DM_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0 && (reinterpret_cast<uintptr_t>(raw_out) & 15) == 0,
                DMNERF_EINVAL, "mlp_fwd(bf16): packed image and raw_out must be 16-byte aligned");
     const int64_t pairs = (in.n_points + tc::kPair - 1) / tc::kPair;
-    const unsigned grid = static_cast<unsigned>(pairs < sm_count ? pairs : sm_count);
+    const int sms = persistent_ctas(sm_count);
+    const unsigned grid = static_cast<unsigned>(pairs < sms ? pairs : sms);
     if (stash) {
         DM_REQUIRE((reinterpret_cast<uintptr_t>(stash) & 15) == 0, DMNERF_EINVAL, "mlp_fwd(bf16): stash must be 16-byte aligned");
         DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
@@ -500,6 +503,8 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
 }
 
 int tc_debug_flags() { return g_tc_debug_flags; }
+// CTAs a persistent one-CTA-per-SM kernel may launch: all SMs minus the reservation (never fewer than one)
+int persistent_ctas(int sm_count) { return sm_count - g_reserved_sms > 1 ? sm_count - g_reserved_sms : 1; }
 
 int debug_counters_v1(long long* host_out8) {
     DM_CUDA(cudaMemcpyFromSymbol(host_out8, tc::g_dbg1, 8 * sizeof(long long)));
@@ -537,6 +542,12 @@ using namespace dmnerf;
 extern "C" int dmnerf_debug_flags(int flags) {
     const int old = g_tc_debug_flags;
     if (flags >= 0) g_tc_debug_flags = flags;
+    return old;
+}
+
+extern "C" int dmnerf_reserve_sms(int n) {
+    const int old = g_reserved_sms;
+    if (n >= 0) g_reserved_sms = n;
     return old;
 }
 

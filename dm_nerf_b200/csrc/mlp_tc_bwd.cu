@@ -647,6 +647,8 @@ int64_t bf16_bwd_workspace_bytes(int64_t n_points) {
     return tc_stash_blocks(n_points) * kStGradBlkBytes + tcb::kGimgFloats * 4;
 }
 
+int persistent_ctas(int sm_count);
+
 int launch_mlp_bwd_bf16(const void* packed, const void* acts, const float* d_raw, int64_t n_points, int ins_num,
                         float* const* grads, void* workspace, int debug_flags, cudaStream_t st) {
     static int sm_count = 0;
@@ -668,13 +670,14 @@ int launch_mlp_bwd_bf16(const void* packed, const void* acts, const float* d_raw
     // further, to 512-point quads, for the CTA-pair forward)
     const int64_t pairs = (n_points + 255) / 256;
     const int64_t blocks = pairs * 4;
+    const int sms = persistent_ctas(sm_count);
     DM_CUDA(cudaFuncSetAttribute(tcb::mlp_dgrad_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::kDgSmTotal));
-    tcb::mlp_dgrad_bf16_kernel<<<static_cast<unsigned>(pairs < sm_count ? pairs : sm_count), tc::kFwThreads, tcb::kDgSmTotal, st>>>(
+    tcb::mlp_dgrad_bf16_kernel<<<static_cast<unsigned>(pairs < sms ? pairs : sms), tc::kFwThreads, tcb::kDgSmTotal, st>>>(
         d_raw, n_points, static_cast<const uint8_t*>(packed), im, static_cast<const uint8_t*>(acts), gstash);
     DM_LAUNCH_CHECK("mlp_dgrad_bf16_kernel");
 
     DM_CUDA(cudaFuncSetAttribute(tcb::mlp_wgrad_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::kWgSmTotal));
-    tcb::mlp_wgrad_bf16_kernel<<<static_cast<unsigned>(blocks < sm_count ? blocks : sm_count), tc::kThreads, tcb::kWgSmTotal, st>>>(
+    tcb::mlp_wgrad_bf16_kernel<<<static_cast<unsigned>(blocks < sms ? blocks : sms), tc::kThreads, tcb::kWgSmTotal, st>>>(
         static_cast<const uint8_t*>(acts), gstash, blocks, gimg, debug_flags & 2 ? 1 : 0);
     DM_LAUNCH_CHECK("mlp_wgrad_bf16_kernel");
 

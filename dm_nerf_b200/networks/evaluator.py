@@ -85,31 +85,34 @@ def ins_criterion_multi(preds, gt_labels, ins_num):
     return out
 
 
-def ins_criterion_device(preds, gt_labels, ins_num, max_label=None):
-    """``ins_criterion`` for a list of predictions with NO host round trip (SURVEY 8f rank 2): static shapes only, the
-    assignment solved by ``dmnerf_hungarian`` on the device, so the whole training step can be enqueued (or captured
-    in a CUDA graph) without a synchronisation.  Labels must lie in ``[0, max_label)`` (default ``ins_num``).
-    Differences to the host path: none in the arithmetic of the three loss terms; ``torch.unique`` (data-dependent
-    shape) is replaced by a presence mask + prefix sum, and the means over the matched / unmatched sets become masked
-    sums divided by device-side counts."""
-    from .. import ops
-    dev, dt = preds[0].device, preds[0].dtype
+def ins_label_prep(gt_labels, ins_num, max_label=None, dtype=torch.float32):
+    """The label side of ``ins_criterion`` (evaluator.py:20-26) with static shapes: ``torch.unique`` (data-dependent
+    shape) becomes a presence mask + prefix sum.  Shared by every prediction matched against the same labels."""
+    dev = gt_labels.device
     n = gt_labels.shape[0]
     nl = int(max_label) if max_label is not None else int(ins_num)
     lab = gt_labels.long()
-    present = torch.zeros(nl, device=dev, dtype=dt).scatter_(0, lab, 1.0)           # 1 for every label in the batch
+    present = torch.zeros(nl, device=dev, dtype=dtype).scatter_(0, lab, 1.0)        # 1 for every label in the batch
     rank = torch.cumsum(present, 0).long() - 1                                       # compact index = position in unique()
     n_valid = present.sum()
     slot = rank[lab]                                                                 # [N] row of the one-hot
-    gt_ins = torch.zeros((n, ins_num), device=dev, dtype=dt).scatter_(1, slot[:, None], 1.0)
-    gt_t, gt_count = gt_ins.t(), gt_ins.sum(0)
-    costs = [_ins_costs(p, gt_t, gt_count, n) for p in preds]
+    gt_ins = torch.zeros((n, ins_num), device=dev, dtype=dtype).scatter_(1, slot[:, None], 1.0)
+    ar = torch.arange(ins_num, device=dev)
+    return {"n": n, "ins_num": int(ins_num), "gt_t": gt_ins.t(), "gt_count": gt_ins.sum(0), "n_valid": n_valid,
+            "n_valid_i32": n_valid.to(torch.int32), "ar": ar, "row_mask": (ar < n_valid).to(dtype),
+            "n_inv": ins_num - n_valid}
+
+
+def ins_criterion_prepped(preds, prep):
+    """The prediction side: cost matrices, device assignment (ONE ``dmnerf_hungarian`` launch for all of ``preds``),
+    the three loss terms as masked sums divided by device-side counts.  Nothing synchronises with the host."""
+    from .. import ops
+    n, ins_num, ar, row_mask, n_valid, n_inv = (prep[k] for k in ("n", "ins_num", "ar", "row_mask", "n_valid", "n_inv"))
+    dev, dt = preds[0].device, preds[0].dtype
+    costs = [_ins_costs(p, prep["gt_t"], prep["gt_count"], n) for p in preds]
     with torch.no_grad():
         scores = torch.stack([ce + siou for ce, siou in costs])
-        col = ops.hungarian(scores, n_valid.to(torch.int32)).long()                  # [B, K]
-    ar = torch.arange(ins_num, device=dev)
-    row_mask = (ar < n_valid).to(dt)                                                 # rows / leading col entries that are matches
-    n_inv = ins_num - n_valid
+        col = ops.hungarian(scores, prep["n_valid_i32"]).long()                      # [B, K]
     out = []
     for i, (p, (ce, siou)) in enumerate(zip(preds, costs)):
         c = col[i]
@@ -120,6 +123,16 @@ def ins_criterion_device(preds, gt_labels, ins_num, max_label=None):
         invalid_ce = torch.where(n_inv > 0, inv_sum / (n * torch.clamp(n_inv, min=1.0)), torch.zeros((), device=dev, dtype=dt))
         out.append((valid_ce + invalid_ce + valid_siou, valid_ce, invalid_ce, valid_siou))
     return out
+
+
+def ins_criterion_device(preds, gt_labels, ins_num, max_label=None):
+    """``ins_criterion`` for a list of predictions with NO host round trip (SURVEY 8f rank 2): static shapes only, the
+    assignment solved by ``dmnerf_hungarian`` on the device, so the whole training step can be enqueued (or captured
+    in a CUDA graph) without a synchronisation.  Labels must lie in ``[0, max_label)`` (default ``ins_num``).
+    Differences to the host path: none in the arithmetic of the three loss terms; ``torch.unique`` (data-dependent
+    shape) is replaced by a presence mask + prefix sum, and the means over the matched / unmatched sets become masked
+    sums divided by device-side counts."""
+    return ins_criterion_prepped(preds, ins_label_prep(gt_labels, ins_num, max_label, preds[0].dtype))
 
 
 def ins_criterion(pred_ins, gt_labels, ins_num):

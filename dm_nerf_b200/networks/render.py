@@ -32,9 +32,11 @@ def _query(model, rays_o, rays_d, z_vals, position_embedder, view_embedder):
 
 
 def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_vals_coarse, args,
-            t_rand=None, u=None):
+            t_rand=None, u=None, on_coarse=None):
     """render.py:31-96.  ``t_rand`` [N,Sc] / ``u`` [N,N_importance] inject the uniforms; when absent
-    they are drawn with torch.rand in the reference's order (jitter first, then u)."""
+    they are drawn with torch.rand in the reference's order (jitter first, then u).  ``on_coarse(ins_coarse)``, if
+    given, is called as soon as the coarse pass is composited (the training step starts the coarse instance
+    assignment on a side stream there, beside the fine pass)."""
     rays_o, rays_d = rays
     rays_o, rays_d = rays_o.float().contiguous(), rays_d.float().contiguous()
     z_vals_coarse = z_vals_coarse.float()
@@ -47,6 +49,8 @@ def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_
         z_vals_coarse = z_vals_coarse.contiguous()
     raw_coarse = _query(model_coarse, rays_o, rays_d, z_vals_coarse, position_embedder, view_embedder)
     rgb_coarse, weights_coarse, depth_coarse, ins_coarse = render_train(raw_coarse, z_vals_coarse, rays_d)
+    if on_coarse is not None:
+        on_coarse(ins_coarse[-args.N_ins:] if (args.is_train and args.N_ins is not None) else ins_coarse)
     det = (args.perturb == 0.)
     if det:
         u_arg = torch.linspace(0., 1., steps=args.N_importance, device=rays_d.device)

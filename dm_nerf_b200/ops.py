@@ -31,6 +31,12 @@ def get_mode() -> int:
     return _default_mode
 
 
+def reserve_sms(n: int) -> int:
+    """SMs the persistent MLP kernels leave free for kernels on other streams (``dmnerf_reserve_sms``); returns the
+    previous value.  Used by the overlapped training step; 0 everywhere else."""
+    return int(_lib.lib().dmnerf_reserve_sms(int(n)))
+
+
 def _stream() -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 

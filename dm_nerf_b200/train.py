@@ -10,7 +10,8 @@ from typing import Dict, Optional
 import torch
 
 from . import parallel
-from .networks.evaluator import img2mse, ins_criterion_device, ins_criterion_multi
+from . import ops
+from .networks.evaluator import img2mse, ins_criterion_device, ins_criterion_multi, ins_criterion_prepped, ins_label_prep
 from .networks.helpers import get_select_full, z_val_sample
 from .networks.penalizer import ins_penalizer
 from .networks.render import dm_nerf
@@ -24,7 +25,7 @@ class TrainStep:
 
     def __init__(self, position_embedder, view_embedder, model_coarse, model_fine, K, args, penalize: bool = True,
                  optimizer: Optional[torch.optim.Optimizer] = None, device_assignment: bool = True, max_label: int = 256,
-                 graph: bool = False):
+                 graph: bool = False, overlap_assignment: Optional[bool] = None):
         self.pe, self.ve, self.mc, self.mf, self.K = position_embedder, view_embedder, model_coarse, model_fine, K
         self.args = SimpleNamespace(**vars(args))
         self.args.is_train, self.args.N_ins = True, None
@@ -47,6 +48,13 @@ class TrainStep:
         else:
             self.opt = optimizer or torch.optim.Adam(self.params, lr=args.lrate, betas=(0.9, 0.999),
                                                      fused=self.params[0].is_cuda)
+        # overlap_assignment (default: on with graph=True): the two Hungarian assignments are serial one-warp kernels
+        # (~1 ms at K=93), so they run on side streams -- the coarse one beside the fine pass, the fine one beside the
+        # coarse model's backward (the two models' autograd graphs are disjoint: render.py:68 detaches the samples) --
+        # while the persistent MLP kernels leave `reserved_sms` SMs free for them (dmnerf_reserve_sms).
+        self.overlap = bool(self.graph_mode if overlap_assignment is None else overlap_assignment) and device_assignment
+        self.reserved_sms = 2
+        self._side = None
         self._graph = self._static = self._static_out = None
         self._K_dev = None
         self.z_coarse = z_val_sample(args.N_train, args.near, args.far, args.N_samples)     # train_dmsr.py:22
@@ -89,6 +97,65 @@ class TrainStep:
         return self._static_out
 
     def _step_eager(self, image, pose, labels, K, decay: bool = True) -> Dict[str, torch.Tensor]:
+        if self.overlap:
+            prev = ops.reserve_sms(self.reserved_sms)
+            try:
+                return self._step_overlapped(image, pose, labels, K, decay)
+            finally:
+                ops.reserve_sms(prev)
+        return self._step_serial(image, pose, labels, K, decay)
+
+    def _finish(self, decay: bool) -> None:
+        if self.flat is None:
+            self.flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=self.params[0].device)
+        parallel.allreduce_grads(self.params, self.flat)
+        self.opt.step()
+        if decay:
+            a = self.args
+            lr = a.lrate * (0.1 ** (self.iteration / (a.lrate_decay * 1000)))              # train_dmsr.py:68-72
+            for group in self.opt.param_groups:
+                group["lr"] = lr
+            self.iteration += 1
+
+    def _step_overlapped(self, image, pose, labels, K, decay: bool) -> Dict[str, torch.Tensor]:
+        a = self.args
+        main = torch.cuda.current_stream()
+        if self._side is None:
+            self._side = (torch.cuda.Stream(), torch.cuda.Stream())
+        side_c, side_f = self._side
+        target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
+        prep = ins_label_prep(target_i, a.ins_num, self.max_label)
+        got = {}
+
+        def on_coarse(ins_coarse):
+            side_c.wait_stream(main)
+            with torch.cuda.stream(side_c):
+                got["c"] = ins_criterion_prepped([ins_coarse], prep)[0][0]
+
+        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, on_coarse=on_coarse)
+        side_f.wait_stream(main)
+        with torch.cuda.stream(side_f):
+            ins_f = ins_criterion_prepped([info["ins_fine"]], prep)[0][0]
+        # coarse model: losses and backward on the main stream while the fine assignment runs on its side stream
+        rgb_c = img2mse(info["rgb_coarse"], target_c)
+        pen_c = ins_penalizer(info["raw_coarse"], info["z_vals_coarse"], info["depth_coarse"], rays[1], a) if self.penalize else None
+        main.wait_stream(side_c)
+        loss_c = rgb_c + got["c"] if pen_c is None else rgb_c + got["c"] + pen_c
+        self.opt.zero_grad(set_to_none=True)
+        loss_c.backward()
+        rgb_f = img2mse(info["rgb_fine"], target_c)
+        pen_f = ins_penalizer(info["raw_fine"], info["z_vals_fine"], info["depth_fine"], rays[1], a) if self.penalize else None
+        main.wait_stream(side_f)
+        loss_f = rgb_f + ins_f if pen_f is None else rgb_f + ins_f + pen_f
+        loss_f.backward()
+        self._finish(decay)
+        rgb_loss, ins_loss = (rgb_c + rgb_f).detach(), (got["c"] + ins_f).detach()
+        out = {"total": (loss_c + loss_f).detach(), "rgb": rgb_loss, "ins": ins_loss}
+        if self.penalize:
+            out["emptiness"] = (pen_c + pen_f).detach()
+        return out
+
+    def _step_serial(self, image, pose, labels, K, decay: bool = True) -> Dict[str, torch.Tensor]:
         a = self.args
         target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
         info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a)
@@ -108,15 +175,7 @@ class TrainStep:
             total = total + emptiness
         self.opt.zero_grad(set_to_none=True)          # backward then installs the fresh gradient tensors: no fills, no adds
         total.backward()
-        if self.flat is None:
-            self.flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=self.params[0].device)
-        parallel.allreduce_grads(self.params, self.flat)
-        self.opt.step()
-        if decay:
-            lr = a.lrate * (0.1 ** (self.iteration / (a.lrate_decay * 1000)))              # train_dmsr.py:68-72
-            for group in self.opt.param_groups:
-                group["lr"] = lr
-            self.iteration += 1
+        self._finish(decay)
         out = {"total": total.detach(), "rgb": rgb_loss.detach(), "ins": ins_loss.detach()}
         if emptiness is not None:
             out["emptiness"] = emptiness.detach()

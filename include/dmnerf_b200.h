@@ -176,6 +176,12 @@ int  dmnerf_selftest_issue_cost(int mode, int count, long long* out2_dev, void* 
 /* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the forward's descriptors; bit1: in wgrad's).
  * flags < 0 only queries.  Returns the previous value. */
 int  dmnerf_debug_flags(int flags);
+/* SM partitioning for overlapped training (train_dmsr.py:24-72 as one step; networks/evaluator.py:45-46 is the
+ * assignment that runs beside the ray kernels): the persistent one-CTA-per-SM MLP kernels (forward, dgrad, wgrad) take a
+ * whole SM's shared memory, so a small kernel on another stream (dmnerf_hungarian) can only run concurrently if some SMs
+ * are left free.  n >= 0 sets how many SMs those kernels leave unused from now on (process-wide; grids are fixed at launch,
+ * so a captured CUDA graph keeps the value it was captured with); n < 0 only queries.  Returns the previous value. */
+int  dmnerf_reserve_sms(int n);
 
 #ifdef __cplusplus
 }

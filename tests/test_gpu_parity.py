@@ -681,3 +681,37 @@ def test_train_step_cuda_graph_replay():
             fresh.load_state_dict(mc.state_dict())
             ref = fresh.query_rays(o, d, z)
     assert torch.equal(got, ref)
+
+
+def test_train_step_overlapped_assignment_matches_serial():
+    """TrainStep(overlap_assignment=True): assignments on side streams, coarse and fine backward as two calls, MLP
+    kernels on sm_count - 2 SMs -- same losses and (up to the order of the wgrad reductions) the same gradients as
+    the serial step on the same rays and uniforms."""
+    from types import SimpleNamespace
+    from dm_nerf_b200 import ops
+    from dm_nerf_b200.train import TrainStep
+    k, n, H, W = 8, 256, 48, 64
+    pe, ve = embedders()
+    Kmat = torch.tensor([[60.0, 0, W / 2], [0, -60.0, H / 2], [0, 0, -1]])
+    args = SimpleNamespace(N_train=n, near=4.0, far=15.0, N_samples=64, N_importance=128, perturb=1.0, ins_num=k,
+                           tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+    gen = torch.Generator().manual_seed(6)
+    lab = cu((torch.arange(H)[:, None] // 12 * 2 + torch.arange(W)[None] // 32) % k)
+    img = cu(torch.rand(H, W, 3, generator=gen))
+    pose = torch.eye(4)[:3, :4].clone(); pose[2, 3] = 6.0
+    res = {}
+    with _bf16_mode():
+        for overlap in (False, True):
+            mc, mf = make_model(k, 1), make_model(k, 2)
+            ts = TrainStep(pe, ve, mc, mf, Kmat, args, penalize=True, graph=False, overlap_assignment=overlap)
+            torch.manual_seed(11)
+            out = ts.step(img, cu(pose), lab)
+            torch.cuda.synchronize()
+            res[overlap] = ({k_: float(v) for k_, v in out.items()},
+                            [p.grad.detach().clone() for p in ts.params])
+    assert ops.reserve_sms(-1) == 0                          # the reservation does not outlive the step
+    for key in res[False][0]:
+        assert abs(res[True][0][key] - res[False][0][key]) <= 1e-5 * max(1.0, abs(res[False][0][key])), key
+    for g1, g0 in zip(res[True][1], res[False][1]):
+        scale = float(g0.abs().max()) + 1e-12
+        assert float((g1 - g0).abs().max()) <= 2e-4 * scale

@@ -24,12 +24,12 @@ img = torch.rand(H, W, 3, device=dev)
 lab = ((torch.arange(H, device=dev)[:, None] // 60) * 8 + (torch.arange(W, device=dev)[None] // 80)) % k
 targs = SimpleNamespace(N_train=n, near=4.0, far=15.0, N_samples=64, N_importance=128, perturb=1.0, ins_num=k,
                         tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
-for graph in (False, True):
+for graph, overlap in ((False, False), (True, False), (True, True)):
     torch.manual_seed(0)
     mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
     mc.load_state_dict(orc.init_params(k, 1)); mf.load_state_dict(orc.init_params(k, 2))
     mc, mf = mc.to(dev), mf.to(dev)
-    ts = TrainStep(pe, ve, mc, mf, Kmat, targs, penalize=True, graph=graph)
+    ts = TrainStep(pe, ve, mc, mf, Kmat, targs, penalize=True, graph=graph, overlap_assignment=overlap)
     w0 = mc.mlps[0].weight.detach().clone()
     losses = []
     for _ in range(5):
@@ -42,7 +42,7 @@ for graph in (False, True):
     dt = (time.perf_counter() - t0) / steps
     ls = [float(x) for x in losses]
     moved = float((mc.mlps[0].weight.detach() - w0).abs().max())
-    print(f"graph={graph}: {dt*1e3:.2f} ms/step {n/dt:.0f} rays/s | loss first {ls[0]:.4f} mid {ls[len(ls)//2]:.4f} last {ls[-1]:.4f} "
+    print(f"graph={graph} overlap={overlap}: {dt*1e3:.2f} ms/step {n/dt:.0f} rays/s | loss first {ls[0]:.4f} mid {ls[len(ls)//2]:.4f} last {ls[-1]:.4f} "
           f"finite={all(np.isfinite(ls))} | max|dW0| {moved:.3e} | iteration {ts.iteration}")
 if os.environ.get("DMNERF_PROFILE"):
     from torch.profiler import profile, ProfilerActivity
