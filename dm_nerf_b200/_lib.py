@@ -90,6 +90,7 @@ _SIGNATURES = {
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
     "dmnerf_reserve_sms": (_int, [_int]),
+    "dmnerf_adam_step": (_int, [_p, _p, _p, _p, _i64, _p, _f, _p, _f, _f, _f, _f, _p]),
 }
 
 EXPORTS = tuple(_SIGNATURES)

@@ -531,6 +531,9 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     tc::pack_dgrad_kernel<<<static_cast<unsigned>((dg_elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_f32_kernel<<<(tc::kF32Floats + 255) / 256, 256, 0, st>>>(pr, im, image);
     DM_LAUNCH_CHECK("pack_bf16");
+    // the operand streams of the parked forward variants are only written while one of them is selected (the host
+    // cache key includes that bit): training repacks every step and should not pay for them
+    if (!(g_tc_debug_flags & (4 | 8 | 32))) return DMNERF_OK;
     if (int rc = tc2::pack_v2(params, ins_num, packed, st)) return rc;
     return tc3::pack_v3(params, ins_num, packed, st);
 }

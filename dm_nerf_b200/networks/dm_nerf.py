@@ -73,7 +73,7 @@ class DM_NeRF(nn.Module):
 
     def packed(self, mode: int) -> torch.Tensor:
         params = self._ordered_params()
-        key = tuple((p.data_ptr(), p._version) for p in params)
+        key = tuple((p.data_ptr(), p._version) for p in params) + (ops.variant_selected(),)
         hit = self._packed.get(mode)
         if hit is None or hit[0] != key:
             hit = (key, ops.pack_weights(params, self.ins_num, mode))

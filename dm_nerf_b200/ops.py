@@ -31,6 +31,11 @@ def get_mode() -> int:
     return _default_mode
 
 
+def variant_selected() -> bool:
+    """True while a parked forward variant is selected by the debug flags (their operand streams are packed on demand)."""
+    return bool(_lib.lib().dmnerf_debug_flags(-1) & (4 | 8 | 32))
+
+
 def reserve_sms(n: int) -> int:
     """SMs the persistent MLP kernels leave free for kernels on other streams (``dmnerf_reserve_sms``); returns the
     previous value.  Used by the overlapped training step; 0 everywhere else."""

@@ -8,8 +8,10 @@ from types import SimpleNamespace
 from typing import Dict, Optional
 
 import torch
+import torch.distributed as dist
 
 from . import parallel
+from .optim import FlatAdam
 from . import ops
 from .networks.evaluator import img2mse, ins_criterion_device, ins_criterion_multi, ins_criterion_prepped, ins_label_prep
 from .networks.helpers import get_select_full, z_val_sample
@@ -40,14 +42,11 @@ class TrainStep:
         self.graph_mode = bool(graph)
         if self.graph_mode and not (device_assignment and optimizer is None):
             raise ValueError("TrainStep(graph=True) needs device_assignment=True and its own optimizer")
-        # train_dmsr.py:127-128 builds torch.optim.Adam(params, lr, betas=(0.9, 0.999)); fused=True is the same update
-        # in one launch for all 60 tensors instead of one foreach chain per step (0.6 -> 0.1 ms of host time)
-        if self.graph_mode:
-            self.lr_t = torch.tensor(float(args.lrate), device=self.params[0].device)
-            self.opt = torch.optim.Adam(self.params, lr=self.lr_t, betas=(0.9, 0.999), fused=True, capturable=True)
-        else:
-            self.opt = optimizer or torch.optim.Adam(self.params, lr=args.lrate, betas=(0.9, 0.999),
-                                                     fused=self.params[0].is_cuda)
+        # train_dmsr.py:127-128 builds torch.optim.Adam(params, lr, betas=(0.9, 0.999)).  Default here: the same update
+        # as one dmnerf_adam_step launch per model over flat buffers (optim.py; torch's fused multi-tensor Adam took
+        # 0.155 ms per step for the 60 tensors); pass ``optimizer`` to keep a torch optimizer (eager mode only).
+        self.lr_t = torch.tensor(float(args.lrate), device=self.params[0].device) if self.graph_mode else None
+        self.opt = optimizer or FlatAdam([model_coarse, model_fine], lr=args.lrate, betas=(0.9, 0.999), lr_tensor=self.lr_t)
         # overlap_assignment (default: on with graph=True): the two Hungarian assignments are serial one-warp kernels
         # (~1 ms at K=93), so they run on side streams -- the coarse one beside the fine pass, the fine one beside the
         # coarse model's backward (the two models' autograd graphs are disjoint: render.py:68 detaches the samples) --
@@ -106,15 +105,31 @@ class TrainStep:
         return self._step_serial(image, pose, labels, K, decay)
 
     def _finish(self, decay: bool) -> None:
-        if self.flat is None:
-            self.flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=self.params[0].device)
-        parallel.allreduce_grads(self.params, self.flat)
-        self.opt.step()
+        if isinstance(self.opt, FlatAdam):
+            # ONE all-reduce per model on the backward's own flat gradient buffer (no gather / scatter copies); the
+            # 1/world of the mean is applied inside the update
+            world = dist.get_world_size() if dist.is_initialized() else 1
+            bufs = self.opt.grad_buffers()
+            if world > 1:
+                for b in bufs:
+                    dist.all_reduce(b, op=dist.ReduceOp.SUM)
+            self.opt.step(bufs, grad_scale=1.0 / world)
+        else:
+            if self.flat is None:
+                self.flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=self.params[0].device)
+            parallel.allreduce_grads(self.params, self.flat)
+            self.opt.step()
+            # torch's fused multi-tensor Adam updates the parameters without moving their version counters, which are
+            # the packed-weight caches' keys: without this the next forward would run on stale operand images
+            self.mc._packed.clear(); self.mf._packed.clear()
         if decay:
             a = self.args
             lr = a.lrate * (0.1 ** (self.iteration / (a.lrate_decay * 1000)))              # train_dmsr.py:68-72
-            for group in self.opt.param_groups:
-                group["lr"] = lr
+            if isinstance(self.opt, FlatAdam):
+                self.opt.lr = lr
+            else:
+                for group in self.opt.param_groups:
+                    group["lr"] = lr
             self.iteration += 1
 
     def _step_overlapped(self, image, pose, labels, K, decay: bool) -> Dict[str, torch.Tensor]:

@@ -176,6 +176,13 @@ int  dmnerf_selftest_issue_cost(int mode, int count, long long* out2_dev, void* 
 /* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the forward's descriptors; bit1: in wgrad's).
  * flags < 0 only queries.  Returns the previous value. */
 int  dmnerf_debug_flags(int flags);
+/* The optimizer step of the training loop (train_dmsr.py:62-72: torch.optim.Adam(betas=(0.9,0.999)).step() + lr decay)
+ * as one kernel over a flat fp32 parameter buffer: p, g, m, v are DEVICE buffers of n floats (n % 4 == 0, 16-byte
+ * aligned; g is read-only).  step_dev: device int32 holding the 1-based step count t; lr_dev: device float with the
+ * learning rate, or NULL to use `lr`.  g is scaled by grad_scale first (1/world_size after a summing all-reduce).
+ * Same arithmetic as torch.optim.Adam with weight_decay = 0, amsgrad = False. */
+int  dmnerf_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev, float lr,
+                      const int* step_dev, float beta1, float beta2, float eps, float grad_scale, void* stream);
 /* SM partitioning for overlapped training (train_dmsr.py:24-72 as one step; networks/evaluator.py:45-46 is the
  * assignment that runs beside the ray kernels): the persistent one-CTA-per-SM MLP kernels (forward, dgrad, wgrad) take a
  * whole SM's shared memory, so a small kernel on another stream (dmnerf_hungarian) can only run concurrently if some SMs

@@ -673,6 +673,12 @@ def test_train_step_cuda_graph_replay():
             assert float((cur - prev).abs().max()) > 0
             prev = cur
         assert ts.iteration == 3 + 4                     # three warm-up steps before the capture, then one per call
+        # the replayed forward must run on the UPDATED weights (operand images repacked inside the graph): on a fixed
+        # image the loss then falls steadily; with stale images it would only wander with the ray draw
+        img = cu(torch.rand(H, W, 3, generator=gen))
+        hist = [float(ts.step(img, cu(pose), lab)["total"]) for _ in range(60)]
+        print("graph replay loss:", " ".join(f"{x:.3f}" for x in hist[::6]))
+        assert np.mean(hist[-10:]) < np.mean(hist[:10]) - 0.1, (np.mean(hist[:10]), np.mean(hist[-10:]))
         o, d = cu(torch.rand(5, 3, generator=gen)), cu(torch.randn(5, 3, generator=gen))
         z = cu(torch.sort(torch.rand(5, 64, generator=gen) * 11 + 4, -1)[0])
         with torch.no_grad():
@@ -715,3 +721,44 @@ def test_train_step_overlapped_assignment_matches_serial():
     for g1, g0 in zip(res[True][1], res[False][1]):
         scale = float(g0.abs().max()) + 1e-12
         assert float((g1 - g0).abs().max()) <= 2e-4 * scale
+
+
+def test_flat_adam_matches_torch_adam():
+    """dmnerf_adam_step over the flat parameter buffers against torch.optim.Adam(betas=(0.9, 0.999)) (the optimizer
+    train_dmsr.py:127-128 builds) on the same gradients for 6 steps, incl. a learning-rate change and grad_scale;
+    parameters stay valid nn.Parameters (state_dict round trip) and the packed-weight caches are refreshed."""
+    from dm_nerf_b200.optim import FlatAdam
+    k = 8
+    ours = [make_model(k, 1), make_model(k, 2)]
+    ref = [make_model(k, 1), make_model(k, 2)]
+    opt = FlatAdam(ours, lr=5e-4)
+    ref_params = [p for m in ref for p in m.parameters()]
+    topt = torch.optim.Adam(ref_params, lr=5e-4, betas=(0.9, 0.999))
+    for m_o, m_r in zip(ours, ref):
+        for (n1, p1), (n2, p2) in zip(m_o.named_parameters(), m_r.named_parameters()):
+            assert n1 == n2 and torch.equal(p1, p2)
+    gen = torch.Generator().manual_seed(3)
+    for it in range(6):
+        lr = 5e-4 * (0.1 ** (it / 3))
+        opt.lr = lr
+        for grp in topt.param_groups:
+            grp["lr"] = lr
+        for p_o, p_r in zip(opt.params, ref_params):
+            g = cu(torch.randn(p_o.shape, generator=gen) * (10.0 ** float(torch.randint(-4, 1, (1,), generator=gen))))
+            p_o.grad = (2.0 * g).clone()            # scaled back by grad_scale = 0.5
+            p_r.grad = g.clone()
+        opt.step(grad_scale=0.5)
+        topt.step()
+        for p_o, p_r in zip(opt.params, ref_params):
+            assert float((p_o - p_r).abs().max()) <= 2e-7 + 1e-5 * lr, it
+    sd = ours[0].state_dict()
+    fresh = make_model(k, 5)
+    fresh.load_state_dict(sd)
+    o, d = cu(torch.rand(5, 3, generator=gen)), cu(torch.randn(5, 3, generator=gen))
+    z = cu(torch.sort(torch.rand(5, 64, generator=gen) * 11 + 4, -1)[0])
+    with torch.no_grad():
+        assert torch.equal(ours[0].query_rays(o, d, z), fresh.query_rays(o, d, z))
+    tsd = opt.state_dict()
+    assert len(tsd["state"]) == 60 and float(tsd["state"][0]["step"]) == 6.0
+    t2 = torch.optim.Adam(ref_params, lr=1.0)
+    t2.load_state_dict(tsd)                                  # torch accepts the exported state
