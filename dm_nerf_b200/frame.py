@@ -9,7 +9,10 @@ from typing import Dict, Optional
 
 import torch
 
+import numpy as np
+
 from . import ops
+from .networks.manipulator import manipulator
 from .networks.render import dm_nerf
 
 
@@ -46,4 +49,71 @@ def render_pixels(position_embedder, view_embedder, model_coarse, model_fine, hw
             out["ins"][a:b] = info["ins_fine"]
             if labels:
                 out["labels"][a:b] = ops.label_argmax(info["ins_fine"])
+    return out
+
+
+def deform_offsets(H: int, W: int, deform_func: str, amplitude: float = 0.0) -> torch.Tensor:
+    """The per-pixel x-offset of the target rays' origins in ``mani_mode == 'deform'`` (manipulator.py:396-429): a
+    function of the image row only, repeated along the row.  ``amplitude`` is the view's ``deform_v[i]`` ('sin' only).
+    Returns float64 [H*W] like the reference (added to the fp32 origins)."""
+    v = np.linspace(1, H, H)
+    if deform_func == "sin":
+        v = np.sin(((8 * np.pi) / 400) * v) * amplitude
+    elif deform_func == "ex":
+        v = np.exp(-1 * v / 50)
+    elif deform_func == "linear":
+        v = (v - 200) / 215
+    elif deform_func == "abs_linear":
+        v = np.abs(v - 200) / 200
+    elif deform_func == "ln":
+        v = np.log(v / 200)
+    else:
+        raise ValueError(f"unknown deform_func {deform_func!r}")
+    return torch.from_numpy(np.repeat(v[:, None], W, axis=-1).reshape(-1))
+
+
+def manipulate_pixels(position_embedder, view_embedder, model_coarse, model_fine, hwk, ori_pose, targets, args,
+                      pix0: int = 0, count: Optional[int] = None, chunk: int = 16384,
+                      out: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, torch.Tensor]:
+    """One edited view: the chunk loop of ``manipulator_demo`` (manipulator.py:383-469) over pixels [pix0, pix0+count).
+    ``targets``: one dict per moved object with ``tar_id`` and either ``transformation`` (4x4; the target rays come
+    from ``transformation @ ori_pose``, :431-433) or ``deform_func`` (+ ``amplitude``; origins shifted along x, :396-429).
+    Rays are generated on the device per chunk and results land in preallocated buffers (no torch.cat growth).
+    Returns rgb [n,3], ins [n,K+1], tar_rgb [n,3], tar_ins [n,K+1] and labels uint8 [n] (argmax over ins[..., :-1])."""
+    H, W, K = hwk
+    dev = next(model_fine.parameters()).device
+    if count is None:
+        count = int(H) * int(W) - pix0
+    kins = model_fine.ins_num
+    if out is None:
+        out = {"rgb": torch.empty((count, 3), device=dev), "ins": torch.empty((count, kins + 1), device=dev),
+               "tar_rgb": torch.empty((count, 3), device=dev), "tar_ins": torch.empty((count, kins + 1), device=dev),
+               "labels": torch.empty((count,), dtype=torch.uint8, device=dev)}
+    ori_pose = torch.as_tensor(ori_pose, dtype=torch.float32)
+    margs = SimpleNamespace(N_samples=args.N_samples, N_importance=args.N_importance, near=args.near, far=args.far,
+                            target_label=[int(t["tar_id"]) for t in targets])
+    tar_poses, offsets = [], []
+    for t in targets:
+        if t.get("deform_func") is not None:
+            tar_poses.append(ori_pose)
+            offsets.append(deform_offsets(int(H), int(W), t["deform_func"], float(t.get("amplitude", 0.0))).to(dev))
+        else:
+            tar_poses.append(torch.as_tensor(t["transformation"], dtype=torch.float32).cpu() @ ori_pose.cpu())
+            offsets.append(None)
+    with torch.no_grad():
+        for a in range(0, count, chunk):
+            b = min(count, a + chunk)
+            ro, rd = ops.rays_k(int(H), int(W), K, ori_pose, pix0 + a, b - a, dev)
+            tars = []
+            for pose, off in zip(tar_poses, offsets):
+                if off is None:
+                    to, td = ops.rays_k(int(H), int(W), K, pose, pix0 + a, b - a, dev)
+                else:
+                    to, td = ro.clone(), rd
+                    to[:, 0] = (to[:, 0] + off[pix0 + a:pix0 + b]).float()          # fp32 + fp64 -> fp32, as :427
+                tars.append(torch.stack([to, td], 0))
+            rgb, ins, tar_rgb, tar_ins = manipulator(position_embedder, view_embedder, model_coarse, model_fine,
+                                                     torch.stack([ro, rd], 0), torch.stack(tars, 0), margs)
+            out["rgb"][a:b], out["ins"][a:b], out["tar_rgb"][a:b], out["tar_ins"][a:b] = rgb, ins, tar_rgb, tar_ins
+            out["labels"][a:b] = ops.label_argmax(ins[:, :-1].contiguous())
     return out

@@ -38,6 +38,27 @@ def get_select_full(rgb, pose, K, ins_target, N_train, numpy_rng=False):
     return rgb.reshape(-1, rgb.shape[-1])[idx], ins_target.reshape(-1)[idx], batch_rays
 
 
+def get_select_crop(rgb, pose, K, ins_target, ins_index, crop_mask, N_train):
+    """helpers.py:64-96 (ScanNet sampling, train_scannet.py): 30 % of the batch from the labelled pixels ``ins_index``,
+    the rest from the crop mask; labelled rays come LAST (``dm_nerf`` slices ``[-N_ins:]``, render.py:88-90).
+    Host glue with the reference's numpy draws -- including its indexing of ``crop_indices`` (not of the set difference)
+    by the unlabelled draw, helpers.py:84-85 -- but rays are generated for the selected pixels only.
+    Returns (target_c [N_train,3], target_i [N_ins], batch_rays [2,N_train,3], N_ins)."""
+    N_ins = min(int(N_train * 0.3), len(ins_index))
+    N_rgb = N_train - N_ins
+    H, W, _ = rgb.shape
+    crop_indices = np.where(np.asarray(crop_mask.cpu() if torch.is_tensor(crop_mask) else crop_mask).reshape(-1) == 1)[0]
+    ins_index_np = np.asarray(ins_index.cpu() if torch.is_tensor(ins_index) else ins_index).reshape(-1)
+    labeled_idx = ins_index_np[np.random.choice(ins_index_np.shape[0], size=[N_ins], replace=False)]
+    n_unlabeled = len(set(crop_indices.tolist()) - set(labeled_idx.tolist()))
+    unlabeled_idx = crop_indices[np.random.choice(n_unlabeled, size=[N_rgb], replace=False)]
+    idx = torch.from_numpy(np.concatenate([unlabeled_idx, labeled_idx]).astype(np.int64)).to(rgb.device)
+    ro, rd = ops.rays_k(int(H), int(W), K, pose, 0, int(N_train), rgb.device, pix_idx=idx)
+    target_c = rgb.reshape(-1, rgb.shape[-1])[idx]
+    target_i = ins_target.reshape(-1)[idx[N_rgb:]]
+    return target_c, target_i, torch.stack([ro, rd], 0), N_ins
+
+
 def z_val_sample(N_rays, near, far, N_samples):
     """helpers.py:114-119: near + linspace(0,1,S)*(far-near), one row broadcast to every ray."""
     dev = torch.device("cuda", torch.cuda.current_device())

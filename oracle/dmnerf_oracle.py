@@ -17,6 +17,8 @@ Randomness is always *injected* (``t_rand``, ``u``) so that parity runs share un
 from __future__ import annotations
 
 import math
+
+import numpy as np
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -425,6 +427,32 @@ def get_rays_k(H: int, W: int, K: Tensor, c2w: Tensor):
     rays_d = torch.sum(dirs[..., None, :] * c2w[:3, :3], -1)
     rays_o = c2w[:3, -1].expand(rays_d.shape)
     return rays_o, rays_d
+
+
+def get_select_full(rgb: Tensor, pose: Tensor, K: Tensor, ins_target: Tensor, n_train: int):
+    """helpers.py:99-111: n_train distinct pixels (numpy draw), their rays / colours / labels."""
+    H, W, _ = rgb.shape
+    rays_o, rays_d = get_rays_k(H, W, K, pose)
+    idx = torch.from_numpy(np.random.choice(H * W, size=[n_train], replace=False))
+    return (rgb.reshape(-1, 3)[idx], ins_target.reshape(-1)[idx],
+            torch.stack([rays_o.reshape(-1, 3)[idx], rays_d.reshape(-1, 3)[idx]], 0))
+
+
+def get_select_crop(rgb: Tensor, pose: Tensor, K: Tensor, ins_target: Tensor, ins_index, crop_mask: Tensor, n_train: int):
+    """helpers.py:64-96: 30 % labelled pixels (drawn from ins_index) placed LAST, the rest from the crop mask.  The
+    unlabelled draw indexes ``crop_indices`` with positions drawn over the SIZE of the set difference (:84-85)."""
+    n_ins = min(int(n_train * 0.3), len(ins_index))
+    n_rgb = n_train - n_ins
+    H, W, _ = rgb.shape
+    rays_o, rays_d = get_rays_k(H, W, K, pose)
+    crop_indices = np.where(crop_mask.reshape(-1).numpy() == 1)[0]
+    ins_index = np.asarray(ins_index)
+    labeled = ins_index[np.random.choice(ins_index.shape[0], size=[n_ins], replace=False)]
+    n_unl = len(set(crop_indices.tolist()) - set(labeled.tolist()))
+    unlabeled = crop_indices[np.random.choice(n_unl, size=[n_rgb], replace=False)]
+    idx = torch.from_numpy(np.concatenate([unlabeled, labeled]).astype(np.int64))
+    return (rgb.reshape(-1, 3)[idx], ins_target.reshape(-1)[idx[n_rgb:]],
+            torch.stack([rays_o.reshape(-1, 3)[idx], rays_d.reshape(-1, 3)[idx]], 0), n_ins)
 
 
 # ----------------------------------------------------------------------------------------

@@ -91,7 +91,12 @@ def synth_rays(n, seed, near_origin=True):
     return torch.stack([o, d], 0)
 
 
+ONLY = set(sys.argv[1:])          # `python oracle/gen_golden.py select_crop ...` rewrites just the named fixtures
+
+
 def save(name, **arrs):
+    if ONLY and name not in ONLY:
+        return
     os.makedirs(OUT, exist_ok=True)
     conv = {}
     for k, v in arrs.items():
@@ -303,6 +308,23 @@ def main():
         out[0].backward()
         save(f"ins_criterion_{tag}", pred=pred.detach(), labels=lab, ins_num=np.int64(kk),
              losses=torch.stack([o.reshape(()).float() for o in out]).detach(), grad=pred.grad)
+
+    # ---- adjacent (8f-3): pixel selection of the training loops (helpers.py:64-111), numpy draws seeded ----------
+    H, W = 12, 16
+    focal = 0.5 * W / np.tan(0.5 * 0.6911)
+    K = torch.tensor([[focal, 0, W / 2], [0, -focal, H / 2], [0, 0, -1]], dtype=torch.float32)
+    c2w = orc.pose_spherical(111.0, -65.0, 7.0)
+    g = torch.Generator().manual_seed(31)
+    rgb = torch.rand(H, W, 3, generator=g)
+    ins_t = torch.randint(0, 7, (H, W), generator=g)
+    crop = torch.zeros(H, W); crop[2:10, 3:14] = 1
+    ins_index = np.where((crop.reshape(-1).numpy() == 1) & (ins_t.reshape(-1).numpy() < 4))[0]
+    np.random.seed(1234)
+    tc, ti, br, n_ins = R.helpers.get_select_crop(rgb, c2w, K, ins_t, ins_index, crop, 40)
+    np.random.seed(1234)
+    fc, fi, fr = R.helpers.get_select_full(rgb, c2w, K, ins_t, 40)
+    save("select_crop", K=K, c2w=c2w, rgb=rgb, ins_target=ins_t, crop_mask=crop, ins_index=ins_index, N_train=np.int64(40),
+         seed=np.int64(1234), target_c=tc, target_i=ti, rays=br, N_ins=np.int64(n_ins), full_c=fc, full_i=fi, full_rays=fr)
 
     torch.rand = rq._orig
 

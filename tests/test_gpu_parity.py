@@ -750,7 +750,7 @@ def test_flat_adam_matches_torch_adam():
         opt.step(grad_scale=0.5)
         topt.step()
         for p_o, p_r in zip(opt.params, ref_params):
-            assert float((p_o - p_r).abs().max()) <= 2e-7 + 1e-5 * lr, it
+            assert float((p_o.detach() - p_r.detach()).abs().max()) <= 2e-7 + 1e-5 * lr, it
     sd = ours[0].state_dict()
     fresh = make_model(k, 5)
     fresh.load_state_dict(sd)
@@ -762,3 +762,60 @@ def test_flat_adam_matches_torch_adam():
     assert len(tsd["state"]) == 60 and float(tsd["state"][0]["step"]) == 6.0
     t2 = torch.optim.Adam(ref_params, lr=1.0)
     t2.load_state_dict(tsd)                                  # torch accepts the exported state
+
+
+def test_pixel_selection_vs_golden(golden):
+    """helpers.get_select_crop / get_select_full(numpy_rng=True) against the reference's own outputs (helpers.py:64-111)
+    under the same numpy seed: same pixels in the same order (labelled rays last), rays generated for those pixels only."""
+    from dm_nerf_b200.networks.helpers import get_select_crop, get_select_full
+    g = golden("select_crop")
+    rgb, ins_t = cu(T(g["rgb"])), cu(torch.from_numpy(g["ins_target"]))
+    np.random.seed(int(g["seed"]))
+    tc, ti, rays, n_ins = get_select_crop(rgb, T(g["c2w"]), T(g["K"]), ins_t, g["ins_index"], T(g["crop_mask"]), int(g["N_train"]))
+    assert n_ins == int(g["N_ins"]) and rays.shape == (2, int(g["N_train"]), 3)
+    close(tc, g["target_c"], 0.0); close(rays[0], g["rays"][0], 0.0); close(rays[1], g["rays"][1], 1e-6)
+    assert np.array_equal(ti.cpu().numpy(), g["target_i"])
+    np.random.seed(int(g["seed"]))
+    fc, fi, fr = get_select_full(rgb, T(g["c2w"]), T(g["K"]), ins_t, int(g["N_train"]), numpy_rng=True)
+    close(fc, g["full_c"], 0.0); close(fr[1], g["full_rays"][1], 1e-6)
+    assert np.array_equal(fi.cpu().numpy(), g["full_i"])
+
+
+def test_manipulate_pixels_matches_chunked_manipulator():
+    """frame.manipulate_pixels (the chunk loop of manipulator_demo, manipulator.py:383-469): a rigid target and a
+    'sin' deform target; equals calling ``manipulator`` on the same rays with the same uniforms, whatever the chunking."""
+    from types import SimpleNamespace
+    from dm_nerf_b200 import ops
+    from dm_nerf_b200.frame import manipulate_pixels, deform_offsets
+    from dm_nerf_b200.networks.manipulator import manipulator
+    k, H, W = 8, 10, 12
+    mc, mf = make_model(k, 1, 8.0), make_model(k, 2, 8.0)
+    pe, ve = embedders()
+    Kmat = torch.tensor([[14.0, 0, W / 2], [0, -14.0, H / 2], [0, 0, -1]])
+    pose = orc.pose_spherical(20.0, -65.0, 7.0)
+    th = 0.3
+    trans = torch.tensor([[np.cos(th), -np.sin(th), 0, 0.2], [np.sin(th), np.cos(th), 0, -0.1], [0, 0, 1, 0], [0, 0, 0, 1]],
+                         dtype=torch.float32)
+    targets = [{"tar_id": 3, "transformation": trans}, {"tar_id": 5, "deform_func": "sin", "amplitude": 0.18}]
+    args = SimpleNamespace(N_samples=64, N_importance=128, near=4.0, far=15.0)
+    torch.manual_seed(21)
+    whole = manipulate_pixels(pe, ve, mc, mf, (H, W, Kmat), pose, targets, args, chunk=H * W)
+    # the same view through the reference-surface call
+    ro, rd = ops.rays_k(H, W, Kmat, pose, 0, H * W, DEV)
+    to, td = ops.rays_k(H, W, Kmat, trans @ pose, 0, H * W, DEV)
+    do = ro.clone(); do[:, 0] = (do[:, 0] + deform_offsets(H, W, "sin", 0.18).to(DEV)).float()
+    margs = SimpleNamespace(N_samples=64, N_importance=128, near=4.0, far=15.0, target_label=[3, 5])
+    torch.manual_seed(21)
+    with torch.no_grad():
+        rgb, ins, tar_rgb, tar_ins = manipulator(pe, ve, mc, mf, torch.stack([ro, rd], 0),
+                                                 torch.stack([torch.stack([to, td], 0), torch.stack([do, rd], 0)], 0), margs)
+    assert torch.equal(whole["rgb"], rgb) and torch.equal(whole["ins"], ins)
+    assert torch.equal(whole["tar_rgb"], tar_rgb) and torch.equal(whole["tar_ins"], tar_ins)
+    assert torch.equal(whole["labels"].long(), torch.sigmoid(ins[:, :-1]).argmax(-1)) or \
+        float((whole["labels"].long() != ins[:, :-1].argmax(-1)).float().mean()) < 0.02
+    # deform rows: sin(8 pi / 400 * row) * amplitude, constant along a row (manipulator.py:401-405)
+    off = deform_offsets(H, W, "sin", 0.18).reshape(H, W)
+    assert torch.allclose(off[:, 0], torch.sin(torch.arange(1, H + 1).double() * (8 * np.pi / 400)) * 0.18)
+    assert bool((off == off[:, :1]).all())
+    for name in ("ex", "linear", "abs_linear", "ln"):
+        assert deform_offsets(H, W, name).shape == (H * W,)

@@ -205,3 +205,18 @@ def test_host_ins_criterion_vs_golden(golden, tag):
     np.testing.assert_allclose(pred2.grad.numpy(), g["grad"], rtol=1e-4, atol=1e-8)
     single = ev.ins_criterion(pred3.detach(), torch.from_numpy(g["labels"]), int(g["ins_num"]))
     np.testing.assert_allclose(float(multi[1][0].detach()), float(single[0]), rtol=2e-6)
+
+
+def test_pixel_selection(golden):
+    """get_select_full / get_select_crop (helpers.py:64-111) with the numpy draws seeded like the fixture's."""
+    g = golden("select_crop")
+    rgb, pose, K, ins_t = T(g["rgb"]), T(g["c2w"]), T(g["K"]), torch.from_numpy(g["ins_target"])
+    np.random.seed(int(g["seed"]))
+    tc, ti, rays, n_ins = orc.get_select_crop(rgb, pose, K, ins_t, g["ins_index"], T(g["crop_mask"]), int(g["N_train"]))
+    assert n_ins == int(g["N_ins"])
+    same(tc, g["target_c"]); same(rays, g["rays"])
+    assert np.array_equal(ti.numpy(), g["target_i"])
+    np.random.seed(int(g["seed"]))
+    fc, fi, fr = orc.get_select_full(rgb, pose, K, ins_t, int(g["N_train"]))
+    same(fc, g["full_c"]); same(fr, g["full_rays"])
+    assert np.array_equal(fi.numpy(), g["full_i"])
