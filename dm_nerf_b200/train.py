@@ -52,7 +52,7 @@ class TrainStep:
         # coarse model's backward (the two models' autograd graphs are disjoint: render.py:68 detaches the samples) --
         # while the persistent MLP kernels leave `reserved_sms` SMs free for them (dmnerf_reserve_sms).
         self.overlap = bool(self.graph_mode if overlap_assignment is None else overlap_assignment) and device_assignment
-        self.reserved_sms = 2
+        self.reserved_sms = 1
         self._side = None
         self._graph = self._static = self._static_out = None
         self._K_dev = None

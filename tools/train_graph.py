@@ -30,6 +30,7 @@ for graph, overlap in ((False, False), (True, False), (True, True)):
     mc.load_state_dict(orc.init_params(k, 1)); mf.load_state_dict(orc.init_params(k, 2))
     mc, mf = mc.to(dev), mf.to(dev)
     ts = TrainStep(pe, ve, mc, mf, Kmat, targs, penalize=True, graph=graph, overlap_assignment=overlap)
+    ts.reserved_sms = int(os.environ.get('DMNERF_RESERVE', ts.reserved_sms))
     w0 = mc.mlps[0].weight.detach().clone()
     losses = []
     for _ in range(5):
