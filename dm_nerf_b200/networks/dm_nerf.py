@@ -65,6 +65,7 @@ class DM_NeRF(nn.Module):
         self.ins_linear = nn.Linear(W // 2, ins_num + 1)
         self.rgb_linear = nn.Linear(W // 2, 3)
         self._packed = {}
+        self._dirty = False
 
     # -- packed-weight cache ---------------------------------------------------------------------
     def _ordered_params(self):
@@ -72,6 +73,12 @@ class DM_NeRF(nn.Module):
         return [sd[k] for k in ops.PARAM_ORDER]
 
     def packed(self, mode: int) -> torch.Tensor:
+        """Operand image of the current weights, cached on (data_ptr, version) of the 30 tensors.  A forward with
+        gradients enabled marks the cache dirty: an optimizer step follows it, and not every optimizer moves the version
+        counters (torch's fused multi-tensor Adam does not), so the next query always repacks."""
+        if self._dirty:
+            self._packed.clear()
+            self._dirty = False
         params = self._ordered_params()
         key = tuple((p.data_ptr(), p._version) for p in params) + (ops.variant_selected(),)
         hit = self._packed.get(mode)
@@ -89,14 +96,16 @@ class DM_NeRF(nn.Module):
         (render.py:49-61 / manipulator.py:108-134 in one launch)."""
         mode = ops.get_mode()
         if self._wants_grad():
-            return ops._MlpFn.apply(rays_o, rays_d, z_vals, None, self.ins_num, mode, self.packed(mode),
-                                    *self._ordered_params())
+            packed = self.packed(mode)
+            self._dirty = True
+            return ops._MlpFn.apply(rays_o, rays_d, z_vals, None, self.ins_num, mode, packed, *self._ordered_params())
         return ops.mlp_fwd(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)[0]
 
     def forward(self, x):
         """x[..., 90] already embedded (dm_nerf.py:80-106)."""
         mode = ops.get_mode()
         if self._wants_grad():
-            return ops._MlpFn.apply(None, None, None, x, self.ins_num, mode, self.packed(mode),
-                                    *self._ordered_params())
+            packed = self.packed(mode)
+            self._dirty = True
+            return ops._MlpFn.apply(None, None, None, x, self.ins_num, mode, packed, *self._ordered_params())
         return ops.mlp_fwd_embedded(x, self.packed(mode), self.ins_num, mode)[0]

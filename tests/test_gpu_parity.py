@@ -819,3 +819,29 @@ def test_manipulate_pixels_matches_chunked_manipulator():
     assert bool((off == off[:, :1]).all())
     for name in ("ex", "linear", "abs_linear", "ln"):
         assert deform_offsets(H, W, name).shape == (H * W,)
+
+
+def test_packed_weight_cache_sees_fused_adam_updates():
+    """The reference's loop with torch.optim.Adam(fused=True) (train_dmsr.py:127-128 + :62-66): that optimizer updates
+    the parameters without moving their version counters, which key the packed operand cache.  A training forward
+    marks the cache dirty, so both the next training forward and a no-grad render run on the updated weights."""
+    k = 8
+    m = make_model(k, 3)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-2, fused=True)
+    gen = torch.Generator().manual_seed(2)
+    o, d = cu(torch.rand(64, 3, generator=gen)), cu(torch.randn(64, 3, generator=gen))
+    z = cu(torch.sort(torch.rand(64, 64, generator=gen) * 11 + 4, -1)[0])
+    with _bf16_mode():
+        losses = []
+        for _ in range(3):
+            raw = m.query_rays(o, d, z)
+            loss = (raw[..., :3] ** 2).mean()
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(float(loss.detach()))
+        assert losses[1] != losses[0] and losses[2] < losses[0]
+        fresh = make_model(k, 9)
+        fresh.load_state_dict(m.state_dict())
+        with torch.no_grad():
+            assert torch.equal(m.query_rays(o, d, z), fresh.query_rays(o, d, z))
