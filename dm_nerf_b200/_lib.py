@@ -18,6 +18,7 @@ SO_PATH = os.path.join(PKG_DIR, "libdmnerf_b200.so")
 
 MODE_FP32, MODE_BF16 = 0, 1
 COMP_DROP_EMPTY, COMP_RAW_INS = 1, 2
+PEN_ACCUMULATE = 2
 NUM_PARAMS = 30
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -73,8 +74,8 @@ _SIGNATURES = {
     "dmnerf_fine_z": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
     "dmnerf_sort_cat": (_int, [C.POINTER(_p), C.POINTER(_int), _int, _i64, _p, _p]),
     "dmnerf_jitter_z": (_int, [_p, _p, _i64, _int, _p, _p]),
-    "dmnerf_penalizer_fwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _p, _p, _p]),
-    "dmnerf_penalizer_bwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _p, _p, _p, _p]),
+    "dmnerf_penalizer_fwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _int, _p, _p, _p]),
+    "dmnerf_penalizer_bwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _int, _p, _p, _p, _p]),
     "dmnerf_exchange": (_int, [_p, _p, _p, _p, _int, _int, _i64, _int, _int, _p, _p, _p]),
     "dmnerf_rays_k": (_int, [_int, _int, C.POINTER(_f), C.POINTER(_f), _i64, _p, _i64, _p, _p, _p]),
     "dmnerf_rays_k_dev": (_int, [_int, _int, _p, _p, _i64, _p, _i64, _p, _p, _p]),

@@ -32,11 +32,22 @@ def _query(model, rays_o, rays_d, z_vals, position_embedder, view_embedder):
 
 
 def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_vals_coarse, args,
-            t_rand=None, u=None, on_coarse=None):
+            t_rand=None, u=None, on_coarse=None, penalizer=None):
     """render.py:31-96.  ``t_rand`` [N,Sc] / ``u`` [N,N_importance] inject the uniforms; when absent
     they are drawn with torch.rand in the reference's order (jitter first, then u).  ``on_coarse(ins_coarse)``, if
     given, is called as soon as the coarse pass is composited (the training step starts the coarse instance
-    assignment on a side stream there, beside the fine pass)."""
+    assignment on a side stream there, beside the fine pass).  ``penalizer=(tolerance, deta_w)`` evaluates
+    ``ins_penalizer`` (penalizer.py:58-62) of both passes inside the compositing nodes and adds ``emptiness_coarse`` /
+    ``emptiness_fine`` to the returned dict (same values as calling ``ins_penalizer`` on the outputs; one fused
+    backward per pass instead of two gradients of ``raw`` that autograd then sums)."""
+    def composite(raw, z):
+        if penalizer is not None and torch.is_grad_enabled() and raw.requires_grad:
+            return ops.composite_penalized(raw, z, rays_d, COMP_DROP_EMPTY, True, penalizer[0], penalizer[1])
+        out = render_train(raw, z, rays_d)
+        if penalizer is not None:
+            return out + (ops.penalizer(raw, z, out[2].detach(), rays_d, penalizer[0], penalizer[1]),)
+        return out + (None,)
+
     rays_o, rays_d = rays
     rays_o, rays_d = rays_o.float().contiguous(), rays_d.float().contiguous()
     z_vals_coarse = z_vals_coarse.float()
@@ -48,7 +59,7 @@ def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_
     else:
         z_vals_coarse = z_vals_coarse.contiguous()
     raw_coarse = _query(model_coarse, rays_o, rays_d, z_vals_coarse, position_embedder, view_embedder)
-    rgb_coarse, weights_coarse, depth_coarse, ins_coarse = render_train(raw_coarse, z_vals_coarse, rays_d)
+    rgb_coarse, weights_coarse, depth_coarse, ins_coarse, pen_coarse = composite(raw_coarse, z_vals_coarse)
     if on_coarse is not None:
         on_coarse(ins_coarse[-args.N_ins:] if (args.is_train and args.N_ins is not None) else ins_coarse)
     det = (args.perturb == 0.)
@@ -58,11 +69,12 @@ def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_
         u_arg = u if u is not None else torch.rand([n, args.N_importance], device=rays_d.device)
     z_vals_fine = ops.fine_z(z_vals_coarse, weights_coarse.detach(), int(args.N_importance), u_arg)
     raw_fine = _query(model_fine, rays_o, rays_d, z_vals_fine, position_embedder, view_embedder)
-    rgb_fine, weights_fine, depth_fine, ins_fine = render_train(raw_fine, z_vals_fine, rays_d)
+    rgb_fine, weights_fine, depth_fine, ins_fine, pen_fine = composite(raw_fine, z_vals_fine)
     if args.is_train and args.N_ins is not None:
         ins_fine = ins_fine[-args.N_ins:]
         ins_coarse = ins_coarse[-args.N_ins:]
-    return {'rgb_fine': rgb_fine, 'ins_fine': ins_fine, 'z_vals_fine': z_vals_fine, 'raw_fine': raw_fine,
+    extra = {} if penalizer is None else {'emptiness_coarse': pen_coarse, 'emptiness_fine': pen_fine}
+    return {**extra, 'rgb_fine': rgb_fine, 'ins_fine': ins_fine, 'z_vals_fine': z_vals_fine, 'raw_fine': raw_fine,
             'raw_coarse': raw_coarse, 'rgb_coarse': rgb_coarse, 'ins_coarse': ins_coarse,
             'z_vals_coarse': z_vals_coarse, 'depth_fine': depth_fine, 'depth_coarse': depth_coarse}
 

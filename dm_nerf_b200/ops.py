@@ -358,16 +358,31 @@ def jitter_z(z, t_rand):
 # ---------------------------------------------------------------------------------------------------
 
 
+def penalizer_fwd(raw, z, depth, rays_d, tolerance: float, deta_w: float, flags: int):
+    n, s, c = raw.shape
+    partials = torch.empty(4, dtype=torch.float32, device=raw.device)
+    loss = torch.empty(1, dtype=torch.float32, device=raw.device)
+    check(_lib.lib().dmnerf_penalizer_fwd(_ptr(raw), _ptr(z), _ptr(depth), _ptr(rays_d), n, s, c, tolerance, deta_w,
+                                          flags, _ptr(partials), _ptr(loss), _stream()), "dmnerf_penalizer_fwd")
+    _count(2)
+    return loss, partials
+
+
+def penalizer_bwd(raw, z, depth, rays_d, tolerance, deta_w, flags, partials, d_loss, d_raw):
+    n, s, c = raw.shape
+    check(_lib.lib().dmnerf_penalizer_bwd(_ptr(raw), _ptr(z), _ptr(depth), _ptr(rays_d), n, s, c, tolerance, deta_w,
+                                          flags, _ptr(partials), _ptr(d_loss), _ptr(d_raw), _stream()),
+          "dmnerf_penalizer_bwd")
+    _count()
+    return d_raw
+
+
 class _PenalizerFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, raw, z, depth, rays_d, tolerance, deta_w):
         raw, z, depth, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(depth, "depth"), _f32(rays_d, "rays_d")
-        n, s, c = raw.shape
-        partials = torch.empty(4, dtype=torch.float32, device=raw.device)
-        loss = torch.empty(1, dtype=torch.float32, device=raw.device)
-        check(_lib.lib().dmnerf_penalizer_fwd(_ptr(raw), _ptr(z), _ptr(depth), _ptr(rays_d), n, s, c, tolerance,
-                                              deta_w, _ptr(partials), _ptr(loss), _stream()), "dmnerf_penalizer_fwd")
-        _count(2)
+        ctx.flags = 0
+        loss, partials = penalizer_fwd(raw, z, depth, rays_d, tolerance, deta_w, 0)
         ctx.save_for_backward(raw, z, depth, rays_d, partials)
         ctx.tol, ctx.dw = tolerance, deta_w
         return loss
@@ -375,18 +390,43 @@ class _PenalizerFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, d_loss):
         raw, z, depth, rays_d, partials = ctx.saved_tensors
-        n, s, c = raw.shape
         d_loss = _f32(d_loss, "d_loss").reshape(1)
-        d_raw = torch.empty_like(raw)
-        check(_lib.lib().dmnerf_penalizer_bwd(_ptr(raw), _ptr(z), _ptr(depth), _ptr(rays_d), n, s, c, ctx.tol, ctx.dw,
-                                              _ptr(partials), _ptr(d_loss), _ptr(d_raw), _stream()),
-              "dmnerf_penalizer_bwd")
-        _count()
+        d_raw = penalizer_bwd(raw, z, depth, rays_d, ctx.tol, ctx.dw, ctx.flags, partials, d_loss, torch.empty_like(raw))
         return d_raw, None, None, None, None, None
 
 
 def penalizer(raw, z, depth, rays_d, tolerance: float, deta_w: float) -> torch.Tensor:
     return _PenalizerFn.apply(raw, z, depth.reshape(-1).detach(), rays_d, float(tolerance), float(deta_w))
+
+
+class _CompositePenalizedFn(torch.autograd.Function):
+    """``render_train`` (render.py:6-28) and ``ins_penalizer`` (penalizer.py:58-62, on the composited depth, detached)
+    of the same ``raw`` as ONE autograd node: the backward writes the compositing gradient and the penalizer adds its
+    own into it in place (DMNERF_PEN_ACCUMULATE) -- no zero-filled second gradient, no [N,S,C] gradient-sum pass."""
+
+    @staticmethod
+    def forward(ctx, raw, z, rays_d, flags, ins_detach, tolerance, deta_w):
+        raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
+        rgb, weights, depth, ins = composite_fwd(raw, z, rays_d, flags)
+        ctx.pen_flags = 0
+        loss, partials = penalizer_fwd(raw, z, depth, rays_d, tolerance, deta_w, 0)
+        ctx.save_for_backward(raw, z, rays_d, depth, partials)
+        ctx.flags, ctx.ins_detach, ctx.tol, ctx.dw = flags, ins_detach, tolerance, deta_w
+        return rgb, weights, depth, ins, loss
+
+    @staticmethod
+    def backward(ctx, d_rgb, d_weights, d_depth, d_ins, d_loss):
+        raw, z, rays_d, depth, partials = ctx.saved_tensors
+        d_raw = composite_bwd(raw, z, rays_d, ctx.flags, ctx.ins_detach, d_rgb, d_depth, d_weights, d_ins)
+        if d_loss is not None:
+            d_loss = _f32(d_loss, "d_loss").reshape(1)
+            penalizer_bwd(raw, z, depth, rays_d, ctx.tol, ctx.dw, ctx.pen_flags | _lib.PEN_ACCUMULATE, partials, d_loss, d_raw)
+        return d_raw, None, None, None, None, None, None
+
+
+def composite_penalized(raw, z, rays_d, flags: int, ins_detach: bool, tolerance: float, deta_w: float):
+    """(rgb, weights, depth, ins, emptiness_loss); see _CompositePenalizedFn."""
+    return _CompositePenalizedFn.apply(raw, z, rays_d, flags, ins_detach, float(tolerance), float(deta_w))
 
 
 # ---------------------------------------------------------------------------------------------------

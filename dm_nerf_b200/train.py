@@ -147,19 +147,20 @@ class TrainStep:
             with torch.cuda.stream(side_c):
                 got["c"] = ins_criterion_prepped([ins_coarse], prep)[0][0]
 
-        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, on_coarse=on_coarse)
+        pen = (a.tolerance, a.deta_w) if self.penalize else None     # emptiness loss inside the compositing nodes
+        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, on_coarse=on_coarse, penalizer=pen)
         side_f.wait_stream(main)
         with torch.cuda.stream(side_f):
             ins_f = ins_criterion_prepped([info["ins_fine"]], prep)[0][0]
         # coarse model: losses and backward on the main stream while the fine assignment runs on its side stream
         rgb_c = img2mse(info["rgb_coarse"], target_c)
-        pen_c = ins_penalizer(info["raw_coarse"], info["z_vals_coarse"], info["depth_coarse"], rays[1], a) if self.penalize else None
+        pen_c = info.get("emptiness_coarse")
         main.wait_stream(side_c)
         loss_c = rgb_c + got["c"] if pen_c is None else rgb_c + got["c"] + pen_c
         self.opt.zero_grad(set_to_none=True)
         loss_c.backward()
         rgb_f = img2mse(info["rgb_fine"], target_c)
-        pen_f = ins_penalizer(info["raw_fine"], info["z_vals_fine"], info["depth_fine"], rays[1], a) if self.penalize else None
+        pen_f = info.get("emptiness_fine")
         main.wait_stream(side_f)
         loss_f = rgb_f + ins_f if pen_f is None else rgb_f + ins_f + pen_f
         loss_f.backward()

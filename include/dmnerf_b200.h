@@ -112,13 +112,16 @@ int  dmnerf_jitter_z(const float* z, const float* t_rand, int64_t n, int s, floa
 /* ---- a7: emptiness penalizer --------------------------------------------------------------------
  * Replaces ins_penalizer/emptiness_penalizer (networks/penalizer.py:5-62).  partials: 4 floats
  * (device) = {sum_before, count_before, sum_middle, count_middle}; zeroed by the call.
- * loss (device scalar) = sum_before/((K+1)*max(count_before,1e-8)) + sum_middle/max(count_middle,1e-8). */
+ * loss (device scalar) = sum_before/((K+1)*max(count_before,1e-8)) + sum_middle/max(count_middle,1e-8).
+ * flags: DMNERF_PEN_ACCUMULATE (backward only) = d_raw already holds another gradient of the same raw (the compositing
+ * backward's) and the penalizer's is ADDED to the logits it weighs, nothing else is touched; 0 otherwise. */
+#define DMNERF_PEN_ACCUMULATE 2
 int  dmnerf_penalizer_fwd(const float* raw, const float* z, const float* depth, const float* rays_d,
-                          int64_t n, int s, int c, float tolerance, float deta_w, float* partials,
+                          int64_t n, int s, int c, float tolerance, float deta_w, int flags, float* partials,
                           float* loss, void* stream);
 /* d_raw[n,s,c] = d_loss * dLoss/draw (channels 0..3 are written as 0). d_loss: device scalar. */
 int  dmnerf_penalizer_bwd(const float* raw, const float* z, const float* depth, const float* rays_d,
-                          int64_t n, int s, int c, float tolerance, float deta_w, const float* partials,
+                          int64_t n, int s, int c, float tolerance, float deta_w, int flags, const float* partials,
                           const float* d_loss, float* d_raw, void* stream);
 
 /* ---- a10: exchanger -------------------------------------------------------------------------------

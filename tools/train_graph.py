@@ -24,6 +24,19 @@ img = torch.rand(H, W, 3, device=dev)
 lab = ((torch.arange(H, device=dev)[:, None] // 60) * 8 + (torch.arange(W, device=dev)[None] // 80)) % k
 targs = SimpleNamespace(N_train=n, near=4.0, far=15.0, N_samples=64, N_importance=128, perturb=1.0, ins_num=k,
                         tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+if os.environ.get("DMNERF_NCU"):
+    # one eager, serial step between cudaProfilerStart/Stop (ncu --profile-from-start off)
+    mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
+    mc.load_state_dict(orc.init_params(k, 1)); mf.load_state_dict(orc.init_params(k, 2))
+    ts = TrainStep(pe, ve, mc.to(dev), mf.to(dev), Kmat, targs, penalize=True, graph=False, overlap_assignment=False)
+    for _ in range(3):
+        ts.step(img, pose, lab)
+    torch.cuda.synchronize()
+    torch.cuda.profiler.start()
+    ts.step(img, pose, lab)
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
+    sys.exit(0)
 for graph, overlap in ((False, False), (True, False), (True, True)):
     torch.manual_seed(0)
     mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
