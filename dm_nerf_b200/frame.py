@@ -117,3 +117,22 @@ def manipulate_pixels(position_embedder, view_embedder, model_coarse, model_fine
             out["rgb"][a:b], out["ins"][a:b], out["tar_rgb"][a:b], out["tar_ins"][a:b] = rgb, ins, tar_rgb, tar_ins
             out["labels"][a:b] = ops.label_argmax(ins[:, :-1].contiguous())
     return out
+
+
+def query_occupancy(model_fine, points: torch.Tensor, voxel_size: float, chunk: int = 1 << 22) -> torch.Tensor:
+    """The field query of ``mesh_main`` (tools/mesh_generator.py:36-62): ``occ = 1 - exp(-relu(sigma) * voxel_size)`` at
+    arbitrary points (there: a 256^3 grid, embedded with zero view directions and sent through ``model_fine`` in N_test
+    chunks that are ``torch.cat``-ed).  Density does not depend on the view direction (dm_nerf.py:88-92 takes it from
+    the trunk, before the direction enters), so the points go through the fused ray kernel as one-sample rays
+    ``o = point, d = e_z, z = 0`` (``o + d*0`` is exact): no [M,90] embedding in HBM, results in one preallocated buffer."""
+    pts = points.reshape(-1, 3).float().contiguous()
+    m = pts.shape[0]
+    occ = torch.empty((m,), dtype=torch.float32, device=pts.device)
+    ez = torch.tensor([0.0, 0.0, 1.0], device=pts.device)
+    with torch.no_grad():
+        for a in range(0, m, chunk):
+            b = min(m, a + chunk)
+            raw = model_fine.query_rays(pts[a:b], ez.expand(b - a, 3).contiguous(),
+                                        torch.zeros((b - a, 1), dtype=torch.float32, device=pts.device))
+            occ[a:b] = 1.0 - torch.exp(-torch.relu(raw[:, 0, 3]) * voxel_size)
+    return occ.reshape(points.shape[:-1])

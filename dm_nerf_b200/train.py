@@ -142,31 +142,40 @@ class TrainStep:
         prep = ins_label_prep(target_i, a.ins_num, self.max_label)
         got = {}
 
+        def ins_loss_and_grad(ins_map):
+            # the instance loss AND its gradient w.r.t. the composited map, both on the side stream: the ~100 small
+            # kernels of that backward then run beside the ray kernels instead of in front of the compositing backward
+            leaf = ins_map.detach().requires_grad_(True)
+            loss = ins_criterion_prepped([leaf], prep)[0][0]
+            (grad,) = torch.autograd.grad(loss, leaf)
+            return loss.detach(), grad
+
         def on_coarse(ins_coarse):
             side_c.wait_stream(main)
             with torch.cuda.stream(side_c):
-                got["c"] = ins_criterion_prepped([ins_coarse], prep)[0][0]
+                got["c"] = ins_loss_and_grad(ins_coarse)
 
         pen = (a.tolerance, a.deta_w) if self.penalize else None     # emptiness loss inside the compositing nodes
         info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, on_coarse=on_coarse, penalizer=pen)
         side_f.wait_stream(main)
         with torch.cuda.stream(side_f):
-            ins_f = ins_criterion_prepped([info["ins_fine"]], prep)[0][0]
+            ins_f, g_ins_f = ins_loss_and_grad(info["ins_fine"])
         # coarse model: losses and backward on the main stream while the fine assignment runs on its side stream
         rgb_c = img2mse(info["rgb_coarse"], target_c)
         pen_c = info.get("emptiness_coarse")
         main.wait_stream(side_c)
-        loss_c = rgb_c + got["c"] if pen_c is None else rgb_c + got["c"] + pen_c
+        ins_c, g_ins_c = got["c"]
+        part_c = rgb_c if pen_c is None else rgb_c + pen_c
         self.opt.zero_grad(set_to_none=True)
-        loss_c.backward()
+        torch.autograd.backward([part_c, info["ins_coarse"]], [None, g_ins_c])
         rgb_f = img2mse(info["rgb_fine"], target_c)
         pen_f = info.get("emptiness_fine")
         main.wait_stream(side_f)
-        loss_f = rgb_f + ins_f if pen_f is None else rgb_f + ins_f + pen_f
-        loss_f.backward()
+        part_f = rgb_f if pen_f is None else rgb_f + pen_f
+        torch.autograd.backward([part_f, info["ins_fine"]], [None, g_ins_f])
         self._finish(decay)
-        rgb_loss, ins_loss = (rgb_c + rgb_f).detach(), (got["c"] + ins_f).detach()
-        out = {"total": (loss_c + loss_f).detach(), "rgb": rgb_loss, "ins": ins_loss}
+        rgb_loss, ins_loss = (rgb_c + rgb_f).detach(), ins_c + ins_f
+        out = {"total": (part_c + part_f).detach().reshape(()) + ins_loss, "rgb": rgb_loss, "ins": ins_loss}
         if self.penalize:
             out["emptiness"] = (pen_c + pen_f).detach()
         return out

@@ -882,3 +882,20 @@ def test_packed_weight_cache_sees_fused_adam_updates():
         fresh.load_state_dict(m.state_dict())
         with torch.no_grad():
             assert torch.equal(m.query_rays(o, d, z), fresh.query_rays(o, d, z))
+
+
+def test_query_occupancy_matches_zero_viewdir_query():
+    """frame.query_occupancy (mesh_main's grid query, tools/mesh_generator.py:36-62) against the oracle network on the
+    reference's own inputs: points embedded with ZERO view directions, occ = 1 - exp(-relu(sigma) * voxel)."""
+    from dm_nerf_b200.frame import query_occupancy
+    k = 16
+    m = make_model(k, 6, 4.0)
+    gen = torch.Generator().manual_seed(14)
+    pts = (torch.rand(7, 9, 5, 3, generator=gen) - 0.5) * 4
+    x = torch.cat([orc.embed(pts.reshape(-1, 3), 10), orc.embed(torch.zeros(7 * 9 * 5, 3), 4)], -1)
+    sigma = orc.mlp_forward(orc.init_params(k, 6, 4.0), x)[:, 3]
+    voxel = (15.0 - 4.0) / 128
+    ref = (1.0 - torch.exp(-torch.relu(sigma) * voxel)).reshape(7, 9, 5)
+    got = query_occupancy(m, cu(pts), voxel, chunk=100)
+    assert got.shape == (7, 9, 5)
+    close(got, ref, 1e-5)
