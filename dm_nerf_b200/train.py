@@ -138,8 +138,14 @@ class TrainStep:
         if self._side is None:
             self._side = (torch.cuda.Stream(), torch.cuda.Stream())
         side_c, side_f = self._side
+        # the operand images of the updated weights are packed on a side stream while the main stream draws the pixels
+        # and prepares the label one-hot (about 0.1 ms of small kernels on each side)
+        side_c.wait_stream(main)
+        with torch.cuda.stream(side_c):
+            self.mc.packed(ops.get_mode()); self.mf.packed(ops.get_mode())
         target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
         prep = ins_label_prep(target_i, a.ins_num, self.max_label)
+        main.wait_stream(side_c)
         got = {}
 
         def ins_loss_and_grad(ins_map):
