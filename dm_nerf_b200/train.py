@@ -14,7 +14,7 @@ from . import parallel
 from .optim import FlatAdam
 from . import ops
 from .networks.evaluator import img2mse, ins_criterion_device, ins_criterion_multi, ins_criterion_prepped, ins_label_prep
-from .networks.helpers import get_select_full, z_val_sample
+from .networks.helpers import get_select_crop, get_select_full, z_val_sample
 from .networks.penalizer import ins_penalizer
 from .networks.render import dm_nerf
 
@@ -60,7 +60,14 @@ class TrainStep:
         self.flat = None
         self.iteration = 0
 
-    def step(self, image, pose, labels) -> Dict[str, torch.Tensor]:
+    def step(self, image, pose, labels, ins_index=None, crop_mask=None) -> Dict[str, torch.Tensor]:
+        """``ins_index`` / ``crop_mask``: the ScanNet loop (train_scannet.py:24-66) -- pixels drawn by ``get_select_crop``
+        (30 % labelled, placed last), instance losses on the last ``N_ins`` rays only (render.py:88-90).  That draw is
+        the reference's host-side numpy code, so this variant runs eagerly and serially."""
+        if ins_index is not None:
+            if self.graph_mode:
+                raise ValueError("TrainStep(graph=True) cannot run the ScanNet step: get_select_crop draws on the host")
+            return self._step_serial(image, pose, labels, self.K, crop=(ins_index, crop_mask))
         if self.graph_mode:
             return self._step_graph(image, pose, labels)
         return self._step_eager(image, pose, labels, self.K)
@@ -186,9 +193,13 @@ class TrainStep:
             out["emptiness"] = (pen_c + pen_f).detach()
         return out
 
-    def _step_serial(self, image, pose, labels, K, decay: bool = True) -> Dict[str, torch.Tensor]:
+    def _step_serial(self, image, pose, labels, K, decay: bool = True, crop=None) -> Dict[str, torch.Tensor]:
         a = self.args
-        target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
+        if crop is not None:
+            a = SimpleNamespace(**vars(a))
+            target_c, target_i, rays, a.N_ins = get_select_crop(image, pose, K, labels, crop[0], crop[1], a.N_train)
+        else:
+            target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
         info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a)
         rgb_loss = img2mse(info["rgb_coarse"], target_c) + img2mse(info["rgb_fine"], target_c)
         emptiness = None

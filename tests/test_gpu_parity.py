@@ -934,3 +934,38 @@ def test_dm_nerf_shape_sweep_vs_oracle(n, k, sc, nimp):
     z_out = out["z_vals_fine"]
     assert bool(torch.all(z_out[:, 1:] >= z_out[:, :-1]))
     assert float(np.median(np.abs(z_out.cpu().numpy() - ref["z_vals_fine"].numpy()))) <= 2e-6
+
+
+def test_train_step_scannet_crop_sampling():
+    """TrainStep.step(..., ins_index, crop_mask): train_scannet.py:24-66 -- get_select_crop draw, instance losses on the
+    labelled rays only (dm_nerf slices ins_* to the last N_ins rows, render.py:88-90); the step runs and learns."""
+    from types import SimpleNamespace
+    from dm_nerf_b200.train import TrainStep
+    from dm_nerf_b200.networks.render import dm_nerf
+    from dm_nerf_b200.networks.helpers import z_val_sample
+    k, n, H, W = 8, 128, 24, 32
+    mc, mf = make_model(k, 1), make_model(k, 2)
+    pe, ve = embedders()
+    Kmat = torch.tensor([[30.0, 0, W / 2], [0, 30.0, H / 2], [0, 0, 1]])
+    args = SimpleNamespace(N_train=n, near=0.0, far=9.5, N_samples=64, N_importance=128, perturb=1.0, ins_num=k,
+                           tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+    gen = torch.Generator().manual_seed(9)
+    img = cu(torch.rand(H, W, 3, generator=gen))
+    lab = cu((torch.arange(H)[:, None] // 6 * 2 + torch.arange(W)[None] // 16) % k)
+    crop = torch.zeros(H, W); crop[2:22, 3:29] = 1
+    ins_index = np.where((crop.reshape(-1).numpy() == 1) & (np.arange(H * W) % 3 == 0))[0]
+    pose = torch.eye(4)[:3, :4].clone(); pose[2, 3] = -3.0
+    # the slice itself
+    rays = cu(torch.stack([torch.zeros(10, 3), torch.randn(10, 3, generator=gen)], 0))
+    a2 = SimpleNamespace(perturb=0.0, N_importance=128, is_train=True, N_ins=4)
+    with torch.no_grad():
+        out = dm_nerf(rays, pe, ve, mc, mf, z_val_sample(10, 0.0, 9.5, 64), a2)
+        a2.N_ins = None
+        full = dm_nerf(rays, pe, ve, mc, mf, z_val_sample(10, 0.0, 9.5, 64), a2)
+    assert out["ins_fine"].shape == (4, k) and torch.equal(out["ins_fine"], full["ins_fine"][-4:])
+    assert torch.equal(out["ins_coarse"], full["ins_coarse"][-4:]) and out["rgb_fine"].shape == (10, 3)
+    with _bf16_mode():
+        ts = TrainStep(pe, ve, mc, mf, Kmat, args, penalize=True, graph=False)
+        np.random.seed(3)
+        hist = [float(ts.step(img, pose, lab, ins_index=ins_index, crop_mask=crop)["total"]) for _ in range(30)]
+    assert all(np.isfinite(hist)) and np.mean(hist[-8:]) < np.mean(hist[:8]), hist
