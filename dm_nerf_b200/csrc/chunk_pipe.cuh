@@ -24,13 +24,14 @@ struct ChunkPipe {
     int64_t issued, consumed;
     bool there_and_back;      // per ray: chunks 0..n-1, then n-1..0 (recompute pass + reverse gradient pass)
     bool stores;              // the consumer bulk-stores tiles back out: wait for those reads before refilling
+    bool reverse;             // per ray: chunks n-1..0 only (single reverse gradient pass)
 
     __device__ __forceinline__ void init(const float* raw, float* ring, uint64_t* bars, int64_t first_ray, int64_t stride,
                                          int64_t n, int S_, int C_, int lane_, bool there_and_back_ = false,
-                                         bool stores_ = false) {
+                                         bool stores_ = false, bool reverse_ = false) {
         base = raw; tile_ptr = ring; tile0 = ptx::smem_u32(ring); bar0 = ptx::smem_u32(bars);
         ray0 = first_ray; ray_stride = stride; S = S_; C = C_; lane = lane_;
-        there_and_back = there_and_back_; stores = stores_;
+        there_and_back = there_and_back_; stores = stores_; reverse = reverse_;
         nchunk = (S + 31) >> 5;
         steps = there_and_back ? 2 * nchunk : nchunk;
         chunk_floats = 32 * C;
@@ -46,6 +47,7 @@ struct ChunkPipe {
     }
     __device__ __forceinline__ int chunk_of(int64_t k) const {
         const int c = static_cast<int>(k % steps);
+        if (reverse) return nchunk - 1 - c;
         return c < nchunk ? c : 2 * nchunk - 1 - c;
     }
     __device__ __forceinline__ void issue() {

@@ -55,7 +55,7 @@ __device__ __forceinline__ void scan_chunk(float sigma, float dist, bool valid, 
 __global__ void __launch_bounds__(kCompWarps * 32)
 composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
                      int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,
-                     float* __restrict__ weights, float* __restrict__ ins) {
+                     float* __restrict__ weights, float* __restrict__ ins, float* __restrict__ trans_out) {
     extern __shared__ float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t ray = static_cast<int64_t>(blockIdx.x) * kCompWarps + warp;
@@ -89,6 +89,7 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
         if (valid) {
             if (weights) weights[ray * S + s] = w;
+            if (trans_out) trans_out[ray * S + s] = trans;
             a_r += w * sigmoidf_ref(tile[lane * CP + 0]);
             a_g += w * sigmoidf_ref(tile[lane * CP + 1]);
             a_b += w * sigmoidf_ref(tile[lane * CP + 2]);
@@ -134,7 +135,7 @@ template <int ST>
 __global__ void __launch_bounds__(kCompBulkWarps * 32)
 composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
                           int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,
-                          float* __restrict__ weights, float* __restrict__ ins) {
+                          float* __restrict__ weights, float* __restrict__ ins, float* __restrict__ trans_out) {
     extern __shared__ __align__(128) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int per_warp = ST * 32 * C + 32;
@@ -192,6 +193,7 @@ composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
         scan_chunk(sigma, dist, valid, lane, carry, alpha, trans, w);
         if (valid) {
             if (weights) weights[ray * S + s] = w;
+            if (trans_out) trans_out[ray * S + s] = trans;
             a_r += w * sigmoidf_ref(tile[lane * C + 0]);
             a_g += w * sigmoidf_ref(tile[lane * C + 1]);
             a_b += w * sigmoidf_ref(tile[lane * C + 2]);
@@ -559,12 +561,146 @@ composite_bwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
     pipe.finish();
 }
 
+// Backward in ONE reverse pass, for callers that kept the forward's per-sample weights and transmittances and its
+// composited instance map (the training path does): what the recompute pass of composite_bwd_bulk_kernel rebuilds --
+// T_s, w_s, and sigmoid'(sum_s w_s logit_s) = p (1 - p) with p the forward's own output -- is read back instead
+// (8 B per sample), so every raw chunk crosses L2 -> shared memory once instead of twice and the warp never walks
+// a ray forwards.  alpha is recomputed from sigma and the sample spacing with the forward's formula.
+template <int ST>
+__global__ void __launch_bounds__(kCompBulkWarps * 32)
+composite_bwd_rev_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
+                         int64_t n, int S, int C, int flags, int ins_detach, const float* __restrict__ d_rgb,
+                         const float* __restrict__ d_depth, const float* __restrict__ d_weights,
+                         const float* __restrict__ d_ins, float* __restrict__ d_raw, const float* __restrict__ fwd_w,
+                         const float* __restrict__ fwd_t, const float* __restrict__ fwd_ins) {
+    extern __shared__ __align__(128) float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int per_warp = ST * 32 * C + 32;
+    float* ring = smem + warp * per_warp;
+    float* wbuf = ring + ST * 32 * C;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp + (kCompBulkWarps * per_warp & 1)) + warp * ST;
+    ChunkPipe<ST> pipe;
+    pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
+              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane, false, true, true);
+    const int L = C - 4;
+    const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
+    const bool need_logits = d_ins != nullptr;
+    const int last_c0 = ((S - 1) >> 5) << 5;
+
+    float norm = 0.f, suffix = 0.f, g_r = 0.f, g_g = 0.f, g_b = 0.f, g_d = 0.f;
+    float dA[4] = {0.f, 0.f, 0.f, 0.f};
+    // per-sample scalars of the NEXT chunk (z, z of the following sample, saved w and T) and, when that chunk opens a
+    // ray, the ray's norm: loaded one chunk ahead, outside the bulk pipe
+    float z_pre = 0.f, zn_pre = 0.f, w_pre = 0.f, t_pre = 0.f, norm_pre = 0.f;
+    auto prefetch = [&]() {
+        int64_t r2; int c2;
+        pipe.peek(r2, c2);
+        const int s2 = c2 + lane;
+        if (s2 < S) {
+            z_pre = __ldg(z + r2 * S + s2);
+            zn_pre = (s2 + 1 < S) ? __ldg(z + r2 * S + s2 + 1) : 0.f;
+            w_pre = __ldg(fwd_w + r2 * S + s2);
+            t_pre = __ldg(fwd_t + r2 * S + s2);
+        }
+        if (c2 == last_c0) {
+            const float dx = __ldg(rays_d + r2 * 3 + 0), dy = __ldg(rays_d + r2 * 3 + 1), dz = __ldg(rays_d + r2 * 3 + 2);
+            norm_pre = sqrtf(dx * dx + dy * dy + dz * dz);
+        }
+    };
+    if (!pipe.done()) prefetch();
+    while (!pipe.done()) {
+        int64_t ray; int c0;
+        float* tile = pipe.acquire(ray, c0);
+        const int cnt = min(32, S - c0);
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        const float zc = z_pre, zn_cur = zn_pre, w = valid ? w_pre : 0.f, trans = t_pre;
+        if (c0 == last_c0) {                               // a new ray starts at its LAST chunk
+            norm = norm_pre;
+            suffix = 0.f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int j = lane + 32 * q;
+                float a = (need_logits && j < Lout) ? __ldg(d_ins + ray * Lout + j) : 0.f;
+                if (need_logits && j < Lout && !(flags & DMNERF_COMP_RAW_INS)) {
+                    const float p = __ldg(fwd_ins + ray * Lout + j);
+                    a *= p * (1.0f - p);
+                }
+                dA[q] = a;
+            }
+            g_r = d_rgb ? __ldg(d_rgb + ray * 3 + 0) : 0.f;
+            g_g = d_rgb ? __ldg(d_rgb + ray * 3 + 1) : 0.f;
+            g_b = d_rgb ? __ldg(d_rgb + ray * 3 + 2) : 0.f;
+            g_d = d_depth ? __ldg(d_depth + ray) : 0.f;
+        }
+        if (!pipe.done()) prefetch();
+        float dw = 0.f, alpha = 0.f, dist = 0.f, sigma = 0.f, c_r = 0.f, c_g = 0.f, c_b = 0.f;
+        if (valid) {
+            dist = ((s + 1 < S) ? (zn_cur - zc) : 1e10f) * norm;
+            sigma = tile[lane * C + 3];
+            alpha = 1.0f - expf(-fmaxf(sigma, 0.0f) * dist);
+            c_r = sigmoidf_ref(tile[lane * C + 0]);
+            c_g = sigmoidf_ref(tile[lane * C + 1]);
+            c_b = sigmoidf_ref(tile[lane * C + 2]);
+            dw = g_r * c_r + g_g * c_g + g_b * c_b + g_d * zc;
+            if (d_weights) dw += d_weights[ray * S + s];
+        }
+        if (!ins_detach && need_logits) {
+            for (int r = 0; r < cnt; ++r) {
+                float part = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int j = lane + 32 * q;
+                    if (j < L) part += dA[q] * tile[r * C + 4 + j];
+                }
+                part = warp_sum(part);
+                if (lane == r) dw += part;
+            }
+        }
+        const float g = valid ? dw * w : 0.f;
+        float incl = g;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const float v = __shfl_down_sync(0xffffffffu, incl, o);
+            if (lane + o < 32) incl += v;
+        }
+        const float after = suffix + (incl - g);
+        suffix += __shfl_sync(0xffffffffu, incl, 0);
+        __syncwarp();
+        if (valid) {
+            const float t = (1.0f - alpha) + 1e-10f;
+            const float dalpha = dw * trans - after / t;
+            const float dsigma = (sigma > 0.f) ? dalpha * dist * (1.0f - alpha) : 0.f;
+            tile[lane * C + 0] = g_r * w * c_r * (1.0f - c_r);
+            tile[lane * C + 1] = g_g * w * c_g * (1.0f - c_g);
+            tile[lane * C + 2] = g_b * w * c_b * (1.0f - c_b);
+            tile[lane * C + 3] = dsigma;
+        }
+        wbuf[lane] = w;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) {
+                float* col = tile + 4 + j;
+                const float a = dA[q];
+#pragma unroll 8
+                for (int r = 0; r < cnt; ++r) col[r * C] = a * wbuf[r];
+            }
+        }
+        pipe.store_tile(d_raw + (ray * S + c0) * static_cast<int64_t>(C), tile, static_cast<uint32_t>(cnt) * C * 4);
+        __syncwarp();
+    }
+    pipe.finish();
+}
+
 }  // namespace dmnerf
 
 using namespace dmnerf;
 
 extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
-                                    int flags, float* rgb, float* depth, float* weights, float* ins, void* stream) {
+                                    int flags, float* rgb, float* depth, float* weights, float* ins, float* trans,
+                                    void* stream) {
     if (n == 0) return DMNERF_OK;
     DM_REQUIRE(raw && z && rays_d && rgb && depth && ins, DMNERF_EINVAL, "composite_fwd: null pointer");
     DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_fwd: n_samples %d outside [1,1024]", s);
@@ -591,7 +727,7 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
         const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
         auto launch = [&](auto kern) {
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins);
+            kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins, trans);
         };
         if (st == 2) launch(composite_fwd_bulk_kernel<2>);
         else if (st == 3) launch(composite_fwd_bulk_kernel<3>);
@@ -604,14 +740,15 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
     DM_CUDA(cudaFuncSetAttribute(composite_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned grid = static_cast<unsigned>((n + kCompWarps - 1) / kCompWarps);
     composite_fwd_kernel<<<grid, kCompWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb,
-                                                                            depth, weights, ins);
+                                                                            depth, weights, ins, trans);
     DM_LAUNCH_CHECK("composite_fwd_kernel");
     return DMNERF_OK;
 }
 
 extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
                                     int flags, int ins_detach, const float* d_rgb, const float* d_depth,
-                                    const float* d_weights, const float* d_ins, float* d_raw, void* stream) {
+                                    const float* d_weights, const float* d_ins, float* d_raw, const float* fwd_weights,
+                                    const float* fwd_trans, const float* fwd_ins, void* stream) {
     if (n == 0) return DMNERF_OK;
     DM_REQUIRE(raw && z && rays_d && d_raw, DMNERF_EINVAL, "composite_bwd: null pointer");
     DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024, DMNERF_EUNSUPPORTED, "composite_bwd: n_samples %d outside [1,1024]", s);
@@ -625,7 +762,8 @@ extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const floa
             DM_CUDA(cudaGetDevice(&dev));
             DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
         }
-        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * 32 * c + 32 + 5 * s) * sizeof(float) + st * 8) + 8; };
+        const bool rev = fwd_weights && fwd_trans && (fwd_ins || !d_ins || (flags & DMNERF_COMP_RAW_INS));
+        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * 32 * c + 32 + (rev ? 0 : 5 * s)) * sizeof(float) + st * 8) + 8; };
         const int dbg = tc_debug_flags();
         int st = kCompStages;
         if ((dbg >> 8) & 3) st = ((dbg >> 8) & 3) + 1;
@@ -642,7 +780,17 @@ extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const floa
                 kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb,
                                                                              d_depth, d_weights, d_ins, d_raw);
             };
-            if (st == 2) launch(composite_bwd_bulk_kernel<2>);
+            auto launch_rev = [&](auto kern) {
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb,
+                                                                             d_depth, d_weights, d_ins, d_raw, fwd_weights,
+                                                                             fwd_trans, fwd_ins);
+            };
+            if (rev) {
+                if (st == 2) launch_rev(composite_bwd_rev_kernel<2>);
+                else if (st == 3) launch_rev(composite_bwd_rev_kernel<3>);
+                else launch_rev(composite_bwd_rev_kernel<4>);
+            } else if (st == 2) launch(composite_bwd_bulk_kernel<2>);
             else if (st == 3) launch(composite_bwd_bulk_kernel<3>);
             else launch(composite_bwd_bulk_kernel<4>);
             DM_LAUNCH_CHECK("composite_bwd_bulk_kernel");

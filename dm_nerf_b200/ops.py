@@ -223,7 +223,7 @@ class _MlpFn(torch.autograd.Function):
 # ---------------------------------------------------------------------------------------------------
 
 
-def composite_fwd(raw, z, rays_d, flags: int, want_weights: bool = True):
+def composite_fwd(raw, z, rays_d, flags: int, want_weights: bool = True, want_trans: bool = False):
     raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
     n, s, c = raw.shape
     dev = raw.device
@@ -232,9 +232,12 @@ def composite_fwd(raw, z, rays_d, flags: int, want_weights: bool = True):
     depth = torch.empty((n,), dtype=torch.float32, device=dev)
     ins = torch.empty((n, lout), dtype=torch.float32, device=dev)
     weights = torch.empty((n, s), dtype=torch.float32, device=dev) if want_weights else None
+    trans = torch.empty((n, s), dtype=torch.float32, device=dev) if want_trans else None
     _timed_call(f"dmnerf_composite_fwd[S={s}]", _lib.lib().dmnerf_composite_fwd, _ptr(raw), _ptr(z), _ptr(rays_d),
-                n, s, c, flags, _ptr(rgb), _ptr(depth), _ptr(weights), _ptr(ins), _stream())
+                n, s, c, flags, _ptr(rgb), _ptr(depth), _ptr(weights), _ptr(ins), _ptr(trans), _stream())
     _count()
+    if want_trans:
+        return rgb, weights, depth, ins, trans
     return rgb, weights, depth, ins
 
 
@@ -252,14 +255,16 @@ def hungarian(scores, n_valid):
     return col
 
 
-def composite_bwd(raw, z, rays_d, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins):
+def composite_bwd(raw, z, rays_d, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins, fwd=None):
+    """``fwd`` = (weights, trans, ins) kept from the forward -> one reverse pass instead of recompute + reverse."""
     n, s, c = raw.shape
     d_raw = torch.empty_like(raw)
     opt = lambda t: None if t is None else _f32(t, "grad")
     d_rgb, d_depth, d_weights, d_ins = opt(d_rgb), opt(d_depth), opt(d_weights), opt(d_ins)
+    fw, ft, fi = fwd if fwd is not None else (None, None, None)
     check(_lib.lib().dmnerf_composite_bwd(_ptr(raw), _ptr(z), _ptr(rays_d), n, s, c, flags, int(ins_detach),
                                           _ptr(d_rgb), _ptr(d_depth), _ptr(d_weights), _ptr(d_ins), _ptr(d_raw),
-                                          _stream()), "dmnerf_composite_bwd")
+                                          _ptr(fw), _ptr(ft), _ptr(fi), _stream()), "dmnerf_composite_bwd")
     _count()
     return d_raw
 
@@ -268,15 +273,16 @@ class _CompositeFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, raw, z, rays_d, flags, ins_detach):
         raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
-        rgb, weights, depth, ins = composite_fwd(raw, z, rays_d, flags)
-        ctx.save_for_backward(raw, z, rays_d)
+        rgb, weights, depth, ins, trans = composite_fwd(raw, z, rays_d, flags, want_trans=True)
+        ctx.save_for_backward(raw, z, rays_d, weights, trans, ins)
         ctx.flags, ctx.ins_detach = flags, ins_detach
         return rgb, weights, depth, ins
 
     @staticmethod
     def backward(ctx, d_rgb, d_weights, d_depth, d_ins):
-        raw, z, rays_d = ctx.saved_tensors
-        d_raw = composite_bwd(raw, z, rays_d, ctx.flags, ctx.ins_detach, d_rgb, d_depth, d_weights, d_ins)
+        raw, z, rays_d, weights, trans, ins = ctx.saved_tensors
+        d_raw = composite_bwd(raw, z, rays_d, ctx.flags, ctx.ins_detach, d_rgb, d_depth, d_weights, d_ins,
+                              fwd=(weights, trans, ins))
         return d_raw, None, None, None, None
 
 
@@ -407,17 +413,18 @@ class _CompositePenalizedFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, raw, z, rays_d, flags, ins_detach, tolerance, deta_w):
         raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
-        rgb, weights, depth, ins = composite_fwd(raw, z, rays_d, flags)
+        rgb, weights, depth, ins, trans = composite_fwd(raw, z, rays_d, flags, want_trans=True)
         ctx.pen_flags = 0
         loss, partials = penalizer_fwd(raw, z, depth, rays_d, tolerance, deta_w, 0)
-        ctx.save_for_backward(raw, z, rays_d, depth, partials)
+        ctx.save_for_backward(raw, z, rays_d, depth, partials, weights, trans, ins)
         ctx.flags, ctx.ins_detach, ctx.tol, ctx.dw = flags, ins_detach, tolerance, deta_w
         return rgb, weights, depth, ins, loss
 
     @staticmethod
     def backward(ctx, d_rgb, d_weights, d_depth, d_ins, d_loss):
-        raw, z, rays_d, depth, partials = ctx.saved_tensors
-        d_raw = composite_bwd(raw, z, rays_d, ctx.flags, ctx.ins_detach, d_rgb, d_depth, d_weights, d_ins)
+        raw, z, rays_d, depth, partials, weights, trans, ins = ctx.saved_tensors
+        d_raw = composite_bwd(raw, z, rays_d, ctx.flags, ctx.ins_detach, d_rgb, d_depth, d_weights, d_ins,
+                              fwd=(weights, trans, ins))
         if d_loss is not None:
             d_loss = _f32(d_loss, "d_loss").reshape(1)
             penalizer_bwd(raw, z, depth, rays_d, ctx.tol, ctx.dw, ctx.pen_flags | _lib.PEN_ACCUMULATE, partials, d_loss, d_raw)

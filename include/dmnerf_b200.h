@@ -77,14 +77,19 @@ int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num, int mode);
 /* ---- a5/a8: volume compositing ---------------------------------------------------------------
  * Replaces render_train (networks/render.py:6-28) [flags=DROP_EMPTY] and manipulator_render
  * (networks/manipulator.py:86-105) [flags=0].  raw [n,s,c]; z [n,s]; rays_d [n,3];
- * rgb [n,3]; depth [n]; weights [n,s] (may be NULL); ins [n, c-4-(DROP_EMPTY?1:0)]. */
+ * rgb [n,3]; depth [n]; weights [n,s] (may be NULL); ins [n, c-4-(DROP_EMPTY?1:0)]; trans [n,s] (may be NULL):
+ * the per-sample transmittances T_s, kept by training callers for the one-pass backward. */
 int  dmnerf_composite_fwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
-                          int flags, float* rgb, float* depth, float* weights, float* ins, void* stream);
+                          int flags, float* rgb, float* depth, float* weights, float* ins, float* trans, void* stream);
 /* Backward of the above.  d_ins touches only raw[...,4:] when ins_detach!=0 (render.py:22-24).
- * Any of d_rgb/d_depth/d_weights/d_ins may be NULL (= zero).  d_raw [n,s,c] is overwritten. */
+ * Any of d_rgb/d_depth/d_weights/d_ins may be NULL (= zero).  d_raw [n,s,c] is overwritten.
+ * fwd_weights / fwd_trans / fwd_ins: the forward's weights, trans and ins outputs for the SAME inputs, or NULL.  With
+ * all three the gradient is taken in one reverse pass over raw (nothing is recomputed forwards); otherwise the kernel
+ * first rebuilds them.  Same result either way. */
 int  dmnerf_composite_bwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
                           int flags, int ins_detach, const float* d_rgb, const float* d_depth,
-                          const float* d_weights, const float* d_ins, float* d_raw, void* stream);
+                          const float* d_weights, const float* d_ins, float* d_raw, const float* fwd_weights,
+                          const float* fwd_trans, const float* fwd_ins, void* stream);
 
 /* ---- a4: hierarchical sampler ------------------------------------------------------------------
  * Replaces sample_pdf (networks/helpers.py:123-155).  bins [n,n_bins]; weights [n,n_bins-1];

@@ -969,3 +969,26 @@ def test_train_step_scannet_crop_sampling():
         np.random.seed(3)
         hist = [float(ts.step(img, pose, lab, ins_index=ins_index, crop_mask=crop)["total"]) for _ in range(30)]
     assert all(np.isfinite(hist)) and np.mean(hist[-8:]) < np.mean(hist[:8]), hist
+
+
+@pytest.mark.parametrize("n,s,k,flags", [(37, 64, 32, 1), (9, 192, 93, 1), (5, 100, 16, 0), (3, 33, 8, 1)])
+def test_composite_backward_one_pass_equals_recompute(n, s, k, flags):
+    """dmnerf_composite_bwd with the forward's (weights, trans, ins) -- one reverse pass -- against the same entry without
+    them (recompute pass + reverse pass): same gradient, incl. d_weights, ragged chunk tails and the manipulator's flags=0
+    / non-detached instance weights."""
+    from dm_nerf_b200 import ops
+    gen = torch.Generator().manual_seed(n + s)
+    c = k + 5
+    raw = cu(torch.randn(n, s, c, generator=gen) * 1.5)
+    z = cu(torch.sort(torch.rand(n, s, generator=gen) * 11 + 4, -1)[0])
+    rd = cu(torch.randn(n, 3, generator=gen))
+    rgb, w, depth, ins, trans = ops.composite_fwd(raw, z, rd, flags, want_trans=True)
+    # T_s is the exclusive product of (1 - alpha + 1e-10) (render.py:18): weights = alpha * T
+    assert float(trans[:, 0].min()) == 1.0 and bool(torch.all(trans[:, 1:] <= trans[:, :-1] * (1 + 1e-6)))
+    d_rgb, d_depth = cu(torch.randn(n, 3, generator=gen)), cu(torch.randn(n, generator=gen))
+    d_w, d_ins = cu(torch.randn(n, s, generator=gen)), cu(torch.randn(ins.shape, generator=gen))
+    for detach in (True, False):
+        a = ops.composite_bwd(raw, z, rd, flags, detach, d_rgb, d_depth, d_w, d_ins)
+        b = ops.composite_bwd(raw, z, rd, flags, detach, d_rgb, d_depth, d_w, d_ins, fwd=(w, trans, ins))
+        scale = float(a.abs().max())
+        assert float((a - b).abs().max()) <= 2e-6 * scale, (detach, float((a - b).abs().max()), scale)

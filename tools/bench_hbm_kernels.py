@@ -44,7 +44,11 @@ for S in (64, 192):
     d_rgb, d_depth, d_ins = torch.randn_like(rgb), torch.randn_like(depth), torch.randn_like(ins)
     bwd_bytes = n * (2 * S * C * 4 + S * 4 + 12 + (3 + 1 + K) * 4)
     ms = timed(lambda: ops.composite_bwd(raw, z, rd, COMP_DROP_EMPTY, True, d_rgb, d_depth, None, d_ins))
-    print(f"composite_bwd S={S} K={K}: {ms*1e3:8.1f} us  {bwd_bytes/ms/1e6:7.0f} GB/s  {bwd_bytes/ms/1e6/peak:.3f}")
+    print(f"composite_bwd S={S} K={K}: {ms*1e3:8.1f} us  {bwd_bytes/ms/1e6:7.0f} GB/s  {bwd_bytes/ms/1e6/peak:.3f} (recompute + reverse pass)")
+    _, w5, _, ins5, t5 = ops.composite_fwd(raw, z, rd, COMP_DROP_EMPTY, want_trans=True)
+    ms = timed(lambda: ops.composite_bwd(raw, z, rd, COMP_DROP_EMPTY, True, d_rgb, d_depth, None, d_ins, fwd=(w5, t5, ins5)))
+    rb = bwd_bytes + n * 2 * S * 4
+    print(f"composite_bwd S={S} K={K}: {ms*1e3:8.1f} us  {rb/ms/1e6:7.0f} GB/s  {rb/ms/1e6/peak:.3f} (one reverse pass on the forward's w, T)")
     pen_bytes = n * (S * (K + 1) * 4 + S * 4 + 16)
     rawg = raw.clone().requires_grad_(True)
     def pen_f():
