@@ -20,7 +20,7 @@ struct ChunkPipe {
     uint32_t bar0;            // smem address of this warp's STAGES mbarriers
     float* tile_ptr;          // generic pointer to the ring
     int64_t ray0, ray_stride, total;
-    int S, C, nchunk, steps, chunk_floats, lane;
+    int S, C, CH, nchunk, steps, chunk_floats, lane;   // CH = samples per chunk (32, or 16 for wide rows)
     int64_t issued, consumed;
     bool there_and_back;      // per ray: chunks 0..n-1, then n-1..0 (recompute pass + reverse gradient pass)
     bool stores;              // the consumer bulk-stores tiles back out: wait for those reads before refilling
@@ -28,13 +28,14 @@ struct ChunkPipe {
 
     __device__ __forceinline__ void init(const float* raw, float* ring, uint64_t* bars, int64_t first_ray, int64_t stride,
                                          int64_t n, int S_, int C_, int lane_, bool there_and_back_ = false,
-                                         bool stores_ = false, bool reverse_ = false) {
+                                         bool stores_ = false, bool reverse_ = false, int ch = 32) {
         base = raw; tile_ptr = ring; tile0 = ptx::smem_u32(ring); bar0 = ptx::smem_u32(bars);
         ray0 = first_ray; ray_stride = stride; S = S_; C = C_; lane = lane_;
         there_and_back = there_and_back_; stores = stores_; reverse = reverse_;
-        nchunk = (S + 31) >> 5;
+        CH = ch;
+        nchunk = (S + CH - 1) / CH;
         steps = there_and_back ? 2 * nchunk : nchunk;
-        chunk_floats = 32 * C;
+        chunk_floats = CH * C;
         const int64_t my_rays = first_ray < n ? (n - first_ray + stride - 1) / stride : 0;
         total = my_rays * steps;
         issued = consumed = 0;
@@ -54,8 +55,8 @@ struct ChunkPipe {
         if (issued < total && lane == 0) {
             if (stores) ptx::bulk_wait_read0();
             const int64_t ray = ray0 + (issued / steps) * ray_stride;
-            const int c0 = chunk_of(issued) * 32;
-            const int cnt = min(32, S - c0);
+            const int c0 = chunk_of(issued) * CH;
+            const int cnt = min(CH, S - c0);
             const uint32_t bytes = static_cast<uint32_t>(cnt) * C * 4;
             const int st = static_cast<int>(issued % STAGES);
             ptx::mbar_arrive_expect_tx(bar0 + 8 * st, bytes);
@@ -70,7 +71,7 @@ struct ChunkPipe {
         const int st = static_cast<int>(consumed % STAGES);
         ptx::mbar_wait(bar0 + 8 * st, static_cast<uint32_t>((consumed / STAGES) & 1));
         ray = ray0 + (consumed / steps) * ray_stride;
-        c0 = chunk_of(consumed) * 32;
+        c0 = chunk_of(consumed) * CH;
         if (back) *back = static_cast<int>(consumed % steps) >= nchunk;
         ++consumed;
         return tile_ptr + st * chunk_floats;
@@ -79,7 +80,7 @@ struct ChunkPipe {
     // (e.g. the z values of that chunk) one chunk ahead.
     __device__ __forceinline__ void peek(int64_t& ray, int& c0) const {
         ray = ray0 + (consumed / steps) * ray_stride;
-        c0 = chunk_of(consumed) * 32;
+        c0 = chunk_of(consumed) * CH;
     }
     // Bulk-store the (modified) tile just acquired to dst; every lane must have finished writing it.
     __device__ __forceinline__ void store_tile(float* dst, const float* tile, uint32_t bytes) {

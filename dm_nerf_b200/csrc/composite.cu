@@ -135,16 +135,16 @@ template <int ST>
 __global__ void __launch_bounds__(kCompBulkWarps * 32)
 composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
                           int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,
-                          float* __restrict__ weights, float* __restrict__ ins, float* __restrict__ trans_out) {
+                          float* __restrict__ weights, float* __restrict__ ins, float* __restrict__ trans_out, int CH) {
     extern __shared__ __align__(128) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int per_warp = ST * 32 * C + 32;
+    const int per_warp = ST * CH * C + 32;
     float* ring = smem + warp * per_warp;
-    float* wbuf = ring + ST * 32 * C;
+    float* wbuf = ring + ST * CH * C;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp) + warp * ST;
     ChunkPipe<ST> pipe;
     pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
-              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane);
+              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane, false, false, false, CH);
     const int L = C - 4;
     const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
     const int rem = (L & 31) <= 4 ? (L & 31) : 0;          // channels summed sample-parallel
@@ -180,7 +180,7 @@ composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
             for (int q = 0; q < 4; ++q) acc[q] = racc[q] = 0.f;
         }
         if (!pipe.done()) prefetch();
-        const int cnt = min(32, S - c0);
+        const int cnt = min(CH, S - c0);
         const int s = c0 + lane;
         const bool valid = lane < cnt;
         float zc = 0.f, dist = 0.f, sigma = 0.f;
@@ -215,7 +215,7 @@ composite_fwd_bulk_kernel(const float* __restrict__ raw, const float* __restrict
                 acc[q] = a;
             }
         }
-        if (c0 + 32 >= S) {                                  // last chunk of this ray: write the outputs
+        if (c0 + CH >= S) {                                  // last chunk of this ray: write the outputs
             a_r = warp_sum(a_r); a_g = warp_sum(a_g); a_b = warp_sum(a_b); a_d = warp_sum(a_d);
             if (lane == 0) {
                 rgb[ray * 3 + 0] = a_r; rgb[ray * 3 + 1] = a_g; rgb[ray * 3 + 2] = a_b;
@@ -572,20 +572,20 @@ composite_bwd_rev_kernel(const float* __restrict__ raw, const float* __restrict_
                          int64_t n, int S, int C, int flags, int ins_detach, const float* __restrict__ d_rgb,
                          const float* __restrict__ d_depth, const float* __restrict__ d_weights,
                          const float* __restrict__ d_ins, float* __restrict__ d_raw, const float* __restrict__ fwd_w,
-                         const float* __restrict__ fwd_t, const float* __restrict__ fwd_ins) {
+                         const float* __restrict__ fwd_t, const float* __restrict__ fwd_ins, int CH) {
     extern __shared__ __align__(128) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int per_warp = ST * 32 * C + 32;
+    const int per_warp = ST * CH * C + 32;
     float* ring = smem + warp * per_warp;
-    float* wbuf = ring + ST * 32 * C;
+    float* wbuf = ring + ST * CH * C;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCompBulkWarps * per_warp + (kCompBulkWarps * per_warp & 1)) + warp * ST;
     ChunkPipe<ST> pipe;
     pipe.init(raw, ring, bars, static_cast<int64_t>(blockIdx.x) * kCompBulkWarps + warp,
-              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane, false, true, true);
+              static_cast<int64_t>(gridDim.x) * kCompBulkWarps, n, S, C, lane, false, true, true, CH);
     const int L = C - 4;
     const int Lout = L - ((flags & DMNERF_COMP_DROP_EMPTY) ? 1 : 0);
     const bool need_logits = d_ins != nullptr;
-    const int last_c0 = ((S - 1) >> 5) << 5;
+    const int last_c0 = ((S - 1) / CH) * CH;
 
     float norm = 0.f, suffix = 0.f, g_r = 0.f, g_g = 0.f, g_b = 0.f, g_d = 0.f;
     float dA[4] = {0.f, 0.f, 0.f, 0.f};
@@ -611,7 +611,7 @@ composite_bwd_rev_kernel(const float* __restrict__ raw, const float* __restrict_
     while (!pipe.done()) {
         int64_t ray; int c0;
         float* tile = pipe.acquire(ray, c0);
-        const int cnt = min(32, S - c0);
+        const int cnt = min(CH, S - c0);
         const int s = c0 + lane;
         const bool valid = lane < cnt;
         const float zc = z_pre, zn_cur = zn_pre, w = valid ? w_pre : 0.f, trans = t_pre;
@@ -714,7 +714,9 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
             DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
         }
         // debug bits 8-9 (1..3 -> 2..4 stages) and 10-12 (blocks per SM) override the launch shape for tuning sweeps
-        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * 32 * c + 32) * sizeof(float) + st * 8); };
+        // wide rows (K > 59): 16-sample chunks halve the ring, which is what bounds the resident warps per SM
+        const int ch = c > 64 ? 16 : 32;
+        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * ch * c + 32) * sizeof(float) + st * 8); };
         const int dbg = tc_debug_flags();
         int st = kCompStages;
         if ((dbg >> 8) & 3) st = ((dbg >> 8) & 3) + 1;
@@ -727,7 +729,7 @@ extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const floa
         const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
         auto launch = [&](auto kern) {
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins, trans);
+            kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, rgb, depth, weights, ins, trans, ch);
         };
         if (st == 2) launch(composite_fwd_bulk_kernel<2>);
         else if (st == 3) launch(composite_fwd_bulk_kernel<3>);
@@ -763,7 +765,8 @@ extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const floa
             DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
         }
         const bool rev = fwd_weights && fwd_trans && (fwd_ins || !d_ins || (flags & DMNERF_COMP_RAW_INS));
-        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * 32 * c + 32 + (rev ? 0 : 5 * s)) * sizeof(float) + st * 8) + 8; };
+        const int ch = (rev && c > 64) ? 16 : 32;
+        auto smem_for = [&](int st) { return static_cast<size_t>(kCompBulkWarps) * ((st * ch * c + 32 + (rev ? 0 : 5 * s)) * sizeof(float) + st * 8) + 8; };
         const int dbg = tc_debug_flags();
         int st = kCompStages;
         if ((dbg >> 8) & 3) st = ((dbg >> 8) & 3) + 1;
@@ -784,7 +787,7 @@ extern "C" int dmnerf_composite_bwd(const float* raw, const float* z, const floa
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
                 kern<<<grid, kCompBulkWarps * 32, smem, as_stream(stream)>>>(raw, z, rays_d, n, s, c, flags, ins_detach, d_rgb,
                                                                              d_depth, d_weights, d_ins, d_raw, fwd_weights,
-                                                                             fwd_trans, fwd_ins);
+                                                                             fwd_trans, fwd_ins, ch);
             };
             if (rev) {
                 if (st == 2) launch_rev(composite_bwd_rev_kernel<2>);
