@@ -15,7 +15,6 @@ from .optim import FlatAdam
 from . import ops
 from .networks.evaluator import img2mse, ins_criterion_device, ins_criterion_multi, ins_criterion_prepped, ins_label_prep
 from .networks.helpers import get_select_crop, get_select_full, z_val_sample
-from .networks.penalizer import ins_penalizer
 from .networks.render import dm_nerf
 
 
@@ -200,13 +199,10 @@ class TrainStep:
             target_c, target_i, rays, a.N_ins = get_select_crop(image, pose, K, labels, crop[0], crop[1], a.N_train)
         else:
             target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
-        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a)
+        pen = (a.tolerance, a.deta_w) if self.penalize else None     # emptiness loss inside the compositing nodes
+        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, penalizer=pen)
         rgb_loss = img2mse(info["rgb_coarse"], target_c) + img2mse(info["rgb_fine"], target_c)
-        emptiness = None
-        if self.penalize:
-            # enqueued BEFORE the instance loss so the device has work while the host runs the Hungarian assignment
-            emptiness = ins_penalizer(info["raw_coarse"], info["z_vals_coarse"], info["depth_coarse"], rays[1], a) + \
-                ins_penalizer(info["raw_fine"], info["z_vals_fine"], info["depth_fine"], rays[1], a)
+        emptiness = info["emptiness_coarse"] + info["emptiness_fine"] if self.penalize else None
         if self.device_assignment:
             ins_c, ins_f = ins_criterion_device([info["ins_coarse"], info["ins_fine"]], target_i, a.ins_num, self.max_label)
         else:
