@@ -25,17 +25,53 @@ __device__ __forceinline__ float linspace01(int i, int n) {
 }
 
 // Builds cdf[0..nb-1] in shared memory from wv[0..nb-2] (= weights + 1e-5 already stored).
+// Semantics: the total and the running sums are accumulated SEQUENTIALLY in double and rounded to float once (what
+// ATen's CPU cumsum does).  When the largest and smallest term are within 2^20 of each other -- always, for weights in
+// [0,1] with the 1e-5 floor -- every partial sum of these <= 512 fp32 terms is exactly representable in a double
+// (common quantum ulp(min) >= min * 2^-24, sum <= 512 max < 2^53 quanta), so the additions are exact, their order
+// does not matter, and the sums are taken as a warp scan instead of two ~60-step dependent chains on one lane.
+// Anything else (negative or wildly scaled weights) takes the sequential path.
 __device__ __forceinline__ void build_cdf(float* cdf, float* wv, int nb, int lane) {
-    double tot = 0.0;
-    for (int j = 0; j < nb - 1; ++j) tot += static_cast<double>(wv[j]);   // every lane, same order
+    const int m = nb - 1;
+    const int per = (m + 31) >> 5, j0 = min(m, lane * per), j1 = min(m, j0 + per);
+    float lo = CUDART_INF_F, hi = 0.f;
+    double part = 0.0;
+    for (int j = j0; j < j1; ++j) { const float v = wv[j]; lo = fminf(lo, v); hi = fmaxf(hi, v); part += static_cast<double>(v); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    const bool exact = lo > 0.f && hi < lo * 1048576.0f;                   // warp-uniform
+    double tot = part;
+    if (exact) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    } else {
+        tot = 0.0;
+        for (int j = 0; j < m; ++j) tot += static_cast<double>(wv[j]);      // every lane, same order
+    }
     const float total = static_cast<float>(tot);
     __syncwarp();
-    for (int j = lane; j < nb - 1; j += 32) wv[j] = __fdiv_rn(wv[j], total);
+    for (int j = lane; j < m; j += 32) wv[j] = __fdiv_rn(wv[j], total);
     __syncwarp();
-    if (lane == 0) {
+    if (exact) {
+        // the normalised terms keep their ratios (one rounding each): still far inside the exactness bound
+        double run = 0.0;
+        for (int j = j0; j < j1; ++j) run += static_cast<double>(wv[j]);
+        double incl = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += up;
+        }
+        double c = incl - run;                                             // exclusive prefix of this lane's segment
+        if (lane == 0) cdf[0] = 0.f;
+        for (int j = j0; j < j1; ++j) { c += static_cast<double>(wv[j]); cdf[j + 1] = static_cast<float>(c); }
+    } else if (lane == 0) {
         double c = 0.0;
         cdf[0] = 0.f;
-        for (int j = 0; j < nb - 1; ++j) { c += static_cast<double>(wv[j]); cdf[j + 1] = static_cast<float>(c); }
+        for (int j = 0; j < m; ++j) { c += static_cast<double>(wv[j]); cdf[j + 1] = static_cast<float>(c); }
     }
     __syncwarp();
 }

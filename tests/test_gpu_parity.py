@@ -992,3 +992,25 @@ def test_composite_backward_one_pass_equals_recompute(n, s, k, flags):
         b = ops.composite_bwd(raw, z, rd, flags, detach, d_rgb, d_depth, d_w, d_ins, fwd=(w, trans, ins))
         scale = float(a.abs().max())
         assert float((a - b).abs().max()) <= 2e-6 * scale, (detach, float((a - b).abs().max()), scale)
+
+
+def test_sample_pdf_cdf_paths_vs_c_restatement(c_oracle):
+    """The sampler's CDF (sequential double accumulation = ATen CPU cumsum): the warp-scan path taken for ordinary weights
+    (partial sums exact in double, order-free) and the sequential fallback for wildly scaled weights are both bit-exact
+    with the C restatement's plain sequential loop -- indices and samples."""
+    from dm_nerf_b200 import ops
+    gen = torch.Generator().manual_seed(77)
+    n, nb, ns = 64, 63, 128
+    bins = torch.sort(torch.rand(n, nb, generator=gen) * 11 + 4, -1)[0]
+    u = torch.rand(n, ns, generator=gen)
+    w_plain = torch.rand(n, nb - 1, generator=gen) ** 4                     # ordinary: [0,1], many near-empty bins
+    w_wild = w_plain.clone()
+    w_wild[::2, 5] = 3.0e9                                                   # max / min far beyond 2^20 -> sequential path
+    w_wild[1::4, 9] = 0.0
+    for w in (w_plain, w_wild):
+        z, inds = ops.sample_pdf(cu(bins), cu(w), ns, cu(u), want_inds=True)
+        zc, ic = np.empty((n, ns), np.float32), np.empty((n, ns), np.int64)
+        bn, wn, un = bins.numpy(), np.ascontiguousarray(w.numpy()), u.numpy()
+        c_oracle.oracle_sample_pdf(bn.ctypes.data, wn.ctypes.data, un.ctypes.data, ns, n, nb, ns, zc.ctypes.data, ic.ctypes.data)
+        np.testing.assert_array_equal(inds.cpu().numpy(), ic)
+        np.testing.assert_array_equal(z.cpu().numpy(), zc)
