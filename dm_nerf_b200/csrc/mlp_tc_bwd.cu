@@ -180,7 +180,7 @@ mlp_dgrad_bf16_kernel(const float* __restrict__ d_raw, int64_t n_points, const u
                         // the last layer's result (G0) only feeds wgrad: keeping it out of smem avoids a race with
                         // the next pair's G9 prologue, which other threads of this row may already be writing
                         if (d + 1 < kDgLayers) ptx::st_shared_v4(a_base + (cb * 4 + g) * kKgBytes + row * 16, w0, w1, w2, w3);
-                        *reinterpret_cast<uint4*>(g_row + (okg0 + cb * 4 + g) * kStKgBytes) = make_uint4(w0, w1, w2, w3);
+                        __stcs(reinterpret_cast<uint4*>(g_row + (okg0 + cb * 4 + g) * kStKgBytes), make_uint4(w0, w1, w2, w3));
                     }
                 }
                 if (d + 1 < kDgLayers) {

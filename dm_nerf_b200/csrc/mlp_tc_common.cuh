@@ -181,7 +181,7 @@ __device__ __forceinline__ uint32_t store_kg_mask(uint32_t a_base, int kg, int r
     const uint32_t w[4] = {ptx::pack_bf16(v[0], v[1], true), ptx::pack_bf16(v[2], v[3], true),
                            ptx::pack_bf16(v[4], v[5], true), ptx::pack_bf16(v[6], v[7], true)};
     ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, w[0], w[1], w[2], w[3]);
-    *reinterpret_cast<uint4*>(gst + gkg * kStKgBytes) = make_uint4(w[0], w[1], w[2], w[3]);
+    __stcs(reinterpret_cast<uint4*>(gst + gkg * kStKgBytes), make_uint4(w[0], w[1], w[2], w[3]));
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int k = g * 4 + j;
