@@ -91,6 +91,7 @@ _SIGNATURES = {
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
     "dmnerf_reserve_sms": (_int, [_int]),
+    "dmnerf_draw_pixels": (_int, [_p, _i64, _i64, _p, C.c_uint64, _p]),
     "dmnerf_adam_step": (_int, [_p, _p, _p, _p, _i64, _p, _f, _p, _f, _f, _f, _f, _p]),
 }
 

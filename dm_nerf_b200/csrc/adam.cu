@@ -67,3 +67,54 @@ extern "C" int dmnerf_adam_step(float* p, const float* g, float* m, float* v, in
     DM_LAUNCH_CHECK("adam_step_kernel");
     return DMNERF_OK;
 }
+
+// ---- pixel draw of the training loops (helpers.py:99-111: np.random.choice(H*W, N, replace=False)) -------------------
+// N DISTINCT pixel indices per step as the first N values of a keyed pseudo-random permutation of [0, total): a 4-round
+// Feistel network over the smallest even-width power-of-two domain, cycle-walked back into range (expected < 4 walks).
+// One launch of N threads instead of permuting all H*W indices (torch.randperm: five radix-sort passes over 307,200
+// keys every step); the key mixes a seed with the DEVICE-side step counter, so the draw changes under CUDA-graph replay.
+namespace dmnerf {
+
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {          // murmur3 finalizer
+    x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+    return x;
+}
+
+__global__ void draw_pixels_kernel(int64_t* __restrict__ out, int64_t n, uint32_t total, const int* __restrict__ step_dev,
+                                   uint32_t seed_lo, uint32_t seed_hi, int half_bits) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t step = static_cast<uint32_t>(*step_dev);
+    const uint32_t key = mix32(seed_lo ^ mix32(step + 0x9E3779B9u)) ^ seed_hi;
+    const uint32_t mask = (1u << half_bits) - 1u;
+    uint32_t v = static_cast<uint32_t>(i);
+    for (int walk = 0; walk < 256; ++walk) {                    // (3/4)^256: never exhausted in practice
+        uint32_t l = v >> half_bits, r = v & mask;
+#pragma unroll
+        for (int round = 0; round < 4; ++round) {
+            const uint32_t f = mix32(r ^ (key + 0x632BE5ABu * (round + 1))) & mask;
+            const uint32_t nl = r;
+            r = l ^ f;
+            l = nl;
+        }
+        v = (l << half_bits) | r;
+        if (v < total) break;                                       // a permutation of the domain restricted to [0,total)
+    }
+    out[i] = static_cast<int64_t>(v < total ? v : static_cast<uint32_t>(i));
+}
+
+}  // namespace dmnerf
+
+extern "C" int dmnerf_draw_pixels(int64_t* idx_out, int64_t n, int64_t total, const int* step_dev, uint64_t seed,
+                                  void* stream) {
+    DM_REQUIRE(idx_out && step_dev, DMNERF_EINVAL, "draw_pixels: null pointer");
+    DM_REQUIRE(n >= 0 && total >= 1 && n <= total && total <= (int64_t(1) << 30), DMNERF_EINVAL,
+               "draw_pixels: need 0 <= n <= total <= 2^30 (n=%lld total=%lld)", static_cast<long long>(n), static_cast<long long>(total));
+    if (n == 0) return DMNERF_OK;
+    int bits = 2;
+    while ((int64_t(1) << bits) < total) bits += 2;                  // even width: two equal halves
+    draw_pixels_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, as_stream(stream)>>>(
+        idx_out, n, static_cast<uint32_t>(total), step_dev, static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32), bits / 2);
+    DM_LAUNCH_CHECK("draw_pixels_kernel");
+    return DMNERF_OK;
+}

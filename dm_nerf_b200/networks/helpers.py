@@ -20,13 +20,15 @@ def get_rays(H, W, focal, c2w):
     return get_rays_k(H, W, K, c2w)
 
 
-def get_select_full(rgb, pose, K, ins_target, N_train, numpy_rng=False):
+def get_select_full(rgb, pose, K, ins_target, N_train, numpy_rng=False, idx=None):
     """helpers.py:99-111: N_train distinct random pixels, their rays (generated for those pixels only, not the
     whole frame), colours and instance labels.  The pixel draw runs on the device (``torch.randperm``); the
     reference's ``np.random.choice(H*W, N, replace=False)`` permutes all H*W indices on the host every step
     (3.7 ms at 640x480) -- pass ``numpy_rng=True`` to reproduce its RNG stream."""
     H, W, _ = rgb.shape
-    if numpy_rng:
+    if idx is not None:
+        pass                                            # drawn by the caller (ops.draw_pixels in the captured training step)
+    elif numpy_rng:
         idx = torch.from_numpy(np.random.choice(H * W, size=[N_train], replace=False)).to(rgb.device)
     else:
         idx = torch.randperm(H * W, device=rgb.device)[:N_train]

@@ -499,6 +499,17 @@ def rays_k_dev(H: int, W: int, K, c2w, n: int, pix_idx: torch.Tensor) -> Tuple[t
     return ro, rd
 
 
+def draw_pixels(n: int, total: int, step: torch.Tensor, seed: int) -> torch.Tensor:
+    """n distinct pixel indices in [0,total) for the training step whose number sits in the device int32 ``step``."""
+    if step.dtype != torch.int32 or not step.is_cuda:
+        raise RuntimeError("draw_pixels: step must be an int32 CUDA tensor")
+    idx = torch.empty((n,), dtype=torch.int64, device=step.device)
+    check(_lib.lib().dmnerf_draw_pixels(_ptr(idx), n, total, _ptr(step), C.c_uint64(seed & 0xFFFFFFFFFFFFFFFF), _stream()),
+          "dmnerf_draw_pixels")
+    _count()
+    return idx
+
+
 def label_argmax(ins) -> torch.Tensor:
     ins = _f32(ins, "ins")
     n, k = ins.shape

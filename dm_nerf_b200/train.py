@@ -53,6 +53,7 @@ class TrainStep:
         self.overlap = bool(self.graph_mode if overlap_assignment is None else overlap_assignment) and device_assignment
         self.reserved_sms = 1
         self._side = None
+        self._draw_step = self._draw_seed = None
         self._graph = self._static = self._static_out = None
         self._K_dev = None
         self.z_coarse = z_val_sample(args.N_train, args.near, args.far, args.N_samples)     # train_dmsr.py:22
@@ -110,6 +111,15 @@ class TrainStep:
                 ops.reserve_sms(prev)
         return self._step_serial(image, pose, labels, K, decay)
 
+    def _draw(self, image) -> torch.Tensor:
+        """N_train distinct pixels in one launch (keyed permutation of the H*W indices, key = seed x DEVICE step counter, so
+        a graph replay draws anew) instead of torch.randperm's radix sort of all H*W keys every step."""
+        if self._draw_step is None:
+            self._draw_step = torch.zeros((), dtype=torch.int32, device=image.device)
+            self._draw_seed = int(torch.initial_seed()) * 1000003 + (dist.get_rank() if dist.is_initialized() else 0)
+        self._draw_step += 1
+        return ops.draw_pixels(int(self.args.N_train), int(image.shape[0]) * int(image.shape[1]), self._draw_step, self._draw_seed)
+
     def _finish(self, decay: bool) -> None:
         if isinstance(self.opt, FlatAdam):
             # ONE all-reduce per model on the backward's own flat gradient buffer (no gather / scatter copies); the
@@ -149,7 +159,7 @@ class TrainStep:
         side_c.wait_stream(main)
         with torch.cuda.stream(side_c):
             self.mc.packed(ops.get_mode()); self.mf.packed(ops.get_mode())
-        target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
+        target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train, idx=self._draw(image))
         prep = ins_label_prep(target_i, a.ins_num, self.max_label)
         main.wait_stream(side_c)
         got = {}
@@ -198,7 +208,7 @@ class TrainStep:
             a = SimpleNamespace(**vars(a))
             target_c, target_i, rays, a.N_ins = get_select_crop(image, pose, K, labels, crop[0], crop[1], a.N_train)
         else:
-            target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train)
+            target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train, idx=self._draw(image))
         pen = (a.tolerance, a.deta_w) if self.penalize else None     # emptiness loss inside the compositing nodes
         info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, penalizer=pen)
         rgb_loss = img2mse(info["rgb_coarse"], target_c) + img2mse(info["rgb_fine"], target_c)

@@ -191,6 +191,11 @@ int  dmnerf_debug_flags(int flags);
  * Same arithmetic as torch.optim.Adam with weight_decay = 0, amsgrad = False. */
 int  dmnerf_adam_step(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev, float lr,
                       const int* step_dev, float beta1, float beta2, float eps, float grad_scale, void* stream);
+/* The pixel draw of the training loops (networks/helpers.py:99-111: np.random.choice(H*W, N, replace=False)): n DISTINCT
+ * indices in [0,total) = the first n values of a keyed pseudo-random permutation (4-round Feistel, cycle-walked).  The
+ * key mixes `seed` with the device int32 at step_dev, so a captured CUDA graph draws new pixels on every replay.
+ * idx_out: device int64 [n].  Not the reference's numpy stream (helpers.get_select_full(numpy_rng=True) reproduces that). */
+int  dmnerf_draw_pixels(int64_t* idx_out, int64_t n, int64_t total, const int* step_dev, uint64_t seed, void* stream);
 /* SM partitioning for overlapped training (train_dmsr.py:24-72 as one step; networks/evaluator.py:45-46 is the
  * assignment that runs beside the ray kernels): the persistent one-CTA-per-SM MLP kernels (forward, dgrad, wgrad) take a
  * whole SM's shared memory, so a small kernel on another stream (dmnerf_hungarian) can only run concurrently if some SMs

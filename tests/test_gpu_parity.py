@@ -1014,3 +1014,28 @@ def test_sample_pdf_cdf_paths_vs_c_restatement(c_oracle):
         c_oracle.oracle_sample_pdf(bn.ctypes.data, wn.ctypes.data, un.ctypes.data, ns, n, nb, ns, zc.ctypes.data, ic.ctypes.data)
         np.testing.assert_array_equal(inds.cpu().numpy(), ic)
         np.testing.assert_array_equal(z.cpu().numpy(), zc)
+
+
+def test_draw_pixels_is_a_random_subset_without_replacement():
+    """dmnerf_draw_pixels (the training loops' np.random.choice(H*W, N, replace=False), helpers.py:99-111): distinct, in
+    range, a different subset per step and per seed, reproducible, close to uniform; n == total gives a full permutation."""
+    from dm_nerf_b200 import ops
+    total, n = 480 * 640, 4096
+    step = torch.zeros((), dtype=torch.int32, device=DEV)
+    seen = []
+    hist = np.zeros(16)
+    for it in range(40):
+        step += 1
+        idx = ops.draw_pixels(n, total, step, 1234).cpu().numpy()
+        assert idx.min() >= 0 and idx.max() < total and len(np.unique(idx)) == n
+        seen.append(idx)
+        hist += np.bincount(idx * 16 // total, minlength=16)
+    assert not np.array_equal(seen[0], seen[1]) and len(np.intersect1d(seen[0], seen[1])) < 200
+    again = ops.draw_pixels(n, total, step, 1234).cpu().numpy()
+    assert np.array_equal(again, seen[-1])                                   # same (seed, step) -> same draw
+    other = ops.draw_pixels(n, total, step, 99).cpu().numpy()
+    assert not np.array_equal(other, seen[-1])
+    expect = 40 * n / 16
+    assert np.all(np.abs(hist - expect) < 6 * np.sqrt(expect))               # 16 equal strips of the image
+    small = ops.draw_pixels(1000, 1000, step, 5).cpu().numpy()
+    assert sorted(small.tolist()) == list(range(1000))
