@@ -32,12 +32,25 @@ __device__ __forceinline__ int warp_argmax_sigmoid(const float* v, int cnt, int 
     return idx;
 }
 
+// argmax_j sigmoid(row[j]), first maximum winning -- the same result as evaluating the fp32 sigmoid of every channel,
+// but the sigmoid is only evaluated where it can matter.  sigmoid is monotone up to its last-ulp rounding, so only
+// channels close to the largest logit can reach the largest sigmoid VALUE: with s = sigmoid(x_max) < 1 a logit more than
+// 32 * 2^-24 / (1 - s) below x_max has a true sigmoid at least 16 ulp below s (slope s (1 - s) >= (1 - s) / 2) and cannot
+// tie or win; with s == 1.0f (saturation, x >~ 17.33: the reference's tie case) every logit >= 16 is a candidate, no other
+// can round to 1.  Typically one candidate per row instead of K+1 expf + IEEE divisions.
 __device__ __forceinline__ int row_argmax_sigmoid(const float* row, int cnt) {
-    float best = sigmoidf_ref(row[0]);
+    float xmax = row[0];
+    for (int j = 1; j < cnt; ++j) xmax = fmaxf(xmax, row[j]);
+    const float smax = sigmoidf_ref(xmax);
+    const float thr = smax >= 1.0f ? fminf(16.0f, xmax) : xmax - 1.9073486e-6f / (1.0f - smax);
+    float best = -1.0f;
     int idx = 0;
-    for (int j = 1; j < cnt; ++j) {
-        const float s = sigmoidf_ref(row[j]);
-        if (s > best) { best = s; idx = j; }
+    for (int j = 0; j < cnt; ++j) {
+        const float x = row[j];
+        if (x >= thr) {
+            const float s = sigmoidf_ref(x);
+            if (s > best) { best = s; idx = j; }
+        }
     }
     return idx;
 }
@@ -59,15 +72,31 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     float* t_ori = smem + warp * (2 * 32 * CP + 32);
     float* t_tar = t_ori + 32 * CP;
     int* act = reinterpret_cast<int*>(t_tar + 32 * CP);
-    const float invC = 1.0f / static_cast<float>(C);
     float* g_ori = ori_raw + (ray * S + c0) * static_cast<int64_t>(C);
     const float* g_tar = tar_raw + (ray * S + c0) * static_cast<int64_t>(C);
     const int total = cnt * C;
-    for (int i = lane; i < total; i += 32) {
-        const int r = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
-        const int col = i - r * C;
-        t_ori[r * CP + col] = g_ori[i];
-        t_tar[r * CP + col] = __ldg(g_tar + i);
+    const unsigned magic = 0xFFFFFFFFu / C + 1u;             // i / C by one multiply-high (i < 32 * 128)
+    // staging: 8 elements of each field per lane in flight (a plain one-load-per-trip loop left every warp waiting on
+    // ~37 dependent DRAM round trips per chunk: the kernel ran at 0.3 of the HBM roofline)
+    constexpr int U = 8;
+    for (int base = 0; base < total; base += 32 * U) {
+        float va[U], vb[U];
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const int i = base + q * 32 + lane;
+            va[q] = i < total ? g_ori[i] : 0.f;
+            vb[q] = i < total ? __ldg(g_tar + i) : 0.f;
+        }
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const int i = base + q * 32 + lane;
+            if (i < total) {
+                const int r = static_cast<int>(__umulhi(static_cast<unsigned>(i), magic));
+                const int col = i - r * C;
+                t_ori[r * CP + col] = va[q];
+                t_tar[r * CP + col] = vb[q];
+            }
+        }
     }
     // per-ray labels from the accumulated maps without their last ("empty") channel
     const int pix = warp_argmax_sigmoid(ori_acc + ray * L, L - 1, lane);
@@ -89,8 +118,12 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     }
     act[lane] = a;
     __syncwarp();
+    // rows that keep their values are not touched; most chunks have none to rewrite
+    int any = 0;
+    if (lane < cnt) any = act[lane];
+    if (__ballot_sync(0xffffffffu, any != 0) == 0u) return;
     for (int i = lane; i < total; i += 32) {
-        const int r = __float2int_rz((static_cast<float>(i) + 0.5f) * invC);
+        const int r = static_cast<int>(__umulhi(static_cast<unsigned>(i), magic));
         const int col = i - r * C;
         const int ar = act[r];
         if (ar == 1) g_ori[i] = t_tar[r * CP + col];

@@ -1039,3 +1039,33 @@ def test_draw_pixels_is_a_random_subset_without_replacement():
     assert np.all(np.abs(hist - expect) < 6 * np.sqrt(expect))               # 16 equal strips of the image
     small = ops.draw_pixels(1000, 1000, step, 5).cpu().numpy()
     assert sorted(small.tolist()) == list(range(1000))
+
+
+def test_exchanger_labels_equal_full_sigmoid_argmax_on_adversarial_logits():
+    """The exchanger's per-sample label argmax(sigmoid(raw[..., 4:])) (manipulator.py:21, first maximum wins) evaluates
+    the sigmoid only for logits that can reach the largest value; it must equal the full evaluation on rows built to
+    tie: saturated logits (>= 17.33 -> 1.0f), exact duplicates, 1-ulp neighbours, values inside one sigmoid plateau."""
+    from dm_nerf_b200 import ops
+    gen = torch.Generator().manual_seed(41)
+    n, s, k = 64, 96, 32
+    c = k + 5
+    raw = torch.randn(n, s, c, generator=gen) * 4
+    lg = raw[..., 4:]
+    lg[0:8] = torch.randn(8, s, k + 1, generator=gen) * 3 + 18            # several saturate to 1.0f
+    lg[8:16] = torch.randn(8, s, k + 1, generator=gen) * 0.5 + 14          # wide plateaus (1 - s ~ 1e-6)
+    base = torch.randn(8, s, 1, generator=gen) * 6
+    lg[16:24] = base + torch.randint(0, 3, (8, s, k + 1), generator=gen).float() * torch.finfo(torch.float32).eps * base.abs()
+    lg[24:32] = torch.round(torch.randn(8, s, k + 1, generator=gen) * 2)    # many exact duplicates
+    lg[32:40] = 11.0 + torch.rand(8, s, k + 1, generator=gen) * 2e-3        # inside / across one plateau at x ~ 11
+    lg[..., 0] = -100.0                                                     # label 0 never wins: move label 0 edits nothing
+    tar = raw.clone()
+    acc = torch.sigmoid(torch.randn(n, k + 1, generator=gen)); acc[:, 0] = 0.0
+    ori_d = cu(raw).clone()
+    lab, tlab = ops.exchange(ori_d, cu(tar), cu(acc), cu(acc), 0, None)
+    want = torch.sigmoid(cu(raw)[..., 4:]).argmax(-1)                       # torch CUDA: the reference's deployment
+    sg = torch.sigmoid(cu(raw)[..., 4:])
+    top = sg.max(-1, keepdim=True)[0]
+    first = (sg == top).float().argmax(-1)                                  # first index holding the maximum value
+    assert torch.equal(lab, first) and torch.equal(tlab, first)
+    assert float((lab != want).float().mean()) == 0.0 or torch.equal(first, want)
+    assert torch.equal(ori_d, cu(raw))                                      # nothing exchanged

@@ -68,3 +68,13 @@ print(f"fine_z det: {ms*1e3:8.1f} us  {n*1280/ms/1e6:7.0f} GB/s  {n*1280/ms/1e6/
 u = torch.rand(n, 128, device=dev, generator=g)
 ms = timed(lambda: ops.fine_z(zc, wc, 128, u))
 print(f"fine_z rand: {ms*1e3:8.1f} us  {n*1792/ms/1e6:7.0f} GB/s  {n*1792/ms/1e6/peak:.3f}")
+# exchanger (a10): one move label on [n, S, C] fields; SURVEY 8d bytes per (ray, target)
+for S in (64, 192):
+    ori = torch.randn(n, S, C, device=dev, generator=g) * 3
+    tar = torch.randn(n, S, C, device=dev, generator=g) * 3
+    oacc = torch.sigmoid(torch.randn(n, K + 1, device=dev, generator=g) * 3)
+    tacc = torch.sigmoid(torch.randn(n, K + 1, device=dev, generator=g) * 3)
+    ex_bytes = n * (2 * S * C * 4 + 2 * (K + 1) * 4 + S * C * 4 + 2 * S * 8)
+    ms = timed(lambda: ops.exchange(ori, tar, oacc, tacc, 3, None))
+    print(f"exchanger S={S} K={K}: {ms*1e3:8.1f} us  {ex_bytes/ms/1e6:7.0f} GB/s  {ex_bytes/ms/1e6/peak:.3f} (reads both fields, "
+          f"rewrites ori_raw, writes two int64 label maps)")
