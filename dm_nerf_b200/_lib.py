@@ -22,32 +22,73 @@ PEN_ACCUMULATE = 2
 NUM_PARAMS = 30
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared"]
+              "-Xcompiler", "-fPIC"]
+OBJ_DIR = os.path.join(PKG_DIR, "build")
+
+
+def experimental() -> bool:
+    """The parked forward variants (csrc/experimental/) are compiled only when DMNERF_EXPERIMENTAL=1."""
+    return os.environ.get("DMNERF_EXPERIMENTAL", "0") not in ("", "0")
 
 
 def sources():
-    return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+    src = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+    if experimental():
+        src += sorted(glob.glob(os.path.join(CSRC, "experimental", "*.cu")))
+    return src
+
+
+def _headers():
+    return (glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "experimental", "*.cuh"))
+            + [os.path.join(PKG_DIR, "..", "include", "dmnerf_b200.h")])
+
+
+def _flavour() -> str:
+    return "exp" if experimental() else "prod"
 
 
 def needs_build() -> bool:
     if not os.path.exists(SO_PATH):
         return True
+    tag = os.path.join(OBJ_DIR, "flavour")
+    if os.path.exists(tag) and open(tag).read().strip() != _flavour():
+        return True
     t = os.path.getmtime(SO_PATH)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.join(PKG_DIR, "..", "include", "dmnerf_b200.h")]
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+    return any(os.path.getmtime(d) > t for d in sources() + _headers() if os.path.exists(d))
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every .cu under csrc/ into one shared library for sm_100a (cross-compiles without a GPU)."""
+    """Compile every .cu under csrc/ for sm_100a (one nvcc per file, in parallel; cross-compiles without a GPU) and
+    link them into one shared library.  Objects are cached under build/ and rebuilt when their source or any header
+    is newer."""
     if not force and not needs_build():
         return SO_PATH
+    from concurrent.futures import ThreadPoolExecutor
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH] + sources()
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    odir = os.path.join(OBJ_DIR, _flavour())
+    os.makedirs(odir, exist_ok=True)
+    flags = NVCC_FLAGS + (["-DDMNERF_EXPERIMENTAL"] if experimental() else []) + (["-Xptxas", "-v"] if verbose else [])
+    hdr_t = max(os.path.getmtime(h) for h in _headers() if os.path.exists(h))
+
+    def compile_one(src):
+        obj = os.path.join(odir, os.path.basename(src)[:-3] + ".o")
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), hdr_t):
+            return obj, ""
+        res = subprocess.run([nvcc] + flags + ["-c", "-o", obj, src], capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"nvcc failed on {src}:\n" + res.stdout + res.stderr)
+        return obj, res.stderr
+
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        results = list(ex.map(compile_one, sources()))
     if verbose:
-        print(res.stderr)
+        print("".join(r[1] for r in results))
+    res = subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", SO_PATH]
+                         + [r[0] for r in results], capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("link failed:\n" + res.stdout + res.stderr)
+    with open(os.path.join(OBJ_DIR, "flavour"), "w") as f:
+        f.write(_flavour())
     return SO_PATH
 
 
@@ -59,6 +100,7 @@ _f = C.c_float
 _SIGNATURES = {
     "dmnerf_version": (_int, []),
     "dmnerf_built_arch": (_int, []),
+    "dmnerf_has_experimental": (_int, []),
     "dmnerf_last_error": (_int, [C.c_char_p, _int]),
     "dmnerf_packed_bytes": (_i64, [_int, _int]),
     "dmnerf_weights_pack": (_int, [C.POINTER(_p), _int, _int, _p, _p]),
@@ -88,6 +130,7 @@ _SIGNATURES = {
     "dmnerf_selftest_umma_rate": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_counters": (_int, [_p]),
     "dmnerf_hungarian": (_int, [_p, _int, _i64, _int, _p, _int, _p, _p]),
+    "dmnerf_hungarian_infeasible": (_int, [C.POINTER(_int), _p]),
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
     "dmnerf_reserve_sms": (_int, [_int]),

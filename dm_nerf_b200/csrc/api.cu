@@ -46,6 +46,14 @@ extern "C" int dmnerf_version(void) { return 100; }
 
 extern "C" int dmnerf_built_arch(void) { return 100; }
 
+extern "C" int dmnerf_has_experimental(void) {
+#ifdef DMNERF_EXPERIMENTAL
+    return 1;
+#else
+    return 0;
+#endif
+}
+
 extern "C" int dmnerf_last_error(char* buf, int cap) {
     const int len = static_cast<int>(strlen(g_err));
     if (buf && cap > 0) {
@@ -78,8 +86,7 @@ extern "C" int dmnerf_weights_pack(const float* const* params, int ins_num, int 
 }
 
 extern "C" int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num, int mode) {
-    (void)ins_num;
-    if (n_points < 0) return -1;
+    if (n_points < 0 || ins_num < 1 || ins_num > kMaxIns) return -1;
     if (mode == DMNERF_MODE_BF16) return bf16_acts_bytes(n_points);
     if (mode != DMNERF_MODE_FP32) return -1;
     const int64_t tiles = (n_points + kTileM - 1) / kTileM;
@@ -119,8 +126,7 @@ extern "C" int dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* pa
 }
 
 extern "C" int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num, int mode) {
-    (void)ins_num;
-    if (n_points < 0) return -1;
+    if (n_points < 0 || ins_num < 1 || ins_num > kMaxIns) return -1;
     if (mode == DMNERF_MODE_BF16) return bf16_bwd_workspace_bytes(n_points);
     return mode == DMNERF_MODE_FP32 ? 0 : -1;
 }

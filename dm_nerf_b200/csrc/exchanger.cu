@@ -42,7 +42,10 @@ __device__ __forceinline__ int row_argmax_sigmoid(const float* row, int cnt) {
     float xmax = row[0];
     for (int j = 1; j < cnt; ++j) xmax = fmaxf(xmax, row[j]);
     const float smax = sigmoidf_ref(xmax);
-    const float thr = smax >= 1.0f ? fminf(16.0f, xmax) : xmax - 1.9073486e-6f / (1.0f - smax);
+    // xmax < -80: sigmoid(xmax) is denormal or 0 and the ulp argument above does not hold -> every channel is a
+    // candidate (all-zero rows then give index 0, like the reference's argmax over zeros)
+    const float thr = xmax < -80.0f ? -INFINITY
+                      : (smax >= 1.0f ? fminf(16.0f, xmax) : xmax - 1.9073486e-6f / (1.0f - smax));
     float best = -1.0f;
     int idx = 0;
     for (int j = 0; j < cnt; ++j) {
@@ -134,7 +137,16 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
 __global__ void label_argmax_kernel(const float* __restrict__ ins, int64_t n, int K, uint8_t* __restrict__ labels) {
     const int64_t ray = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (ray >= n) return;
-    labels[ray] = static_cast<uint8_t>(row_argmax_sigmoid(ins + ray * K, K));
+    // the composited maps are probabilities already (render.py:25, manipulator.py:102); the reference takes a plain
+    // torch.argmax of them (evaluator.py:132, manipulator.py:321,478): first maximum wins, no second sigmoid
+    const float* row = ins + ray * K;
+    float best = row[0];
+    int idx = 0;
+    for (int j = 1; j < K; ++j) {
+        const float v = row[j];
+        if (v > best) { best = v; idx = j; }
+    }
+    labels[ray] = static_cast<uint8_t>(idx);
 }
 
 struct Camera {

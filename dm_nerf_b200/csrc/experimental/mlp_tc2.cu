@@ -7,7 +7,7 @@
 // issuer + TMEM owner.  Barriers per tile t and half j: acc_done[t][j] (tcgen05.commit -> epilogue),
 // h_ready[t][j] (epilogue -> MMA issuer: H[j] of this layer is in shared memory and accumulator half j is drained;
 // one arrival per warp after its threads' proxy fence).
-#include "mlp_tc_common.cuh"
+#include "../mlp_tc_common.cuh"
 
 namespace dmnerf {
 
@@ -384,18 +384,10 @@ int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, floa
     return DMNERF_OK;
 }
 
-namespace tc3 { int debug_counters_v3(long long* host_out8); }
-namespace tc4 { int debug_counters_v4(long long* host_out8); }
-int tc_debug_flags();
-int debug_counters_v1(long long* host_out8);
-}  // namespace dmnerf
-
-extern "C" int dmnerf_debug_counters(long long* host_out8) {
-    DM_REQUIRE(host_out8, DMNERF_EINVAL, "debug_counters: null pointer");
-    DM_CUDA(cudaDeviceSynchronize());
-    if (dmnerf::tc_debug_flags() & 16) return dmnerf::debug_counters_v1(host_out8);
-    if (dmnerf::tc_debug_flags() & 32) return dmnerf::tc4::debug_counters_v4(host_out8);
-    if (dmnerf::tc_debug_flags() & 8) return dmnerf::tc3::debug_counters_v3(host_out8);
-    DM_CUDA(cudaMemcpyFromSymbol(host_out8, dmnerf::tc2::g_dbg, 8 * sizeof(long long)));
+namespace tc2 {
+int debug_counters_v2(long long* host_out8) {
+    DM_CUDA(cudaMemcpyFromSymbol(host_out8, g_dbg, 8 * sizeof(long long)));
     return DMNERF_OK;
 }
+}  // namespace tc2
+}  // namespace dmnerf

@@ -16,7 +16,7 @@
 // by the peer's relay when ITS half has landed; w_empty[s] and acc_ready[t] by multicast tcgen05.commit; a_ready[t]
 // (leader only) one pending arrival (the issuer's own expect_tx, re-armed after every wait) + 4 bytes per epilogue warp
 // of tile t from BOTH CTAs (st.async ... mbarrier::complete_tx; a remote mbarrier.arrive blocks the lane ~800 clk).
-#include "mlp_tc_common.cuh"
+#include "../mlp_tc_common.cuh"
 
 namespace dmnerf {
 namespace tc3 {

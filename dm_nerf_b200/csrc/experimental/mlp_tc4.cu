@@ -17,7 +17,7 @@
 // Weight streams, chunk schedule and the GEMM-side biases are those of mlp_tc3 (pack_v3, mlp_tc3.cuh).
 // Roles per CTA (18 warps): 0-15 epilogue (lane quarter q = w & 3, column slice cg = w >> 2), 16 weight producer,
 // 17 MMA issuer (leader CTA) / "chunk landed" relay (peer CTA).
-#include "mlp_tc_common.cuh"
+#include "../mlp_tc_common.cuh"
 
 namespace dmnerf {
 namespace tc4 {

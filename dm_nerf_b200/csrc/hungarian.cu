@@ -24,6 +24,9 @@ __device__ __forceinline__ unsigned long long dkey(double x) {
     return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
 }
 
+// launches whose score matrix had a row without any finite entry (NaN / inf: a diverged step) since the last query
+__device__ int g_hung_infeasible = 0;
+
 __global__ void __launch_bounds__(32)
 hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, const int* __restrict__ n_valid_ptr, int nc,
                  int* __restrict__ col_out) {
@@ -92,7 +95,14 @@ hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, c
             if (lane == (j & 31)) vis |= 1u << (j >> 5);
             if (owner < 0) sink = j; else i = owner;
         }
-        if (sink < 0) break;
+        if (sink < 0) {
+            // infeasible: scipy raises ValueError here.  A kernel cannot, so the result is DEFINED -- the identity
+            // permutation, every slot of `out` written, nothing out of range -- and counted for
+            // dmnerf_hungarian_infeasible(), which the host checks outside captured graphs.
+            for (int j = lane; j < nc; j += 32) out[j] = j;
+            if (lane == 0) atomicAdd(&g_hung_infeasible, 1);
+            return;
+        }
         // dual update (uses the matching BEFORE augmentation); the path costs are published for the row duals
 #pragma unroll
         for (int k = 0; k < kHungCols; ++k) s_spc[lane + 32 * k] = spc[k];
@@ -138,6 +148,15 @@ hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, c
 }  // namespace dmnerf
 
 using namespace dmnerf;
+
+extern "C" int dmnerf_hungarian_infeasible(int* count_out, void* stream) {
+    DM_REQUIRE(count_out, DMNERF_EINVAL, "hungarian_infeasible: null pointer");
+    DM_CUDA(cudaStreamSynchronize(as_stream(stream)));
+    DM_CUDA(cudaMemcpyFromSymbol(count_out, g_hung_infeasible, sizeof(int)));
+    const int zero = 0;
+    DM_CUDA(cudaMemcpyToSymbol(g_hung_infeasible, &zero, sizeof(int)));
+    return DMNERF_OK;
+}
 
 extern "C" int dmnerf_hungarian(const float* scores, int n_mats, int64_t mat_stride, int ld, const int* n_valid, int n_cols,
                                 int* col_out, void* stream) {

@@ -459,16 +459,21 @@ umma_selftest_kernel(const float* __restrict__ a, const float* __restrict__ b, i
 
 }  // namespace tc
 
+#ifdef DMNERF_EXPERIMENTAL
 int launch_mlp_bf16_v2(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16_v3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16_v4(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+#endif
 int launch_masks_from_acts(void* acts, int64_t n_points, cudaStream_t st);
 int persistent_ctas(int sm_count);
 
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
-    // debug bit2 selects the pipelined variant (mlp_tc2.cu).  It is correct (same parity tests) but not faster:
-    // its N=128 cells re-read the A operand twice, which makes the SS-mode MMAs shared-memory-bandwidth bound
-    // once the epilogue's stores overlap them (measured 7.06 ms vs 6.92 ms per 32768x192 points); see DESIGN.md.
+    // debug bits 2/3/5 select the parked variants of csrc/experimental/ (built only with -DDMNERF_EXPERIMENTAL; all
+    // correct, none faster than this kernel -- measurements in DESIGN.md 4.1)
+#ifndef DMNERF_EXPERIMENTAL
+    DM_REQUIRE(!(g_tc_debug_flags & (4 | 8 | 32)), DMNERF_EUNSUPPORTED,
+               "mlp_fwd(bf16): forward variants are not in this build (compile with -DDMNERF_EXPERIMENTAL)");
+#else
     if (g_tc_debug_flags & (4 | 8 | 32)) {
         const int rc = (g_tc_debug_flags & 4)   ? launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st)
                        : (g_tc_debug_flags & 8) ? launch_mlp_bf16_v3(in, packed, ins_num, raw_out, stash, st)
@@ -476,6 +481,7 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
         // the variants stash the activations only; the dgrad chain's sign masks are derived from them here
         return (rc == DMNERF_OK && stash) ? launch_masks_from_acts(stash, in.n_points, st) : rc;
     }
+#endif
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -511,8 +517,10 @@ int debug_counters_v1(long long* host_out8) {
     return DMNERF_OK;
 }
 
+#ifdef DMNERF_EXPERIMENTAL
 namespace tc2 { int pack_v2(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
 namespace tc3 { int pack_v3(const float* const* params, int ins_num, void* packed, cudaStream_t st); }
+#endif
 
 int64_t bf16_image_bytes(int ins_num) { return tc::make_image(ins_num).total_bytes; }
 
@@ -533,14 +541,38 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     DM_LAUNCH_CHECK("pack_bf16");
     // the operand streams of the parked forward variants are only written while one of them is selected (the host
     // cache key includes that bit): training repacks every step and should not pay for them
+#ifdef DMNERF_EXPERIMENTAL
     if (!(g_tc_debug_flags & (4 | 8 | 32))) return DMNERF_OK;
     if (int rc = tc2::pack_v2(params, ins_num, packed, st)) return rc;
     return tc3::pack_v3(params, ins_num, packed, st);
+#else
+    return DMNERF_OK;
+#endif
 }
 
 }  // namespace dmnerf
 
 using namespace dmnerf;
+
+#ifdef DMNERF_EXPERIMENTAL
+namespace dmnerf {
+namespace tc2 { int debug_counters_v2(long long* host_out8); }
+namespace tc3 { int debug_counters_v3(long long* host_out8); }
+namespace tc4 { int debug_counters_v4(long long* host_out8); }
+}
+#endif
+
+// cycle counters of block 0 of the last forward launch that ran with debug bit 4 (or a parked variant's bit) set
+extern "C" int dmnerf_debug_counters(long long* host_out8) {
+    DM_REQUIRE(host_out8, DMNERF_EINVAL, "debug_counters: null pointer");
+    DM_CUDA(cudaDeviceSynchronize());
+#ifdef DMNERF_EXPERIMENTAL
+    if (g_tc_debug_flags & 32) return tc4::debug_counters_v4(host_out8);
+    if (g_tc_debug_flags & 8) return tc3::debug_counters_v3(host_out8);
+    if (g_tc_debug_flags & 4) return tc2::debug_counters_v2(host_out8);
+#endif
+    return debug_counters_v1(host_out8);
+}
 
 extern "C" int dmnerf_debug_flags(int flags) {
     const int old = g_tc_debug_flags;

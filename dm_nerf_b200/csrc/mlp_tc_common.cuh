@@ -4,8 +4,10 @@
 #include "mlp_layout.cuh"
 #include "tc_ptx.cuh"
 #include <cuda_bf16.h>
-#include "mlp_tc2.cuh"
-#include "mlp_tc3.cuh"
+#ifdef DMNERF_EXPERIMENTAL            // parked forward variants (csrc/experimental/): not part of the product library
+#include "experimental/mlp_tc2.cuh"
+#include "experimental/mlp_tc3.cuh"
+#endif
 
 namespace dmnerf {
 namespace tc {
@@ -63,7 +65,9 @@ constexpr int kDgLayers = 9;
 constexpr int kF32Rgbf = 0, kF32Insf = 65536, kF32Rgb0 = 131072, kF32Ins0 = 131072 + 32768,
               kF32BRgbf = 131072 + 65536, kF32BInsf = kF32BRgbf + 256, kF32Floats = kF32BInsf + 256;
 
+#ifdef DMNERF_EXPERIMENTAL
 static_assert(tc2::kExtKg == kExtKg, "mlp_tc2.cuh out of sync");
+#endif
 
 struct Image {
     int64_t chunk_off[kLayers];   // byte offset of the layer's first chunk
@@ -103,17 +107,21 @@ __host__ __device__ inline Image make_image(int ins_num) {
         off += static_cast<int64_t>(im.dg_k[d]) * 256 * 2;
     }
     im.f32_off = off;        off += static_cast<int64_t>(kF32Floats) * 4;
+    im.fwb_off = off;        off += 9 * kFwBiasBlkBytes;
+    im.npad2 = ((ins_num + 5) + 31) & ~31;
+    im.v2_off = im.v2_sched_off = im.v3_off[0] = im.v3_off[1] = im.v3_sched_off = 0;
+    im.v2_chunks = im.v3_chunks = 0;
+#ifdef DMNERF_EXPERIMENTAL
     uint32_t v2_bytes = 0;
     im.v2_chunks = tc2::build_schedule(im.npad, nullptr, &v2_bytes);
     im.v2_off = off;         off += v2_bytes;
     im.v2_sched_off = off;   off += static_cast<int64_t>(tc2::kMaxChunks) * sizeof(tc2::Chunk);
-    im.fwb_off = off;        off += 9 * kFwBiasBlkBytes;
-    im.npad2 = ((ins_num + 5) + 31) & ~31;
     uint32_t v3_bytes = 0;
     im.v3_chunks = tc3::build_schedule(im.npad2, nullptr, nullptr, &v3_bytes);
     im.v3_off[0] = off;      off += v3_bytes;
     im.v3_off[1] = off;      off += v3_bytes;
     im.v3_sched_off = off;   off += static_cast<int64_t>(tc3::kMaxChunks) * sizeof(tc3::Chunk) + 16 * sizeof(int);
+#endif
     im.total_bytes = off;
     return im;
 }

@@ -87,7 +87,7 @@ penalizer_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         }
         __syncwarp();
         const int per = C - 5;
-        const unsigned total = static_cast<unsigned>(nbef) * per, magic = 0xFFFFFFFFu / per + 1u;
+        const unsigned total = static_cast<unsigned>(nbef) * per, magic = per > 1 ? 0xFFFFFFFFu / per + 1u : 0u;   // per == 1 (K = 1): li = e below
         constexpr int U = 4;
         for (unsigned base = 0; base < total; base += 32 * U) {
             float x[U], w[U];
@@ -96,7 +96,7 @@ penalizer_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                 const unsigned e = base + q * 32 + lane;
                 w[q] = 0.f; x[q] = 0.f;
                 if (e < total) {
-                    const unsigned li = __umulhi(e, magic);
+                    const unsigned li = per > 1 ? __umulhi(e, magic) : e;
                     const int sidx = list[li];
                     w[q] = cb[sidx - u.s0];
                     x[q] = __ldg(row + static_cast<int64_t>(sidx) * C + 4 + (e - li * per));
@@ -175,7 +175,7 @@ penalizer_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     }
     __syncwarp();
     const int per = C - 5;
-    const unsigned total = static_cast<unsigned>(nbef) * per, magic = 0xFFFFFFFFu / per + 1u;
+    const unsigned total = static_cast<unsigned>(nbef) * per, magic = per > 1 ? 0xFFFFFFFFu / per + 1u : 0u;   // per == 1 (K = 1): li = e below
     constexpr int U = 4;
     for (unsigned base = 0; base < total; base += 32 * U) {
         float x[U], w[U], acc[U];
@@ -185,7 +185,7 @@ penalizer_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
             const unsigned e = base + q * 32 + lane;
             w[q] = 0.f; x[q] = 0.f; acc[q] = 0.f; idx[q] = 0;
             if (e < total) {
-                const unsigned li = __umulhi(e, magic);
+                const unsigned li = per > 1 ? __umulhi(e, magic) : e;
                 const int sidx = list[li];
                 w[q] = cb[sidx - u.s0];
                 idx[q] = static_cast<int64_t>(sidx) * C + 4 + (e - li * per);

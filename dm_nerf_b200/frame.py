@@ -79,7 +79,8 @@ def manipulate_pixels(position_embedder, view_embedder, model_coarse, model_fine
     ``targets``: one dict per moved object with ``tar_id`` and either ``transformation`` (4x4; the target rays come
     from ``transformation @ ori_pose``, :431-433) or ``deform_func`` (+ ``amplitude``; origins shifted along x, :396-429).
     Rays are generated on the device per chunk and results land in preallocated buffers (no torch.cat growth).
-    Returns rgb [n,3], ins [n,K+1], tar_rgb [n,3], tar_ins [n,K+1] and labels uint8 [n] (argmax over ins[..., :-1])."""
+    Returns rgb [n,3], ins [n,K+1], tar_rgb [n,3], tar_ins [n,K+1] and labels uint8 [n] (argmax over all K+1 channels of
+    ins, K = "empty", as the demo's label image at manipulator.py:478)."""
     H, W, K = hwk
     dev = next(model_fine.parameters()).device
     if count is None:
@@ -115,7 +116,7 @@ def manipulate_pixels(position_embedder, view_embedder, model_coarse, model_fine
             rgb, ins, tar_rgb, tar_ins = manipulator(position_embedder, view_embedder, model_coarse, model_fine,
                                                      torch.stack([ro, rd], 0), torch.stack(tars, 0), margs)
             out["rgb"][a:b], out["ins"][a:b], out["tar_rgb"][a:b], out["tar_ins"][a:b] = rgb, ins, tar_rgb, tar_ins
-            out["labels"][a:b] = ops.label_argmax(ins[:, :-1].contiguous())
+            out["labels"][a:b] = ops.label_argmax(ins)       # torch.argmax(ins, -1) over all K+1 channels (:478)
     return out
 
 

@@ -1,2 +1,2 @@
 """Shadow of the reference's ``networks`` package for the per-ray hot path."""
-from . import dm_nerf, helpers, render, penalizer, manipulator  # noqa: F401
+from . import dm_nerf, helpers, render, penalizer, manipulator, evaluator  # noqa: F401

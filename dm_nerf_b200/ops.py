@@ -255,6 +255,14 @@ def hungarian(scores, n_valid):
     return col
 
 
+def hungarian_infeasible() -> int:
+    """Launches of ``hungarian`` since the last call whose score matrix had no assignment (a row of NaN / inf; scipy
+    raises ValueError there).  Synchronises the current stream -- call it outside captured graphs."""
+    cnt = C.c_int(0)
+    check(_lib.lib().dmnerf_hungarian_infeasible(C.byref(cnt), _stream()), "dmnerf_hungarian_infeasible")
+    return int(cnt.value)
+
+
 def composite_bwd(raw, z, rays_d, flags, ins_detach, d_rgb, d_depth, d_weights, d_ins, fwd=None):
     """``fwd`` = (weights, trans, ins) kept from the forward -> one reverse pass instead of recompute + reverse."""
     n, s, c = raw.shape

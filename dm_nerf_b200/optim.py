@@ -112,3 +112,5 @@ class FlatAdam:
                 idx += 1
         if sd.get("param_groups"):
             self.lr = float(sd["param_groups"][0]["lr"])
+            if self.lr_tensor is not None:               # the value a captured step actually reads
+                self.lr_tensor.fill_(self.lr)

@@ -59,4 +59,5 @@ def allreduce_grads(params: List[torch.nn.Parameter], flat: Optional[torch.Tenso
     torch._foreach_copy_(list(flat.split([g.numel() for g in grads])), [g.reshape(-1) for g in grads])
     dist.all_reduce(flat, op=dist.ReduceOp.SUM)
     flat.div_(dist.get_world_size())
-    torch._foreach_copy_([g.reshape(-1) for g in grads], list(flat.split([g.numel() for g in grads])))
+    # copy back through views shaped like the gradients: reshape(-1) of a non-contiguous grad would be a temporary
+    torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])

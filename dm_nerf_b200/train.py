@@ -83,9 +83,19 @@ class TrainStep:
         s_img.copy_(image, non_blocking=True)
         s_pose.copy_(torch.as_tensor(pose, dtype=torch.float32)[:3, :4], non_blocking=True)
         s_lab.copy_(labels, non_blocking=True)
-        self.lr_t.fill_(a.lrate * (0.1 ** (self.iteration / (a.lrate_decay * 1000))))         # train_dmsr.py:68-72
+        # step i runs with lr(i-1), as the eager path and the reference do: the decay is applied AFTER the optimizer
+        # step (train_dmsr.py:66-72), so it first acts on the next iteration
+        self.lr_t.fill_(a.lrate * (0.1 ** (max(self.iteration - 1, 0) / (a.lrate_decay * 1000))))
         if self._graph is None:
-            # warm-up on a side stream (allocator, lazy state of Adam, NCCL), then capture one step
+            # warm-up on a side stream (allocator, NCCL communicators, lazy module state), then capture one step.  The
+            # warm-up steps are real optimizer steps on this first batch, so they run on throw-away state: parameters,
+            # Adam moments, step counter and the pixel-draw counter are snapshotted and put back after the capture --
+            # the first replay is then step 0 of the schedule, exactly like the eager path.
+            if self._draw_step is None:
+                self._draw(s_img)                             # creates the device counter; the draw itself is discarded
+                self._draw_step.zero_()
+            snap = [(g["p"].clone(), g["m"].clone(), g["v"].clone()) for g in self.opt.groups]
+            snap_step, snap_draw = self.opt.step_t.clone(), self._draw_step.clone()
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
@@ -95,7 +105,11 @@ class TrainStep:
             self._graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self._graph):
                 self._static_out = self._step_eager(s_img, s_pose, s_lab, self._K_dev, decay=False)
-            self.iteration += 3
+            for g, (p0, m0, v0) in zip(self.opt.groups, snap):
+                g["p"].copy_(p0); g["m"].copy_(m0); g["v"].copy_(v0)
+            self.opt.step_t.copy_(snap_step)
+            self._draw_step.copy_(snap_draw)
+            self.mc._packed.clear(); self.mf._packed.clear()
         self._graph.replay()
         self.iteration += 1
         # the packed-weight caches were filled inside the graph: their keys do not see the replayed Adam updates

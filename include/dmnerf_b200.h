@@ -37,6 +37,7 @@ extern "C" {
 int  dmnerf_version(void);
 int  dmnerf_last_error(char* buf, int cap);        /* copies the last message, returns its length */
 int  dmnerf_built_arch(void);                      /* 100 => sm_100a image present               */
+int  dmnerf_has_experimental(void);                /* 1 when built with -DDMNERF_EXPERIMENTAL (parked forward variants) */
 
 /* ---- weights -------------------------------------------------------------------------------
  * params: HOST array of DMNERF_NUM_PARAMS device pointers in state_dict order:
@@ -151,7 +152,8 @@ int  dmnerf_rays_k_dev(int H, int W, const float* K_dev, const float* c2w_dev, i
                        const int64_t* pix_idx, int64_t n, float* rays_o, float* rays_d, void* stream);
 /* Standalone Embedder.embed (networks/dm_nerf.py:37-38): x [n,3] -> out [n, 3+6*n_freqs]. */
 int  dmnerf_embed(const float* x, int64_t n, int n_freqs, float* out, void* stream);
-/* Per-ray label image: argmax over sigmoid'ed instance map (first max wins), uint8 out. */
+/* Per-ray label image: plain argmax of a composited instance map whose entries are probabilities already (first
+ * maximum wins) = torch.argmax(ins, -1) at networks/evaluator.py:132, networks/manipulator.py:321,478; uint8 out. */
 int  dmnerf_label_argmax(const float* ins, int64_t n, int k, uint8_t* labels, void* stream);
 
 /* Linear-sum assignment on the device (replaces scipy.optimize.linear_sum_assignment at networks/evaluator.py:45-46
@@ -161,6 +163,10 @@ int  dmnerf_label_argmax(const float* ins, int64_t n, int k, uint8_t* labels, vo
  * of each assigned row, then the unmatched columns in ascending order.  No host synchronisation. */
 int  dmnerf_hungarian(const float* scores, int n_mats, int64_t mat_stride, int ld, const int* n_valid, int n_cols,
                       int* col_out, void* stream);
+/* A score matrix with a row that has no finite entry (NaN / inf, e.g. a diverged step) has no assignment; scipy raises
+ * ValueError (evaluator.py:45).  The kernel then writes the identity permutation (every slot defined and in range) and
+ * counts the launch.  This call SYNCHRONISES the stream, returns the count since the last query and resets it. */
+int  dmnerf_hungarian_infeasible(int* count_out, void* stream);
 
 /* ---- self test of the tcgen05 building blocks (used by tests/) ---------------------------------------
  * D[128,n] = A[128,k] * B[n,k]^T in bf16 with fp32 accumulate; a,b fp32 in, d fp32 out. */

@@ -326,6 +326,50 @@ def main():
     save("select_crop", K=K, c2w=c2w, rgb=rgb, ins_target=ins_t, crop_mask=crop, ins_index=ins_index, N_train=np.int64(40),
          seed=np.int64(1234), target_c=tc, target_i=ti, rays=br, N_ins=np.int64(n_ins), full_c=fc, full_i=fi, full_rays=fr)
 
+    # ---- a10 on realistic logits: the coarse field's own raw and the fine pass's accumulated maps, as manipulator.py
+    # :141-177 hands them to exchanger (no planted ties; the move label is the most frequent pixel label) -------------
+    ins_num, n = 32, 96
+    pc, pf, mc, mf = ref_models(R, ins_num, 510, 610, 8.0)
+    ori_rays = synth_rays(n, 51)
+    tar_rays = ori_rays + 0.05 * synth_rays(n, 52)
+    g = torch.Generator().manual_seed(23)
+    with torch.no_grad():
+        def stage(rays, u):
+            raw, z = R.mani.manipulator_nerf(rays, pe, ve, mc, 64, 4.0, 15.0)
+            _, w, _, _ = R.mani.manipulator_render(raw, z, rays[1])
+            rq.push(u)
+            zs = R.helpers.sample_pdf(.5 * (z[..., 1:] + z[..., :-1]), w[..., 1:-1], 128).detach()
+            zf, _ = torch.sort(torch.cat([z, zs], -1), -1)
+            raw_f, _ = R.mani.manipulator_nerf(rays, pe, ve, mf, z_vals=zf)
+            _, _, _, acc = R.mani.manipulator_render(raw_f, zf, rays[1])
+            return raw, acc
+        o_raw_in, o_acc = stage(ori_rays, torch.rand(n, 128, generator=g))
+        t_raw_in, t_acc = stage(tar_rays, torch.rand(n, 128, generator=g))
+        move = int(torch.bincount(torch.argmax(torch.sigmoid(o_acc[..., :-1]), -1), minlength=ins_num).argmax())
+        o_raw, _, o_lab, t_lab = R.mani.exchanger(o_raw_in.clone(), [t_raw_in.clone()], o_acc, [t_acc], [move])
+    save("exchanger_real", ori_raw=o_raw_in, tar_raw0=t_raw_in, ori_acc=o_acc, tar_acc0=t_acc,
+         move_labels=np.array([move]), out_raw=o_raw, out_label=o_lab, tar_label=t_lab)
+
+    # ---- a11 on a batch large enough for a statistic (the 9-ray fixture above stays as the smoke case) -----------------
+    ins_num, n = 32, 96
+    pc, pf, mc, mf = ref_models(R, ins_num, 500, 600, 8.0)
+    ori_rays = synth_rays(n, 61)
+    tar_rays = (ori_rays + 0.05 * synth_rays(n, 62))[None]
+    g = torch.Generator().manual_seed(28)
+    us = [torch.rand(n, 128, generator=g) for _ in range(3)]
+    rq.push(*[u.clone() for u in us])
+    with torch.no_grad():
+        stage1_raw, _ = R.mani.manipulator_nerf(ori_rays, pe, ve, mc, 64, 4.0, 15.0)
+        _, _, _, acc1 = R.mani.manipulator_render(stage1_raw, R.mani.manipulator_nerf(ori_rays, pe, ve, mc, 64, 4.0, 15.0)[1],
+                                                  ori_rays[1])
+        move = int(torch.bincount(torch.argmax(acc1[..., :-1], -1), minlength=ins_num).argmax())
+        args = SimpleNamespace(N_samples=64, N_importance=128, near=4.0, far=15.0, target_label=[move])
+        f_rgb, f_ins, t_rgb, t_acc = R.mani.manipulator(pe, ve, mc, mf, ori_rays, tar_rays, args)
+    assert not rq.q
+    save("manipulator_n96", ori_rays=ori_rays, tar_rays=tar_rays, u0=us[0], u1=us[1], u2=us[2],
+         final_rgb=f_rgb, final_ins=f_ins, tar_rgb=t_rgb, tar_acc=t_acc, target_label=np.array([move]),
+         seed_c=np.int64(500), seed_f=np.int64(600), head_gain=np.float32(8.0), ins_num=np.int64(32))
+
     torch.rand = rq._orig
 
 

@@ -295,12 +295,37 @@ def test_exchanger(golden):
     assert o.data_ptr() == ori.data_ptr()
     amb = _sigmoid_tie_rows(g["ori_raw"][..., 4:]) | _sigmoid_tie_rows(g["tar_raw0"][..., 4:]) \
         | _sigmoid_tie_rows(g["tar_raw1"][..., 4:])
+    print(f"exchanger stress fixture: {amb.mean():.4f} of rows excluded as 2-ulp sigmoid ties "
+          f"(the fixture plants x6 logits + 12 boosts to produce them); "
+          f"label mismatches overall: {(lab.cpu().numpy() != g['out_label']).sum()} of {amb.size}")
     assert amb.mean() < 0.15
     ok = ~amb
     assert np.array_equal(lab.cpu().numpy()[ok], g["out_label"][ok])
     assert np.array_equal(tlab.cpu().numpy()[ok], g["tar_label"][ok])
     assert np.array_equal(o.cpu().numpy()[ok], g["out_raw"][ok])
     assert (lab.cpu().numpy() == g["out_label"]).mean() > 0.999
+
+
+def test_exchanger_realistic_logits(golden):
+    """The same comparison on the logits ``manipulator`` really hands over (coarse raw of a random-init field with
+    8x heads, accumulated maps of its fine pass; nothing planted): the excluded fraction must be ~0, and everything,
+    excluded rows included, must agree to 99.9 %."""
+    from dm_nerf_b200.networks.manipulator import exchanger
+    g = golden("exchanger_real")
+    ori = cu(g["ori_raw"]).clone()
+    o, _, lab, tlab = exchanger(ori, [cu(g["tar_raw0"]).clone()], cu(g["ori_acc"]), [cu(g["tar_acc0"])],
+                                [int(m) for m in g["move_labels"]])
+    amb = _sigmoid_tie_rows(g["ori_raw"][..., 4:]) | _sigmoid_tie_rows(g["tar_raw0"][..., 4:])
+    lab, tlab, o = lab.cpu().numpy(), tlab.cpu().numpy(), o.cpu().numpy()
+    changed = float((g["out_raw"] != g["ori_raw"]).any(-1).mean())
+    print(f"exchanger realistic fixture: excluded {amb.mean():.5f} of {amb.size} rows, {changed:.2f} of rows edited, "
+          f"label mismatches {(lab != g['out_label']).sum()} + {(tlab != g['tar_label']).sum()}")
+    assert changed > 0.2                       # the fixture does exercise the exchange
+    assert amb.mean() <= 0.002
+    ok = ~amb
+    assert np.array_equal(lab[ok], g["out_label"][ok]) and np.array_equal(tlab[ok], g["tar_label"][ok])
+    assert np.array_equal(o[ok], g["out_raw"][ok])
+    assert (lab == g["out_label"]).mean() >= 0.999 and (o == g["out_raw"]).all(-1).mean() >= 0.999
 
 
 def test_exchanger_hand_built():
@@ -329,10 +354,11 @@ def test_exchanger_hand_built():
     assert int(ref_lab[2, 0]) == 0
 
 
-def test_manipulator_end_to_end(golden):
+@pytest.mark.parametrize("fixture,floor", [("manipulator", 8 / 9), ("manipulator_n96", 0.95)])
+def test_manipulator_end_to_end(golden, fixture, floor):
     from types import SimpleNamespace
     from dm_nerf_b200.networks.manipulator import manipulator
-    g = golden("manipulator")
+    g = golden(fixture)
     mc = make_model(32, int(g["seed_c"]), float(g["head_gain"]))
     mf = make_model(32, int(g["seed_f"]), float(g["head_gain"]))
     pe, ve = embedders()
@@ -344,8 +370,18 @@ def test_manipulator_end_to_end(golden):
     close(t_rgb, g["tar_rgb"], 1e-4); close(t_acc, g["tar_acc"], 1e-4)
     # the final image depends on discrete per-sample exchange decisions; a flipped near-tie label
     # changes one ray, so compare ray-wise and require (almost) all rays within the fp32 bound
-    err = np.abs(rgb.cpu().numpy() - g["final_rgb"]).max(-1)
-    assert (err <= 1e-4).mean() >= 0.85 and ins.shape == g["final_ins"].shape
+    # (a per-sample label that flips on a near-tie swaps or zeroes that sample's raw row, manipulator.py:64-81), so the
+    # bound is per ray: rgb AND every channel of the composited instance map within 1e-4, for all but the flipped rays
+    assert ins.shape == g["final_ins"].shape
+    err_rgb = np.abs(rgb.cpu().numpy() - g["final_rgb"]).max(-1)
+    err_ins = np.abs(ins.cpu().numpy() - g["final_ins"]).max(-1)
+    good = (err_rgb <= 1e-4) & (err_ins <= 1e-4)
+    lab_ok = ins.cpu().numpy().argmax(-1) == g["final_ins"].argmax(-1)
+    print(f"{fixture}: {int((~good).sum())} of {good.size} rays outside 1e-4 (rgb {int((err_rgb > 1e-4).sum())}, "
+          f"ins {int((err_ins > 1e-4).sum())}; worst rgb {err_rgb.max():.2e}, ins {err_ins.max():.2e}); "
+          f"pixel labels differ on {int((~lab_ok).sum())} rays")
+    assert good.mean() >= floor - 1e-9
+    assert lab_ok.mean() >= floor - 1e-9
 
 
 def test_rays_k(golden):
@@ -595,6 +631,8 @@ def test_mlp_bf16_pipelined_variant_matches_lockstep(flag, n_rays, k):
     debug bit 5) compute the same network as the default kernel; the only numeric difference is the bias entering through the GEMM as a
     bf16 hi+lo pair."""
     from dm_nerf_b200 import _lib
+    if not _lib.lib().dmnerf_has_experimental():
+        pytest.skip("parked forward variants are not in the product library (build with DMNERF_EXPERIMENTAL=1)")
     m = make_model(k, 4)
     gen = torch.Generator().manual_seed(8)
     o, d = cu((torch.rand(n_rays, 3, generator=gen) - 0.5) * 2), cu(torch.randn(n_rays, 3, generator=gen))
@@ -848,8 +886,7 @@ def test_manipulate_pixels_matches_chunked_manipulator():
                                                  torch.stack([torch.stack([to, td], 0), torch.stack([do, rd], 0)], 0), margs)
     assert torch.equal(whole["rgb"], rgb) and torch.equal(whole["ins"], ins)
     assert torch.equal(whole["tar_rgb"], tar_rgb) and torch.equal(whole["tar_ins"], tar_ins)
-    assert torch.equal(whole["labels"].long(), torch.sigmoid(ins[:, :-1]).argmax(-1)) or \
-        float((whole["labels"].long() != ins[:, :-1].argmax(-1)).float().mean()) < 0.02
+    assert torch.equal(whole["labels"].long(), ins.argmax(-1))            # manipulator.py:478: all K+1 channels
     # deform rows: sin(8 pi / 400 * row) * amplitude, constant along a row (manipulator.py:401-405)
     off = deform_offsets(H, W, "sin", 0.18).reshape(H, W)
     assert torch.allclose(off[:, 0], torch.sin(torch.arange(1, H + 1).double() * (8 * np.pi / 400)) * 0.18)

@@ -1,0 +1,167 @@
+"""The drop-in boundary: after ``dm_nerf_b200.install()`` the reference's OWN drivers bind to the B200
+path -- every import line of train_dmsr.py:5-11, test_dmsr.py:5-10, networks/tester.py:11-15,
+tools/mesh_generator.py:8-9 executes, hot-path names resolve to dm_nerf_b200, everything else stays the reference's.
+
+The reference is read from ``oracle/_ref`` (staged by oracle/make_ref.sh; it travels to the GPU box) or, in the
+authoring container, /root/reference.  Every case runs in a subprocess: install() patches ``sys.modules``.
+"""
+import os
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import ref_loader  # noqa: E402
+
+REF = ref_loader.reference_root()
+needs_ref = pytest.mark.skipif(REF is None, reason="reference not staged (oracle/make_ref.sh)")
+
+
+def _run(code: str, env_extra=None, timeout=600):
+    env = dict(os.environ)
+    env.pop("DMNERF_REFERENCE", None)
+    env.update(env_extra or {})
+    res = subprocess.run([sys.executable, "-c", textwrap.dedent(code)], capture_output=True, text=True, cwd=ROOT, env=env,
+                         timeout=timeout)
+    assert res.returncode == 0, res.stdout[-3000:] + "\n" + res.stderr[-3000:]
+    return res.stdout
+
+
+def _import_lines(path, first, last):
+    """The import statements among lines [first, last] of a reference file (1-based, inclusive), verbatim."""
+    lines = open(path).read().split("\n")[first - 1:last]
+    return [ln for ln in lines if ln.startswith(("import ", "from "))]
+
+
+@needs_ref
+def test_driver_import_lines_bind_after_install():
+    lines = (_import_lines(os.path.join(REF, "train_dmsr.py"), 1, 11)
+             + _import_lines(os.path.join(REF, "test_dmsr.py"), 1, 10)
+             + _import_lines(os.path.join(REF, "networks", "tester.py"), 1, 15)
+             + _import_lines(os.path.join(REF, "tools", "mesh_generator.py"), 1, 9))
+    assert any("render_test" in ln for ln in lines) and any("ins_criterion" in ln for ln in lines)
+    assert any(ln.strip() == "from networks import manipulator" for ln in lines)
+    code = f"""
+        import sys
+        sys.path.insert(0, {ROOT!r}); sys.path.insert(0, {os.path.join(ROOT, 'oracle')!r})
+        import ref_loader, types, os
+        ref_loader.stub_io_modules()
+        # this image ships an unrelated regular package called `datasets` (Hugging Face), which shadows the reference's
+        # namespace directory of that name whatever the path order: point the name at the reference's loaders
+        ds = types.ModuleType("datasets"); ds.__path__ = [os.path.join({REF!r}, "datasets")]; sys.modules["datasets"] = ds
+        import dm_nerf_b200
+        assert dm_nerf_b200.install(reference_root={REF!r}) == "patched"
+        import torch
+        assert not torch.is_anomaly_enabled()
+        for ln in {lines!r}:
+            exec(ln)
+        ours = lambda f: f.__module__.startswith("dm_nerf_b200.")
+        # train_dmsr.py:5-11
+        assert ours(dm_nerf) and ours(ins_penalizer) and ours(get_select_full) and ours(z_val_sample) and ours(ins_criterion)
+        assert img2mse.__module__ == "networks.evaluator" and mse2psnr.__module__ == "networks.evaluator"
+        assert render_test.__module__ == "networks.tester"
+        # test_dmsr.py:5-10 -- the reference's demo / eval loops, our per-chunk functions inside them
+        assert manipulator.manipulator_demo.__module__ == "networks.manipulator"
+        assert manipulator.manipulator_eval.__module__ == "networks.manipulator"
+        for n in ("exchanger", "manipulator_render", "manipulator_nerf", "manipulator", "get_rays_k", "sample_pdf"):
+            assert ours(getattr(manipulator, n)), n
+        assert manipulator.to8b.__module__ == "networks.evaluator" and manipulator.ins_eval.__module__ == "networks.evaluator"
+        assert ours(create_nerf.__globals__["DM_NeRF"]) and ours(create_nerf.__globals__["get_embedder"])
+        assert mesh_main.__module__ == "tools.mesh_generator" and ours(mesh_main.__globals__["dm_nerf"])
+        # networks/tester.py:11-15 as the module itself bound them
+        import networks.tester as t
+        assert ours(t.dm_nerf) and ours(t.get_rays_k) and ours(t.z_val_sample)
+        assert t.to8b.__module__ == "networks.evaluator" and t.ins_eval.__module__ == "networks.evaluator"
+        # the state_dict contract through the reference's own constructor (config.py:152-158)
+        from types import SimpleNamespace
+        a = SimpleNamespace(multires=10, multires_views=4, i_embed=0, netdepth=8, netwidth=256, ins_num=32, device="cpu")
+        pe, ve, mc, mf, _ = create_nerf(a)
+        assert type(mc).__module__ == "dm_nerf_b200.networks.dm_nerf" and pe.out_dim == 63 and ve.out_dim == 27
+        dm_nerf_b200.uninstall()
+        import networks.render as r
+        assert r.dm_nerf.__module__ == "networks.render" and t.dm_nerf.__module__ == "networks.render"
+        print("bound ok")
+    """
+    assert "bound ok" in _run(code)
+
+
+def test_install_without_reference_aliases_the_mirror():
+    code = f"""
+        import sys
+        sys.path.insert(0, {ROOT!r})
+        import dm_nerf_b200
+        assert dm_nerf_b200.install() == "aliased"
+        from networks.render import dm_nerf, render_train
+        from networks.helpers import sample_pdf, z_val_sample, get_rays_k
+        from networks.dm_nerf import DM_NeRF, get_embedder
+        from networks.penalizer import ins_penalizer
+        from networks import manipulator
+        assert dm_nerf.__module__ == "dm_nerf_b200.networks.render" and manipulator.exchanger.__module__.startswith("dm_nerf_b200")
+        print("alias ok")
+    """
+    assert "alias ok" in _run(code, env_extra={"PYTHONPATH": ""})
+
+
+@needs_ref
+def test_harness_drives_the_unmodified_reference(tmp_path):
+    """tests/driver_harness.py with the reference untouched (torch CPU): proves the GPU case below drives real driver
+    code -- render_test's chunk loop + metrics plumbing, manipulator_demo's loop -- and not a re-implementation."""
+    out = str(tmp_path / "ref.npz")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "driver_harness.py"), "reference", "cpu", out],
+                         capture_output=True, text=True, cwd=ROOT, timeout=900)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
+    g = np.load(out)
+    assert g["render_rgb"].shape == (2 * 24 * 32, 3) and int(g["n_chunks"]) == 6
+    assert list(g["bound"]) == ["networks.helpers", "networks.manipulator", "networks.manipulator", "networks.dm_nerf"]
+    assert g["render_png0"].dtype == np.uint8 and g["mani_mask0"].shape == (24, 32)
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_reference_drivers_run_on_the_b200_path(tmp_path):
+    """render_test (tester.py:54-84) and manipulator_demo (manipulator.py:383-469) after install(), 32x24 frame, against
+    frame.render_pixels / frame.manipulate_pixels on the same models: identical pixels (rays are independent; chunking
+    must not matter), identical 8-bit images, identical label image."""
+    import torch
+    from types import SimpleNamespace
+    from dm_nerf_b200 import synth
+    from dm_nerf_b200.frame import manipulate_pixels, render_pixels
+    from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
+    import driver_harness as dh
+    out = str(tmp_path / "inst.npz")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "driver_harness.py"), "installed", "cuda", out],
+                         capture_output=True, text=True, cwd=ROOT, timeout=900)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
+    g = np.load(out)
+    assert list(g["bound"]) == ["dm_nerf_b200.networks.helpers", "dm_nerf_b200.networks.manipulator",
+                                "networks.manipulator", "dm_nerf_b200.networks.dm_nerf"]
+    assert int(g["n_chunks"]) == 6
+    dev = "cuda"
+    mc, mf = DM_NeRF(8, 256, 63, 27, [4], dh.K_INS), DM_NeRF(8, 256, 63, 27, [4], dh.K_INS)
+    mc.load_state_dict(synth.init_state_dict(dh.K_INS, 1, 8.0)); mf.load_state_dict(synth.init_state_dict(dh.K_INS, 2, 8.0))
+    mc, mf = mc.to(dev), mf.to(dev)
+    pe, ve = get_embedder(10, 0)[0], get_embedder(4, 0)[0]
+    Kmat, _ = synth.dmsr_camera(dh.H, dh.W, 0)
+    frames = []
+    for v in range(2):
+        pose = synth.dmsr_camera(dh.H, dh.W, v)[1]
+        f = render_pixels(pe, ve, mc, mf, (dh.H, dh.W, Kmat), pose, dh.NEAR, dh.FAR, dh.SC, dh.NIMP)
+        frames.append({k: t.cpu().numpy().copy() for k, t in f.items()})
+    rgb = np.concatenate([f["rgb"] for f in frames], 0)
+    ins = np.concatenate([f["ins"] for f in frames], 0)
+    assert np.array_equal(g["render_rgb"], rgb) and np.array_equal(g["render_ins"], ins)
+    to8b = lambda x: (255 * np.clip(x, 0, 1)).astype(np.uint8)                       # evaluator.py:13
+    assert np.array_equal(g["render_png0"], to8b(frames[0]["rgb"].reshape(dh.H, dh.W, 3)))
+    assert np.array_equal(frames[0]["labels"], frames[0]["ins"].argmax(-1).astype(np.uint8))
+    # manipulator_demo's view: same rays, same chunking (N_test), same torch.rand stream
+    args = SimpleNamespace(N_samples=dh.SC, N_importance=dh.NIMP, near=dh.NEAR, far=dh.FAR)
+    pose0 = synth.dmsr_camera(dh.H, dh.W, 0)[1]
+    torch.manual_seed(11)
+    m = manipulate_pixels(pe, ve, mc, mf, (dh.H, dh.W, Kmat), pose0, [{"tar_id": 8, "transformation": torch.from_numpy(g["mani_trans"])}],
+                          args, chunk=dh.N_TEST)
+    assert np.array_equal(g["mani_png0"], to8b(m["rgb"].cpu().numpy().reshape(dh.H, dh.W, 3)))
+    assert np.array_equal(g["mani_mask0"], m["labels"].cpu().numpy().reshape(dh.H, dh.W))
