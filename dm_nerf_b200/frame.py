@@ -19,9 +19,12 @@ from .networks.render import dm_nerf
 def render_pixels(position_embedder, view_embedder, model_coarse, model_fine, hwk, c2w, near: float, far: float,
                   n_samples: int = 64, n_importance: int = 128, pix0: int = 0, count: Optional[int] = None,
                   chunk: int = 32768, rays: Optional[torch.Tensor] = None, labels: bool = True,
-                  out: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, torch.Tensor]:
+                  out: Optional[Dict[str, torch.Tensor]] = None, balance: bool = True) -> Dict[str, torch.Tensor]:
     """Deterministic (perturb=0) render of a pixel range.  Returns rgb [n,3], depth [n], ins [n,K]
-    and (optionally) labels uint8 [n].  ``rays`` [2,n,3] overrides in-kernel ray generation."""
+    and (optionally) labels uint8 [n].  ``rays`` [2,n,3] overrides in-kernel ray generation.
+    ``chunk`` bounds the rays per pass (raw_fine scratch = chunk * 192 * C * 4 bytes); with ``balance`` the range is cut
+    into equal passes of at most ``chunk`` rays instead of full chunks plus a short tail (the persistent MLP kernels
+    deal 256-point tile pairs round-robin to the SMs: a 5,632-ray tail costs whole rounds for a fraction of the work)."""
     H, W, K = hwk
     dev = next(model_fine.parameters()).device
     if count is None:
@@ -35,6 +38,10 @@ def render_pixels(position_embedder, view_embedder, model_coarse, model_fine, hw
     args = SimpleNamespace(perturb=0.0, N_importance=n_importance, is_train=False, N_ins=None)
     t = torch.linspace(0., 1., steps=n_samples, device=dev)
     z_row = (near + t * (far - near))[None]
+    if balance and count > 0:
+        passes = -(-count // chunk)
+        chunk = -(-count // passes)
+        chunk = min(count, (chunk + 127) // 128 * 128)          # whole 128-point tiles per pass
     with torch.no_grad():
         for a in range(0, count, chunk):
             b = min(count, a + chunk)

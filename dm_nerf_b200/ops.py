@@ -459,9 +459,8 @@ def exchange(ori_raw, tar_raw, ori_acc, tar_acc, move_label: int, ori_label: Opt
     if first:
         ori_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device)
     tar_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device)
-    check(_lib.lib().dmnerf_exchange(_ptr(ori_raw), _ptr(tar_raw), _ptr(ori_acc), _ptr(tar_acc), int(move_label),
-                                     int(first), n, s, c, _ptr(ori_label), _ptr(tar_label), _stream()),
-          "dmnerf_exchange")
+    _timed_call(f"dmnerf_exchange[S={s}]", _lib.lib().dmnerf_exchange, _ptr(ori_raw), _ptr(tar_raw), _ptr(ori_acc),
+                _ptr(tar_acc), int(move_label), int(first), n, s, c, _ptr(ori_label), _ptr(tar_label), _stream())
     _count()
     return ori_label, tar_label
 

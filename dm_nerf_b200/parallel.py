@@ -36,15 +36,61 @@ def gather_rows(local: torch.Tensor, total: int, dst: int = 0) -> Optional[torch
     return torch.cat([bufs[r][: sizes[r][1] - sizes[r][0]] for r in range(world)], 0)
 
 
-def render_sharded(render_fn: Callable[[int, int], Dict[str, torch.Tensor]], total: int,
-                   keys: Sequence[str] = ("rgb", "depth", "labels")) -> Optional[Dict[str, torch.Tensor]]:
-    """Each rank renders its pixel block with ``render_fn(pix0, count)``; rank 0 gets the frame."""
+def gather_frame(local: Dict[str, torch.Tensor], frame: Optional[Dict[str, torch.Tensor]], total: int,
+                 keys: Sequence[str], dst: int = 0) -> Optional[Dict[str, torch.Tensor]]:
+    """The final gather of a row-sharded frame without padding or concatenation: every rank sends its block of each
+    output ONCE, point to point, and ``dst`` receives it straight into rows [start_r, stop_r) of its preallocated frame
+    buffer (a contiguous slice: rows are the leading dimension).  All transfers form one batch (one NCCL group = the
+    ncclSend/ncclRecv formulation of a gather).  ``frame`` may already hold ``dst``'s own block (when ``local`` are views
+    of it nothing is copied).  Returns ``frame`` on ``dst``, None elsewhere."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        if frame is None:
+            return dict(local)
+        for k in keys:
+            if frame[k].data_ptr() != local[k].data_ptr():
+                frame[k][: local[k].shape[0]].copy_(local[k])
+        return frame
+    world, rank = dist.get_world_size(), dist.get_rank()
+    ops_ = []
+    if rank == dst:
+        assert frame is not None, "gather_frame: the destination rank passes the frame buffers"
+        a0, b0 = shard_range(total, dst, world)
+        for k in keys:
+            if frame[k][a0:b0].data_ptr() != local[k].data_ptr():
+                frame[k][a0:b0].copy_(local[k])
+            for r in range(world):
+                if r != dst:
+                    a, b = shard_range(total, r, world)
+                    if b > a:
+                        ops_.append(dist.P2POp(dist.irecv, frame[k][a:b], r))
+    else:
+        for k in keys:
+            if local[k].shape[0] > 0:
+                ops_.append(dist.P2POp(dist.isend, local[k].contiguous(), dst))
+    if ops_:
+        for w in dist.batch_isend_irecv(ops_):
+            w.wait()
+    return frame if rank == dst else None
+
+
+def render_sharded(render_fn: Callable[..., Dict[str, torch.Tensor]], total: int,
+                   keys: Sequence[str] = ("rgb", "depth", "labels"),
+                   frame: Optional[Dict[str, torch.Tensor]] = None) -> Optional[Dict[str, torch.Tensor]]:
+    """ONE frame split over the ranks (tester.py:62-76's chunk loop, sharded): rank r renders the contiguous pixel
+    block ``shard_range(total, r, world)`` with ``render_fn(pix0, count)`` -- no data-path communication -- and rank 0
+    ends up with the whole frame (``gather_frame``).  With ``frame`` (rank 0's preallocated buffers) rank 0 renders
+    straight into its rows: ``render_fn(pix0, count, out=...)`` is then called with views of them."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     rank = dist.get_rank() if dist.is_initialized() else 0
     a, b = shard_range(total, rank, world)
-    local = render_fn(a, b - a)
-    frame = {k: gather_rows(local[k], total) for k in keys}
-    return frame if rank == 0 else None
+    if frame is not None and rank == 0:
+        local = render_fn(a, b - a, out={k: frame[k][a:b] for k in frame})
+    else:
+        local = render_fn(a, b - a)
+    if rank == 0 and frame is None and world > 1:
+        frame = {k: torch.empty((total,) + tuple(local[k].shape[1:]), dtype=local[k].dtype, device=local[k].device)
+                 for k in keys}
+    return gather_frame(local, frame, total, keys)
 
 
 def allreduce_grads(params: List[torch.nn.Parameter], flat: Optional[torch.Tensor] = None) -> None:

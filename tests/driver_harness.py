@@ -36,9 +36,16 @@ def main(which: str, device: str, out_path: str) -> None:
         import dm_nerf_b200
         assert dm_nerf_b200.install(reference_root=root) == "patched"
     dev = torch.device(device)
-    if dev.type == "cuda" and which == "reference":
-        torch.set_default_device(dev)          # what config.initial() does with set_default_tensor_type (config.py:170);
-                                               # the B200 path allocates on the device explicitly and does not need it
+    # seeded inputs first, as numpy (the CPU generators must not see the CUDA default tensor type set below)
+    sd_c, sd_f = synth.init_state_dict(K_INS, 1, 8.0), synth.init_state_dict(K_INS, 2, 8.0)
+    K_np = synth.dmsr_camera(H, W, 0)[0].numpy()
+    poses_np = np.stack([synth.dmsr_camera(H, W, v)[1].numpy() for v in range(2)], 0)
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    imgs_np = torch.rand(2, H, W, 3, generator=gen, device="cpu").numpy()
+    labels_np = synth.block_labels(H, W, 4, device="cpu")[None].repeat(2, 1, 1).numpy()
+    if dev.type == "cuda":
+        # exactly what config.initial() does on a CUDA machine (config.py:169-171)
+        torch.set_default_tensor_type('torch.cuda.FloatTensor')
 
     # ---- the imports the drivers make (train_dmsr.py:5-11, test_dmsr.py:5-10), executed verbatim ----
     import config
@@ -51,15 +58,14 @@ def main(which: str, device: str, out_path: str) -> None:
                            device=dev, datadir="./data/dmsr/bedroom", N_test=N_TEST, near=NEAR, far=FAR, N_samples=SC,
                            N_importance=NIMP, perturb=0.0, is_train=False, N_ins=None, target_label=None)
     pe, ve, mc, mf, args = config.create_nerf(args)
-    mc.load_state_dict(synth.init_state_dict(K_INS, 1, 8.0))
-    mf.load_state_dict(synth.init_state_dict(K_INS, 2, 8.0))
+    mc.load_state_dict(sd_c)
+    mf.load_state_dict(sd_f)
     mc, mf = mc.to(dev).eval(), mf.to(dev).eval()
-    Kmat, _ = synth.dmsr_camera(H, W, 0)
-    poses = torch.stack([synth.dmsr_camera(H, W, v)[1] for v in range(2)], 0).cpu()
-    hwk = (H, W, Kmat.cpu().numpy())
-    gen = torch.Generator(device="cpu").manual_seed(5)
-    gt_imgs = torch.rand(2, H, W, 3, generator=gen, device="cpu")
-    gt_labels = synth.block_labels(H, W, 4, device="cpu").to(torch.int16)[None].repeat(2, 1, 1)
+    hwk = (H, W, K_np)
+    # test_dmsr.py:23-25 builds its inputs with torch.Tensor(numpy): on the default device
+    poses = torch.Tensor(poses_np)
+    gt_imgs = torch.Tensor(imgs_np)
+    gt_labels = torch.Tensor(labels_np).type(torch.int16)
     ins_rgbs = np.random.RandomState(0).randint(0, 255, size=(64, 3))
 
     # record what the hot path hands back to the driver, chunk by chunk
@@ -72,6 +78,21 @@ def main(which: str, device: str, out_path: str) -> None:
         rec["ins"].append(info["ins_fine"].detach().cpu())
         return info
     tester_mod.dm_nerf = recording_dm_nerf
+    if dev.type == "cuda":
+        # the reference's AP code (evaluator.py:76-175, out of scope) was written for torch 1.8 and mixes CPU inputs
+        # with default-device temporaries, which torch 2.x refuses; it is given the CPU default it needs for the call
+        import networks.evaluator as eval_mod
+        inner_eval = tester_mod.ins_eval
+
+        def ins_eval_on_cpu(*a, **k):
+            torch.set_default_tensor_type('torch.FloatTensor')
+            keep, eval_mod.device = eval_mod.device, torch.device("cpu")          # evaluator.py:16 module global
+            try:
+                return inner_eval(*a, **k)
+            finally:
+                eval_mod.device = keep
+                torch.set_default_tensor_type('torch.cuda.FloatTensor')
+        tester_mod.ins_eval = ins_eval_on_cpu
 
     out = {}
     with tempfile.TemporaryDirectory() as tmp, torch.no_grad():

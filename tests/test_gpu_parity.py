@@ -354,7 +354,7 @@ def test_exchanger_hand_built():
     assert int(ref_lab[2, 0]) == 0
 
 
-@pytest.mark.parametrize("fixture,floor", [("manipulator", 8 / 9), ("manipulator_n96", 0.95)])
+@pytest.mark.parametrize("fixture,floor", [("manipulator", 1.0), ("manipulator_n96", 1.0)])
 def test_manipulator_end_to_end(golden, fixture, floor):
     from types import SimpleNamespace
     from dm_nerf_b200.networks.manipulator import manipulator
@@ -747,7 +747,10 @@ def test_train_step_cuda_graph_replay():
             cur = mc.mlps[0].weight.detach().clone()
             assert float((cur - prev).abs().max()) > 0
             prev = cur
-        assert ts.iteration == 3 + 4                     # three warm-up steps before the capture, then one per call
+        assert ts.iteration == 4                         # the warm-up steps before the capture run on throw-away state
+        assert int(ts.opt.step_t) == 4                   # ... Adam's step counter included: 4 calls = 4 updates
+        want_lr = args.lrate * 0.1 ** (2 / (args.lrate_decay * 1000))       # call i (0-based) runs with lr(i-1) (train_dmsr.py:66-72)
+        assert abs(float(ts.lr_t) - want_lr) <= 1e-9
         # the replayed forward must run on the UPDATED weights (operand images repacked inside the graph): on a fixed
         # image the loss then falls steadily; with stale images it would only wander with the ray draw
         img = cu(torch.rand(H, W, 3, generator=gen))

@@ -43,6 +43,24 @@ def _worker(rank, world, port, q):
             ok = frame is None
         a, b = shard_range(n, rank, world)
         ok = ok and (b - a) == (51 if rank == 0 else 50)
+        # 1b. the same frame gathered point to point into rank 0's preallocated buffers (no padding, no cat); rank 0
+        # renders straight into its rows through `out`
+        def render_into(a, cnt, out=None):
+            res = render_fn(a, cnt)
+            if out is None:
+                return res
+            for kk in out:
+                out[kk].copy_(res[kk])
+            return out
+        bufs = None
+        if rank == 0:
+            bufs = {"rgb": torch.full((n, 3), -1.0), "depth": torch.full((n,), -1.0),
+                    "labels": torch.full((n,), 255, dtype=torch.uint8)}
+        frame2 = render_sharded(render_into, n, frame=bufs)
+        if rank == 0:
+            ok = ok and frame2 is bufs and all(torch.equal(frame2[kk], full[kk]) for kk in full)
+        else:
+            ok = ok and frame2 is None
         # 2. gradient all-reduce == gradient of the mean loss over the concatenated batch
         torch.manual_seed(1)
         lin = torch.nn.Linear(6, 3)
