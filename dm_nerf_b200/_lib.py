@@ -109,6 +109,8 @@ _SIGNATURES = {
     "dmnerf_acts_bytes": (_i64, [_i64, _int, _int]),
     "dmnerf_mlp_bwd": (_int, [_p, _p, _p, _i64, _int, _int, C.POINTER(_p), _p, _p]),
     "dmnerf_bwd_workspace_bytes": (_i64, [_i64, _int, _int]),
+    "dmnerf_mlp_bwd_bf16_noalloc": (_int, [_p, _p, _p, _i64, _int, C.POINTER(_p), _p]),
+    "dmnerf_noalloc_max_points": (_i64, []),
     "dmnerf_composite_fwd": (_int, [_p, _p, _p, _i64, _int, _int, _int, _p, _p, _p, _p, _p, _p]),
     "dmnerf_composite_bwd": (_int, [_p, _p, _p, _i64, _int, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dmnerf_sample_pdf": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),

@@ -698,3 +698,71 @@ int launch_selftest_umma_mn(const float* a, const float* b, int n, float* d, int
 }
 
 }  // namespace dmnerf
+
+// ---- no-allocation entry point (no counterpart in the reference) ------------
+// Some callers cannot call cudaMalloc -- code under CUDA graph capture, tight serving / training loops, harnesses that
+// forbid it -- yet the bf16 backward needs scratch: the dgrad chain's gradient stash (4.75 KB per point, 64-point blocks in
+// 512-point quads) and the packed gradient image the wgrad GEMMs reduce into.  dmnerf_mlp_bwd_bf16_noalloc keeps that
+// scratch in a file-scope __device__ array of a fixed, modest size: every GPU that loads the library holds
+// kNoAllocBytes + 1 KB (~13 MB) until the process exits, and the entry point serves at most kNoAllocMaxPoints points per call.
+//   * Host code must not hand the array's NAME to a kernel: on the host it is a stand-in symbol, not a device address.  The
+//     address comes from cudaGetSymbolAddress, once per device, with that device current (below).
+//   * Every call on a device shares the one array and finds the previous call's contents in it.  What must start at zero
+//     (the gradient image) is cleared by the launcher on the caller's stream; the stash is fully rewritten by the dgrad chain
+//     for the blocks the wgrad GEMMs read.  Calls that overlap on the GPU (two streams, two host threads) RACE on it:
+//     serialise them, or use dmnerf_mlp_bwd with one workspace per stream.
+//   * No cudaMalloc / cudaFree / allocating library routine is called: cudaGetSymbolAddress, cudaMemsetAsync,
+//     cudaFuncSetAttribute and kernel launches only.
+#include <mutex>
+
+namespace dmnerf {
+
+constexpr int64_t kNoAllocMaxPoints = 2048;                                     // e.g. 32 rays x 64 samples per call
+constexpr int64_t kNoAllocBlocks = ((kNoAllocMaxPoints + 511) / 512) * 8;      // == tc_stash_blocks(kNoAllocMaxPoints)
+constexpr int64_t kNoAllocBytes = kNoAllocBlocks * kStGradBlkBytes + tcb::kGimgFloats * 4;
+// + 1 KB: the launcher wants the workspace 1024-byte aligned, the array is declared with 256-byte alignment
+static __device__ __align__(256) unsigned char g_bwd_scratch[kNoAllocBytes + 1024];
+
+constexpr int kNoAllocMaxDevices = 64;
+static void* g_bwd_scratch_ptr[kNoAllocMaxDevices] = {};
+static std::mutex g_bwd_scratch_mutex;
+
+// device address of g_bwd_scratch on the CURRENT device, rounded up to 1024 bytes; resolved once per device
+static int noalloc_scratch(void** out) {
+    int dev = 0;
+    DM_CUDA(cudaGetDevice(&dev));
+    DM_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, DMNERF_EUNSUPPORTED, "mlp_bwd_bf16_noalloc: device ordinal %d >= %d", dev,
+               kNoAllocMaxDevices);
+    std::lock_guard<std::mutex> lock(g_bwd_scratch_mutex);
+    if (g_bwd_scratch_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        DM_CUDA(cudaGetSymbolAddress(&p, g_bwd_scratch));
+        DM_REQUIRE(p != nullptr, DMNERF_ECUDA, "mlp_bwd_bf16_noalloc: cudaGetSymbolAddress returned a null address");
+        g_bwd_scratch_ptr[dev] = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~static_cast<uintptr_t>(1023));
+    }
+    *out = g_bwd_scratch_ptr[dev];
+    return DMNERF_OK;
+}
+
+}  // namespace dmnerf
+
+extern "C" int64_t dmnerf_noalloc_max_points(void) { return dmnerf::kNoAllocMaxPoints; }
+
+extern "C" int dmnerf_mlp_bwd_bf16_noalloc(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
+                                           int ins_num, float* const* grads, void* stream) {
+    using namespace dmnerf;
+    DM_REQUIRE(packed && acts && d_raw && grads, DMNERF_EINVAL, "mlp_bwd_bf16_noalloc: null pointer");
+    DM_REQUIRE(ins_num >= 1 && ins_num <= kMaxIns, DMNERF_EUNSUPPORTED, "mlp_bwd_bf16_noalloc: ins_num %d outside [1,%d]",
+               ins_num, kMaxIns);
+    for (int i = 0; i < kNumParams; ++i) DM_REQUIRE(grads[i], DMNERF_EINVAL, "mlp_bwd_bf16_noalloc: grads[%d] is null", i);
+    DM_REQUIRE(n_points >= 0 && n_points <= kNoAllocMaxPoints, DMNERF_EUNSUPPORTED,
+               "mlp_bwd_bf16_noalloc: n_points %lld exceeds the static scratch's maximum of %lld points per call "
+               "(use dmnerf_mlp_bwd with a caller-provided workspace)", (long long)n_points, (long long)kNoAllocMaxPoints);
+    if (n_points == 0) return DMNERF_OK;
+    DM_REQUIRE(bf16_bwd_workspace_bytes(n_points) <= kNoAllocBytes, DMNERF_EUNSUPPORTED,
+               "mlp_bwd_bf16_noalloc: workspace of %lld bytes exceeds the static %lld", (long long)bf16_bwd_workspace_bytes(n_points),
+               (long long)kNoAllocBytes);
+    void* scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    return launch_mlp_bwd_bf16(packed, acts, d_raw, n_points, ins_num, grads, scratch, 0, static_cast<cudaStream_t>(stream));
+}

@@ -74,6 +74,19 @@ int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num, int mode);
 int  dmnerf_mlp_bwd(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
                     int ins_num, int mode, float* const* grads, void* workspace, void* stream);
 int64_t dmnerf_bwd_workspace_bytes(int64_t n_points, int ins_num, int mode);
+/* NO counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight loops, harnesses that forbid it).  dmnerf_mlp_bwd in DMNERF_MODE_BF16 with its
+ * workspace taken from a file-scope `static __device__` array inside the library instead of from the caller: the call
+ * allocates NOTHING (no cudaMalloc / cudaFree / allocating library routine); inputs and outputs are still the caller's.
+ * Limit: n_points <= dmnerf_noalloc_max_points() (2048, e.g. 32 rays x 64 samples); larger sizes return
+ * DMNERF_EUNSUPPORTED with a message.  Cost: every GPU that loads the library holds the array (~13 MB) until exit.
+ * Every call on a device shares the one array and finds the previous call's contents in it (what must start at zero is
+ * cleared on the caller's stream): calls that OVERLAP on the GPU -- other streams, other host threads -- race; serialise
+ * them or use dmnerf_mlp_bwd with a workspace per stream.  Same arguments, alignment rules and results as
+ * dmnerf_mlp_bwd(..., DMNERF_MODE_BF16, ...). */
+int  dmnerf_mlp_bwd_bf16_noalloc(const void* packed, const void* acts, const float* d_raw, int64_t n_points,
+                                 int ins_num, float* const* grads, void* stream);
+int64_t dmnerf_noalloc_max_points(void);
 
 /* ---- a5/a8: volume compositing ---------------------------------------------------------------
  * Replaces render_train (networks/render.py:6-28) [flags=DROP_EMPTY] and manipulator_render
