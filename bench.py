@@ -1,17 +1,20 @@
 #!/usr/bin/env python
 """bench.py -- rays/sec of DM-NeRF's per-ray hot path on B200 (BASELINE.json metric).
 
-Workload at every N: DM-SR full-image render (BASELINE.json configs[1]): 640x480 = 307,200 rays,
-64 coarse + 128 fine samples per ray, K=32 instances, RGB + depth + instance map (+ uint8 labels),
-synthetic pose, random-init weights.  One "step" = one full frame per rank (weak scaling: each rank
-renders its own view of the sweep; rank 0 gathers the label maps).
+Headline workload at every N: ONE DM-SR frame (BASELINE.json configs[1]): 640x480 = 307,200 rays, 64 coarse + 128
+fine samples per ray, K=32 instances, RGB + depth + K-channel instance map + uint8 labels, synthetic pose,
+random-init weights.  One "step" = that one frame, its pixel rows sharded over the N ranks (STRONG scaling: rank r
+renders rows shard_range(H*W, r, N), no data-path communication) and gathered onto rank 0 inside the timed region.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--mode bf16|fp32] [--impl reference]
 
-Prints ONE JSON line (rank 0).  `value` = device-resident throughput (rays already in HBM),
-`e2e` = same frame through the public API with pinned HOST ray buffers in and host results out,
-`roofline` = the dominant kernel (fused PE+MLP, fine pass) against the measured bf16 tensor peak,
-`cpu_baseline` = the CPU oracle port (torch CPU fp32, all host threads) on a bounded ray sample.
+Prints ONE JSON line (rank 0):
+  value            device-resident throughput (rays generated on the device), max over ranks, gather included
+  e2e              same frame through the public API with pinned HOST ray buffers in and host results out
+  roofline         the dominant kernel (fused PE+MLP, fine pass) against the measured bf16 tensor peak
+  cpu_baseline     the UNMODIFIED reference (oracle/_ref, torch CPU fp32, all host threads) on a bounded ray sample
+  parity           bf16 mode against the fp32 parity mode on this very frame (PSNR delta, label agreement)
+  weak / c4 / c5 / fp32_mode / train   the other BASELINE.json configs and modes
 """
 from __future__ import annotations
 
@@ -32,20 +35,16 @@ H, W, K_INS, SC, NIMP = 480, 640, 32, 64, 128
 NEAR, FAR = 4.0, 15.0
 N_RAYS = H * W
 CPU_SAMPLE_RAYS = 24576                          # ~10-20 s of host work for the cpu_baseline leg
-MACS_PER_POINT = 691840 + 128 * K_INS            # algorithmic, padding not counted
-FLOP_PER_RAY = 2 * MACS_PER_POINT * (SC + SC + NIMP)
+REF_STEP_RAYS = 8192                             # rays per step of the --impl reference arm (2 tester.py chunks)
+C4 = dict(H=968, W=1296, K=16, near=0.0, far=9.5)            # ScanNet-shaped frame (configs[3])
 
 
-def synth_camera(torch, view: int):
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    focal = 0.5 * W / math.tan(0.5 * 0.6911)
-    Kmat = torch.tensor([[focal, 0, W / 2], [0, -focal, H / 2], [0, 0, -1]], dtype=torch.float32)
-    th, ph, rad = (37.0 + 45.0 * view) / 180 * math.pi, -65.0 / 180 * math.pi, 7.0
-    t = torch.eye(4); t[2, 3] = rad
-    rp = torch.tensor([[1, 0, 0, 0], [0, math.cos(ph), -math.sin(ph), 0], [0, math.sin(ph), math.cos(ph), 0], [0, 0, 0, 1]])
-    rt = torch.tensor([[math.cos(th), 0, -math.sin(th), 0], [0, 1, 0, 0], [math.sin(th), 0, math.cos(th), 0], [0, 0, 0, 1]])
-    flip = torch.tensor([[-1., 0, 0, 0], [0, 0, 1, 0], [0, 1, 0, 0], [0, 0, 0, 1]])
-    return Kmat, (flip @ rt.float() @ rp.float() @ t)
+def macs_per_point(k: int) -> int:
+    return 691840 + 128 * k                      # algorithmic, padding not counted
+
+
+def flop_per_ray(k: int, points: int = SC + SC + NIMP) -> float:
+    return 2.0 * macs_per_point(k) * points
 
 
 class ClockSampler(threading.Thread):
@@ -66,7 +65,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([c.strip() for c in r.stdout.strip().split(",")])
             except Exception:
                 pass
-            self._stop_evt.wait(0.2)
+            self._stop_evt.wait(0.1)
 
     def summary(self):
         self._stop_evt.set()
@@ -78,305 +77,6 @@ class ClockSampler(threading.Thread):
                 reasons.append(name)
         mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
-
-
-def cpu_oracle_rays_per_s(torch, n_rays: int, repeats: int = 1):
-    """The oracle port (torch CPU fp32, reference op order) on a bounded sample of the same workload:
-    n_rays of the frame, tester.py-style chunk.  Returns (rays/s, cores, seconds)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import dmnerf_oracle as orc
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    pc, pf = orc.init_params(K_INS, 1), orc.init_params(K_INS, 2)
-    Kmat, c2w = synth_camera(torch, 0)
-    ro, rd = orc.get_rays_k(H, W, Kmat, c2w)
-    sel = torch.linspace(0, N_RAYS - 1, n_rays).long()
-    rays = torch.stack([ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel]], 0)
-    zc = orc.z_val_sample(n_rays, NEAR, FAR, SC)
-    best = None
-    with torch.no_grad():
-        for _ in range(repeats):
-            t0 = time.perf_counter()
-            for a in range(0, n_rays, 4096):                       # tester.py:62 chunking (N_test = 4096)
-                orc.dm_nerf(rays[:, a:a + 4096], pc, pf, zc[a:a + 4096], perturb=0.0, n_importance=NIMP)
-            dt = time.perf_counter() - t0
-            best = dt if best is None else min(best, dt)
-    return n_rays / best, cores, best
-
-
-def cpu_oracle_train_rays_per_s(torch, n_rays: int):
-    """One training step of the oracle port on the host cores (forward, MSE + penalizer losses, backward)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import dmnerf_oracle as orc
-    torch.set_num_threads(os.cpu_count() or 1)
-    pc = {k: v.requires_grad_(True) for k, v in orc.init_params(K_INS, 1).items()}
-    pf = {k: v.requires_grad_(True) for k, v in orc.init_params(K_INS, 2).items()}
-    Kmat, c2w = synth_camera(torch, 0)
-    ro, rd = orc.get_rays_k(H, W, Kmat, c2w)
-    sel = torch.linspace(0, N_RAYS - 1, n_rays).long()
-    rays = torch.stack([ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel]], 0)
-    zc = orc.z_val_sample(n_rays, NEAR, FAR, SC)
-    tgt = torch.rand(n_rays, 3)
-    t0 = time.perf_counter()
-    o = orc.dm_nerf(rays, pc, pf, zc, perturb=1.0, n_importance=NIMP, t_rand=torch.rand(n_rays, SC),
-                    u=torch.rand(n_rays, NIMP))
-    loss = ((o["rgb_fine"] - tgt) ** 2).mean() + ((o["rgb_coarse"] - tgt) ** 2).mean()
-    loss = loss + orc.ins_penalizer(o["raw_coarse"], o["z_vals_coarse"], o["depth_coarse"], rays[1], 0.05, 0.05)
-    loss = loss + orc.ins_penalizer(o["raw_fine"], o["z_vals_fine"], o["depth_fine"], rays[1], 0.05, 0.05)
-    loss.backward()
-    dt = time.perf_counter() - t0
-    return n_rays / dt, dt
-
-
-def run_reference(args):
-    import torch
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    n = 8192
-    times = []
-    for i in range(args.warmup + args.steps):
-        rps, cores, dt = cpu_oracle_rays_per_s(torch, n)
-        if i >= args.warmup:
-            times.append(dt)
-    ms = 1000 * sum(times) / len(times)
-    val = n / (ms / 1000)
-    sample = f"{n} rays of the 640x480 frame per step (oracle port, torch CPU fp32, {cores} threads)"
-    emit({
-        "impl": "reference", "metric": "rays/sec render (64+128 samples/ray)", "value": val, "unit": "rays/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "DM-SR full-image render 640x480, 64+128 samples/ray, K=32 (bounded sample)"},
-        "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    })
-
-
-def train_leg(args, torch, dist, dev, rank, world):
-    """Training throughput (BASELINE.json configs[0] and configs[2]): full steps of dm_nerf_b200.train.TrainStep --
-    pixel draw, dm_nerf fwd, MSE + Hungarian instance loss + emptiness penalizer, backward, one all-reduce of the
-    flat gradient, Adam -- data-parallel over ray batches (each rank its own view and rays; weak scaling)."""
-    import numpy as np
-    import dmnerf_oracle as orc
-    from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
-    from dm_nerf_b200.train import TrainStep
-    pe, ve = get_embedder(10, 0)[0], get_embedder(4, 0)[0]
-    out = {}
-    for tag, n, k, near, far in (("C1_study_1024rays_K32", 1024, 32, 4.0, 15.0), ("C3_replica_4096rays_K93", 4096, 93, 0.0, 6.5)):
-        torch.manual_seed(3 + rank); np.random.seed(rank)
-        mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
-        mc.load_state_dict(orc.init_params(k, 1)); mf.load_state_dict(orc.init_params(k, 2))
-        mc, mf = mc.to(dev), mf.to(dev)
-        Kmat, c2w = synth_camera(torch, rank)
-        pose = c2w[:3, :4].to(dev)
-        img = torch.rand(H, W, 3, device=dev)
-        lab = ((torch.arange(H, device=dev)[:, None] // 60) * 8 + (torch.arange(W, device=dev)[None] // 80)) % k
-        targs = SimpleNamespace(N_train=n, near=near, far=far, N_samples=SC, N_importance=NIMP, perturb=1.0, ins_num=k,
-                                tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
-        # the whole step is one CUDA-graph replay (device-side Hungarian, no host round trip); inputs are copied
-        # into the graph's static buffers every step, as a real loop does with the image it drew
-        ts = TrainStep(pe, ve, mc, mf, Kmat, targs, penalize=True, graph=True)
-        for _ in range(max(3, args.warmup)):
-            ts.step(img, pose, lab)
-        steps = max(10, args.steps)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(steps):
-            losses = ts.step(img, pose, lab)
-        b.record()
-        torch.cuda.synchronize()
-        ms = torch.tensor([a.elapsed_time(b) / steps], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        ms = float(ms)
-        macs = 691840 + 128 * k
-        flop_per_ray = 2.0 * (3 * macs - 101248) * (SC + SC + NIMP)            # SURVEY 8(d): fwd + dgrad + wgrad
-        out[tag] = {"value": n * world / (ms / 1000), "unit": "rays/s", "ms_per_step": ms, "rays_per_step_per_gpu": n,
-                    "steps": steps, "loss": float(losses["total"]),
-                    "algorithmic_tflops": flop_per_ray * n * world / (ms / 1000) / 1e12}
-    return {"metric": "rays/sec train (64+128 samples/ray, fwd+bwd+Adam, penalizer on)", "scaling": "weak",
-            "step": "dm_nerf_b200.train.TrainStep(graph=True): one CUDA-graph replay per step",
-            "parallelism": f"data-parallel ray batches x{world}, one all-reduce of the flat gradient per step",
-            "configs": out}
-
-
-def run_gpu(args):
-    import torch
-    import torch.distributed as dist
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import dmnerf_oracle as orc
-    from dm_nerf_b200 import ops, _lib
-    from dm_nerf_b200.frame import render_pixels
-    from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
-    from dm_nerf_b200.parallel import gather_rows
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    mode = args.mode
-    if mode == "bf16" and _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) <= 0:
-        raise RuntimeError("bf16 tensor-core mode is not built")
-    ops.set_mode(mode)
-    mc, mf = DM_NeRF(8, 256, 63, 27, [4], K_INS), DM_NeRF(8, 256, 63, 27, [4], K_INS)
-    mc.load_state_dict(orc.init_params(K_INS, 1)); mf.load_state_dict(orc.init_params(K_INS, 2))
-    mc, mf = mc.to(dev), mf.to(dev)
-    pe, ve = get_embedder(10, 0)[0], get_embedder(4, 0)[0]
-    Kmat, c2w = synth_camera(torch, rank)                      # each rank renders its own view of the sweep
-    hwk = (H, W, Kmat)
-    ro, rd = ops.rays_k(H, W, Kmat, c2w, 0, N_RAYS, dev)
-    rays_dev = torch.stack([ro, rd], 0)
-    rays_host = rays_dev.cpu().pin_memory()
-    out = {"rgb": torch.empty((N_RAYS, 3), device=dev), "depth": torch.empty((N_RAYS,), device=dev),
-           "ins": torch.empty((N_RAYS, K_INS), device=dev), "labels": torch.empty((N_RAYS,), dtype=torch.uint8, device=dev)}
-    host_out = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in out.items() if k != "ins"}
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
-
-    def frame(rays):
-        render_pixels(pe, ve, mc, mf, hwk, c2w, NEAR, FAR, SC, NIMP, rays=rays, chunk=args.chunk, out=out)
-        if world > 1:
-            gather_rows(out["labels"], N_RAYS * world)          # the final gather (rank 0 collects label maps)
-
-    def sync():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        """max-over-ranks device time (ms) of `steps` calls, CUDA events on the launching stream."""
-        evs = []
-        sync()
-        for _ in range(steps):
-            flush.zero_()                                        # L2 flush between timed iterations
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(); fn(); b.record()
-            evs.append((a, b))
-        sync()
-        ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms) / steps
-
-    for _ in range(args.warmup):
-        frame(rays_dev)
-    sync()
-    sampler = ClockSampler(local)
-    sampler.start()
-    l0 = ops.launches
-    with ops.KernelTimer() as kt:
-        ms_step = timed(lambda: frame(rays_dev), args.steps)
-    launches = (ops.launches - l0)
-    totals = kt.totals()
-
-    def e2e_step():
-        r = rays_host.to(dev, non_blocking=True)
-        frame(r)
-        for k in host_out:
-            host_out[k].copy_(out[k], non_blocking=True)
-    e2e_step(); sync()
-    ms_e2e = timed(e2e_step, args.steps)
-    clocks = sampler.summary()
-    train = None
-    if not args.no_train:
-        train = train_leg(args, torch, dist, dev, rank, world)
-
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    mode_id = _lib.MODE_BF16 if mode == "bf16" else _lib.MODE_FP32
-    name = f"dmnerf_mlp_fwd[S={SC + NIMP},mode={mode_id}]"
-    n_launch, ms_kernel = totals.get(name, (0, 0.0))
-    rays_per_launch = min(args.chunk, N_RAYS)
-    roofline = None
-    if n_launch:
-        traffic = ncu_traffic_bytes() if (mode == "bf16" and rays_per_launch == 32768 and K_INS == 32) else None
-        # achieved = algorithmic FLOPs per launch / mean launch duration (fine pass: 192 points per ray)
-        flops_total = 2.0 * MACS_PER_POINT * (SC + NIMP) * N_RAYS * args.steps
-        achieved = flops_total / (ms_kernel / 1000) / 1e12
-        peak = peaks.get("bf16_tflops_sustained", 1400.0)
-        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                    "traffic": traffic, "traffic_source": "profiles/r01_render_kernels_metrics.csv (ncu --set full, "
-                    "dram__bytes_read.sum + dram__bytes_write.sum of the fine-pass launch)" if traffic else None,
-                    "kernel": name, "launches": n_launch, "ms_per_launch": ms_kernel / n_launch,
-                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback",
-                    "kernel_share_of_step": ms_kernel / (ms_step * args.steps)}
-    stage_ms = {k: round(v[1] / args.steps, 3) for k, v in totals.items()}
-    # the HBM-bound ray kernels of the same frame against the measured copy bandwidth (SURVEY 8d: algorithmic bytes per
-    # ray, K=32: compositing fine 29,340 / coarse 10,140; sampler 1,280 with in-kernel linspace uniforms)
-    hbm_peak = peaks.get("hbm_gbs", 6400.0)
-    secondary = []
-    for kname, bytes_per_ray in ((f"dmnerf_composite_fwd[S={SC + NIMP}]", 29340), (f"dmnerf_composite_fwd[S={SC}]", 10140),
-                                 ("dmnerf_fine_z", 1280)):
-        cnt, ms_k = totals.get(kname, (0, 0.0))
-        if cnt:
-            gbps = bytes_per_ray * N_RAYS * args.steps / (ms_k / 1000) / 1e9
-            secondary.append({"kernel": kname, "bound": "hbm" if "composite" in kname else "latency (CDF + searches per ray; HBM figure for scale)", "achieved": gbps, "peak": hbm_peak, "unit": "GB/s",
-                              "frac": gbps / hbm_peak, "ms_per_launch": ms_k / cnt})
-
-    if rank == 0:
-        cpu = None
-        try:
-            rps, cores, secs = cpu_oracle_rays_per_s(torch, CPU_SAMPLE_RAYS)
-            cpu = {"value": rps, "unit": "rays/s", "cores": cores, "kind": "port",
-                   "sample": f"{CPU_SAMPLE_RAYS} of the frame's 307200 rays in tester.py-style 4096-ray chunks, one pass "
-                             f"({secs:.1f} s), oracle port torch CPU fp32"}
-            if train is not None:
-                t_rps, t_secs = cpu_oracle_train_rays_per_s(torch, 1024)
-                train["cpu_baseline"] = {"value": t_rps, "unit": "rays/s", "cores": cores, "kind": "port",
-                                         "sample": f"one C1 step (1024 rays, K=32: dm_nerf + MSE + penalizer + backward, "
-                                                   f"{t_secs:.1f} s), oracle port torch CPU fp32"}
-        except Exception as e:  # pragma: no cover
-            cpu = {"value": None, "error": str(e)}
-        total_rays = N_RAYS * world
-        h2d = rays_host.numel() * 4
-        d2h = sum(v.numel() * v.element_size() for v in host_out.values())
-        emit({
-            "metric": "rays/sec render (64+128 samples/ray)", "value": total_rays / (ms_step / 1000), "unit": "rays/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16" if mode == "bf16" else "f32", "data": "synthetic",
-            "config": {"workload": "DM-SR full-image render 640x480 = 307200 rays x (64+128) samples, K=32, "
-                                   "rgb+depth+instance map+labels, one frame per rank per step",
-                       "mode": mode, "chunk_rays": args.chunk, "l2": "flushed between timed iterations (256 MiB write)",
-                       "parallelism": f"rays/views sharded x{world}, final gather of label maps"},
-            "e2e": {"value": total_rays / (ms_e2e / 1000), "unit": "rays/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
-            "gpu_launches": launches, "roofline": roofline, "roofline_secondary": secondary, "cpu_baseline": cpu, "clocks": clocks,
-            "stage_ms_per_step": stage_ms, "train": train,
-        })
-    if world > 1:
-        dist.destroy_process_group()
-
-
-def ncu_traffic_bytes():
-    """DRAM bytes per launch of the dominant kernel (fine-pass MLP forward, 32768 rays x 192 points, K=32) from the
-    committed ncu --set full capture of this same workload; None when the summary is absent."""
-    try:
-        rows = {}
-        with open(os.path.join(ROOT, "profiles", "r01_render_kernels_metrics.csv")) as f:
-            for line in f:
-                if line.startswith("#"):
-                    continue
-                parts = line.rstrip("\n").split(",")
-                rows[parts[0]] = parts[1:]
-        names, dur = rows["Kernel Name"][1:], [float(x) for x in rows["gpu__time_duration.sum"][1:]]
-        idx = max((i for i, nm in enumerate(names) if "mlp_fwd_bf16" in nm), key=lambda i: dur[i])
-        scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
-        total = 0.0
-        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-            total += float(rows[key][1:][idx]) * scale[rows[key][0]]
-        return total
-    except Exception:
-        return None
 
 
 _JSON_FD = None
@@ -395,10 +95,700 @@ def quiet_stdout():
 def emit(obj):
     line = (json.dumps(obj) + "\n").encode()
     sys.stdout.flush()
-    if _JSON_FD is None:
-        os.write(1, line)
-    else:
-        os.write(_JSON_FD, line)
+    os.write(1 if _JSON_FD is None else _JSON_FD, line)
+
+
+def log(*a):
+    print("[bench]", *a, file=sys.stderr, flush=True)
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+# =====================================================================================================================
+# CPU arm: the reference's own implementation of the path on the box's host cores.  The unmodified reference is read
+# from oracle/_ref (staged by oracle/make_ref.sh, travels to the GPU box); when it is absent the CPU restatement
+# (oracle/dmnerf_oracle.py) stands in and the line says kind = "port".  This is the ONLY place bench.py touches oracle/.
+# =====================================================================================================================
+class CpuArm:
+    def __init__(self, torch):
+        self.torch = torch
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        self.R = None
+        try:
+            import ref_loader
+            if ref_loader.reference_root() is not None:
+                self.R = ref_loader.load()
+        except Exception as e:                                   # pragma: no cover
+            log("reference not loadable, falling back to the port:", repr(e))
+        self.kind = "reference" if self.R is not None else "port"
+        if self.R is None:
+            import dmnerf_oracle
+            self.orc = dmnerf_oracle
+        from dm_nerf_b200 import synth                           # seeded inputs (pure torch-CPU helpers)
+        self.synth = synth
+
+    def describe(self):
+        return ("unmodified reference (oracle/_ref: networks/render.py dm_nerf, torch CPU fp32)" if self.R is not None
+                else "oracle port (oracle/dmnerf_oracle.py, torch CPU fp32)")
+
+    def embedders(self):
+        return self.R.model.get_embedder(10, 0)[0], self.R.model.get_embedder(4, 0)[0]
+
+    def models(self, k, requires_grad=False):
+        sd_c, sd_f = self.synth.init_state_dict(k, 1), self.synth.init_state_dict(k, 2)
+        if self.R is None:
+            if requires_grad:
+                sd_c = {n: v.requires_grad_(True) for n, v in sd_c.items()}
+                sd_f = {n: v.requires_grad_(True) for n, v in sd_f.items()}
+            return sd_c, sd_f
+        mc, mf = self.R.model.DM_NeRF(8, 256, 63, 27, [4], k), self.R.model.DM_NeRF(8, 256, 63, 27, [4], k)
+        mc.load_state_dict(sd_c); mf.load_state_dict(sd_f)
+        for m in (mc, mf):
+            m.train(requires_grad)
+            for p in m.parameters():
+                p.requires_grad_(requires_grad)
+        return mc, mf
+
+    def sample_rays(self, n_rays, view=0):
+        torch = self.torch
+        Kmat, c2w = self.synth.dmsr_camera(H, W, view)
+        get = self.R.helpers.get_rays_k if self.R is not None else self.orc.get_rays_k
+        ro, rd = get(H, W, Kmat, c2w)
+        sel = torch.linspace(0, N_RAYS - 1, n_rays).long()
+        return torch.stack([ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel]], 0).float()
+
+    def render(self, n_rays, repeats=1):
+        """tester.py:54-76 on ``n_rays`` of the frame: N_test = 4096 chunks of dm_nerf, perturb = 0.  -> (rays/s, s)"""
+        torch = self.torch
+        mc, mf = self.models(K_INS)
+        rays = self.sample_rays(n_rays)
+        best = None
+        with torch.no_grad():
+            if self.R is not None:
+                pe, ve = self.embedders()
+                args = SimpleNamespace(perturb=0.0, N_importance=NIMP, is_train=False, N_ins=None)
+            for _ in range(repeats):
+                t0 = time.perf_counter()
+                for a in range(0, n_rays, 4096):
+                    b = min(n_rays, a + 4096)
+                    if self.R is not None:
+                        zc = self.R.helpers.z_val_sample(b - a, NEAR, FAR, SC)
+                        self.R.render.dm_nerf(rays[:, a:b], pe, ve, mc, mf, zc, args)
+                    else:
+                        zc = self.orc.z_val_sample(b - a, NEAR, FAR, SC)
+                        self.orc.dm_nerf(rays[:, a:b], mc, mf, zc, perturb=0.0, n_importance=NIMP)
+                dt = time.perf_counter() - t0
+                best = dt if best is None else min(best, dt)
+        return n_rays / best, best
+
+    def train(self, n_rays, timed=2):
+        """train_dmsr.py:30-66 on the host: dm_nerf (perturb = 1) + MSE + Hungarian instance loss + emptiness penalizer,
+        backward, Adam.  One untimed warm-up step, then ``timed`` steps.  -> (rays/s, s/step, s/step with the
+        reference's autograd anomaly detection left on -- dm_nerf.py:5 -- or None for the port)"""
+        torch = self.torch
+        if self.R is None:
+            pc, pf = self.models(K_INS, requires_grad=True)
+            params = list(pc.values()) + list(pf.values())
+        else:
+            mc, mf = self.models(K_INS, requires_grad=True)
+            params = list(mc.parameters()) + list(mf.parameters())
+            pe, ve = self.embedders()
+        opt = torch.optim.Adam(params, lr=5e-4, betas=(0.9, 0.999))
+        rays = self.sample_rays(n_rays)
+        g = torch.Generator().manual_seed(0)
+        tgt = torch.rand(n_rays, 3, generator=g)
+        lab = (torch.arange(n_rays) * 8 // n_rays) % K_INS
+        args = SimpleNamespace(perturb=1.0, N_importance=NIMP, is_train=True, N_ins=None, tolerance=0.05, deta_w=0.05)
+
+        def step():
+            if self.R is not None:
+                R = self.R
+                zc = R.helpers.z_val_sample(n_rays, NEAR, FAR, SC)
+                o = R.render.dm_nerf(rays, pe, ve, mc, mf, zc, args)
+                loss = R.evaluator.img2mse(o["rgb_fine"], tgt) + R.evaluator.img2mse(o["rgb_coarse"], tgt)
+                loss = loss + R.evaluator.ins_criterion(o["ins_coarse"], lab, K_INS)[0] \
+                    + R.evaluator.ins_criterion(o["ins_fine"], lab, K_INS)[0]
+                loss = loss + R.pen.ins_penalizer(o["raw_coarse"], o["z_vals_coarse"], o["depth_coarse"], rays[1], args)
+                loss = loss + R.pen.ins_penalizer(o["raw_fine"], o["z_vals_fine"], o["depth_fine"], rays[1], args)
+            else:
+                orc = self.orc
+                zc = orc.z_val_sample(n_rays, NEAR, FAR, SC)
+                o = orc.dm_nerf(rays, pc, pf, zc, perturb=1.0, n_importance=NIMP, t_rand=torch.rand(n_rays, SC),
+                                u=torch.rand(n_rays, NIMP))
+                loss = ((o["rgb_fine"] - tgt) ** 2).mean() + ((o["rgb_coarse"] - tgt) ** 2).mean()
+                loss = loss + orc.ins_penalizer(o["raw_coarse"], o["z_vals_coarse"], o["depth_coarse"], rays[1], 0.05, 0.05)
+                loss = loss + orc.ins_penalizer(o["raw_fine"], o["z_vals_fine"], o["depth_fine"], rays[1], 0.05, 0.05)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+
+        step()
+        t0 = time.perf_counter()
+        for _ in range(timed):
+            step()
+        dt = (time.perf_counter() - t0) / timed
+        dt_anomaly = None
+        if self.R is not None:
+            torch.autograd.set_detect_anomaly(True)
+            try:
+                t0 = time.perf_counter(); step(); dt_anomaly = time.perf_counter() - t0
+            finally:
+                torch.autograd.set_detect_anomaly(False)
+        return n_rays / dt, dt, dt_anomaly
+
+    def manipulate(self, n_rays):
+        """One N_test-style chunk of ``manipulator`` (manipulator.py:137-205), T = 1.  -> (rays/s, s)"""
+        torch = self.torch
+        mc, mf = self.models(K_INS)
+        ori, tar = self.sample_rays(n_rays, 0), self.sample_rays(n_rays, 1)
+        args = SimpleNamespace(N_samples=SC, N_importance=NIMP, near=NEAR, far=FAR, target_label=[8])
+        with torch.no_grad():
+            t0 = time.perf_counter()
+            if self.R is not None:
+                pe, ve = self.embedders()
+                self.R.mani.manipulator(pe, ve, mc, mf, ori, tar[None], args)
+            else:
+                self.orc.manipulator(mc, mf, ori, tar[None], n_samples=SC, n_importance=NIMP, near=NEAR, far=FAR,
+                                     target_label=[8])
+            dt = time.perf_counter() - t0
+        return n_rays / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation, all host threads, on the arm's metric and config;
+    each step a bounded sample (REF_STEP_RAYS rays of the frame).  Under torchrun rank 0 alone runs it."""
+    import torch
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cpu = CpuArm(torch)
+    times = []
+    for i in range(args.warmup + args.steps):
+        _, dt = cpu.render(REF_STEP_RAYS)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1000 * sum(times) / len(times)
+    val = REF_STEP_RAYS / (ms / 1000)
+    sample = (f"{REF_STEP_RAYS} rays of the 640x480 frame per step in tester.py-style 4096-ray chunks "
+              f"({cpu.describe()}, {cpu.cores} threads); rays/s is size-independent (rays are independent units)")
+    emit({
+        "impl": "reference", "metric": "rays/sec render (64+128 samples/ray)", "value": val, "unit": "rays/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "rays_per_step": REF_STEP_RAYS,
+        "config": {"workload": "DM-SR full-image render 640x480 = 307200 rays x (64+128) samples, K=32, rgb+depth+instance "
+                               "map+labels, one frame per step",
+                   "sample": f"bounded: {REF_STEP_RAYS} of the frame's 307200 rays per step"},
+        "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cpu.cores, "kind": cpu.kind, "sample": sample},
+        "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    })
+
+
+# =====================================================================================================================
+# GPU arm
+# =====================================================================================================================
+class Ctx:
+    """torch / torch.distributed handles + this rank's place in the job."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args = torch, dist, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)       # > 126 MB L2
+
+    def sync(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def timed(self, fn, steps, flush=True):
+        """ms per call of ``fn``: CUDA events on the launching stream around every call, barrier + synchronize on both
+        sides of the region, L2 flushed (256 MiB write) before every call, MAX over ranks of the per-rank sums."""
+        torch = self.torch
+        evs = []
+        self.sync()
+        for _ in range(steps):
+            if flush:
+                self.flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            evs.append((a, b))
+        self.sync()
+        ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], device=self.dev, dtype=torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(ms, op=self.dist.ReduceOp.MAX)
+        return float(ms) / steps
+
+    def sum_int(self, v: int) -> int:
+        if self.world == 1:
+            return int(v)
+        t = self.torch.tensor([int(v)], device=self.dev, dtype=self.torch.int64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return int(t)
+
+
+def make_models(torch, k, dev, gain=1.0):
+    from dm_nerf_b200 import synth
+    from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
+    mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
+    mc.load_state_dict(synth.init_state_dict(k, 1, gain)); mf.load_state_dict(synth.init_state_dict(k, 2, gain))
+    return get_embedder(10, 0)[0], get_embedder(4, 0)[0], mc.to(dev), mf.to(dev)
+
+
+class FrameJob:
+    """ONE frame, its pixel rows sharded over the ranks, gathered onto rank 0 (parallel.render_sharded's scheme with
+    preallocated buffers): the strong-scaling unit of configs[1] (C2) and configs[3] (C4)."""
+
+    KEYS = ("rgb", "depth", "ins", "labels")
+
+    def __init__(self, cx: Ctx, models, Hh, Ww, k, near, far, camera, chunk):
+        from dm_nerf_b200.parallel import shard_range
+        torch = cx.torch
+        self.cx, self.models, self.hw, self.k, self.near, self.far, self.chunk = cx, models, (Hh, Ww), k, near, far, chunk
+        self.Kmat, self.c2w = camera
+        self.total = Hh * Ww
+        self.a, self.b = shard_range(self.total, cx.rank, cx.world)
+        n = self.total if cx.rank == 0 else self.b - self.a
+        dev = cx.dev
+        bufs = {"rgb": torch.empty((n, 3), device=dev), "depth": torch.empty((n,), device=dev),
+                "ins": torch.empty((n, k), device=dev), "labels": torch.empty((n,), dtype=torch.uint8, device=dev)}
+        self.frame = bufs if cx.rank == 0 else None
+        self.local = {kk: v[self.a:self.b] for kk, v in bufs.items()} if cx.rank == 0 else bufs
+        self.host_rays = self.host_out = None
+
+    def step(self, rays=None):
+        from dm_nerf_b200.frame import render_pixels
+        from dm_nerf_b200.parallel import gather_frame
+        pe, ve, mc, mf = self.models
+        render_pixels(pe, ve, mc, mf, (self.hw[0], self.hw[1], self.Kmat), self.c2w, self.near, self.far, SC, NIMP,
+                      pix0=self.a, count=self.b - self.a, chunk=self.chunk, rays=rays, out=self.local)
+        gather_frame(self.local, self.frame, self.total, self.KEYS)
+
+    def prepare_host(self):
+        """Pinned host buffers of the end-to-end path: this rank's rays in, the frame out (rank 0)."""
+        from dm_nerf_b200 import ops
+        torch = self.cx.torch
+        ro, rd = ops.rays_k(self.hw[0], self.hw[1], self.Kmat, self.c2w, self.a, self.b - self.a, self.cx.dev)
+        self.host_rays = torch.stack([ro, rd], 0).cpu().pin_memory()
+        if self.cx.rank == 0:
+            self.host_out = {kk: torch.empty(v.shape, dtype=v.dtype).pin_memory() for kk, v in self.frame.items()}
+
+    def step_e2e(self):
+        r = self.host_rays.to(self.cx.dev, non_blocking=True)
+        self.step(rays=r)
+        if self.cx.rank == 0:
+            for kk, v in self.host_out.items():
+                v.copy_(self.frame[kk], non_blocking=True)
+
+    def io_bytes(self):
+        h2d = self.total * 2 * 3 * 4
+        d2h = self.total * (3 * 4 + 4 + self.k * 4 + 1)
+        return h2d, d2h
+
+
+def ncu_traffic_bytes():
+    """DRAM bytes per launch of the dominant kernel (fine-pass MLP forward, K=32) from the committed ncu --set full
+    capture of this workload (newest round first); (bytes, rays in that launch, file) or None."""
+    for fname, rays in (("r02_render_kernels_metrics.csv", 30720), ("r01_render_kernels_metrics.csv", 32768)):
+        try:
+            rows = {}
+            with open(os.path.join(ROOT, "profiles", fname)) as f:
+                for line in f:
+                    if line.startswith("#"):
+                        continue
+                    parts = line.rstrip("\n").split(",")
+                    rows[parts[0]] = parts[1:]
+            names, dur = rows["Kernel Name"][1:], [float(x) for x in rows["gpu__time_duration.sum"][1:]]
+            idx = max((i for i, nm in enumerate(names) if "mlp_fwd_bf16" in nm), key=lambda i: dur[i])
+            scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+            total = 0.0
+            for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                total += float(rows[key][1:][idx]) * scale[rows[key][0]]
+            return total, rays, "profiles/" + fname
+        except Exception:
+            continue
+    return None
+
+
+def snapshot(frame):
+    return {k: v.clone() for k, v in frame.items()}
+
+
+def frame_parity(torch, ref, got, gt_noise_seed=0):
+    """``got`` (tensor-core mode) against ``ref`` (fp32 parity mode), both whole frames on the device: north_star's
+    bf16 clause (PSNR within 0.05 dB, label agreement >= 99.9 %) evaluated on the frame the bench times."""
+    gen = torch.Generator(device="cpu").manual_seed(gt_noise_seed)
+    noise = (0.03 * torch.randn(ref["rgb"].shape, generator=gen)).to(ref["rgb"].device)
+    gt = (ref["rgb"] + noise).clamp(0, 1)                        # a ~30 dB "ground truth" around the fp32 render
+    psnr = lambda x: -10.0 * math.log10(float(((x - gt) ** 2).mean()))
+    lab_ref, lab_got = ref["ins"].argmax(-1), got["ins"].argmax(-1)
+    top2 = torch.topk(ref["ins"], 2, dim=-1).values
+    margin = top2[:, 0] - top2[:, 1]
+    agree = (lab_ref == lab_got)
+    out = {"psnr_fp32_db": psnr(ref["rgb"]), "psnr_delta_db": psnr(got["rgb"]) - psnr(ref["rgb"]),
+           "psnr_between_modes_db": -10.0 * math.log10(max(float(((got["rgb"] - ref["rgb"]) ** 2).mean()), 1e-20)),
+           "label_agreement": float(agree.float().mean()),
+           "max_abs_rgb": float((got["rgb"] - ref["rgb"]).abs().max()),
+           "max_abs_depth": float((got["depth"] - ref["depth"]).abs().max()),
+           "mean_abs_depth": float((got["depth"] - ref["depth"]).abs().mean()),
+           "max_abs_ins": float((got["ins"] - ref["ins"]).abs().max()),
+           "median_top2_margin": float(margin.median()), "pixels": int(agree.numel())}
+    for thr in (1e-4, 1e-3, 1e-2):
+        sure = margin > thr
+        out[f"label_agreement_margin_{thr:g}"] = float(agree[sure].float().mean()) if int(sure.sum()) else None
+        out[f"pixels_margin_{thr:g}"] = float(sure.float().mean())
+    return out
+
+
+def train_models(cx: Ctx, k, n_rays, steps, near, far, Hh, Ww, camera, gain=1.0, penalize=True, image=None, labels=None):
+    """``steps`` optimisation steps of dm_nerf_b200.train.TrainStep (one CUDA-graph replay each) on one synthetic view;
+    returns (models, TrainStep, image, labels, pose)."""
+    from dm_nerf_b200 import synth
+    from dm_nerf_b200.train import TrainStep
+    torch = cx.torch
+    pe, ve, mc, mf = make_models(torch, k, cx.dev, gain)
+    Kmat, c2w = camera
+    pose = c2w[:3, :4].to(cx.dev)
+    if image is None:
+        image = torch.rand(Hh, Ww, 3, device=cx.dev)
+    if labels is None:
+        labels = synth.block_labels(Hh, Ww, k, device=cx.dev)
+    targs = SimpleNamespace(N_train=n_rays, near=near, far=far, N_samples=SC, N_importance=NIMP, perturb=1.0, ins_num=k,
+                            tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+    ts = TrainStep(pe, ve, mc, mf, Kmat, targs, penalize=penalize, graph=True)
+    for _ in range(steps):
+        ts.step(image, pose, labels)
+    return (pe, ve, mc, mf), ts, image, labels, pose
+
+
+def train_leg(cx: Ctx):
+    """Training throughput (configs[0] C1 and configs[2] C3): full steps of dm_nerf_b200.train.TrainStep -- pixel draw,
+    dm_nerf fwd, MSE + Hungarian instance loss + emptiness penalizer, backward, all-reduce of the flat gradient, Adam --
+    data-parallel over ray batches (each rank its own view and rays: weak scaling by construction)."""
+    import numpy as np
+    from dm_nerf_b200 import synth
+    torch, args = cx.torch, cx.args
+    out = {}
+    for tag, n, k, near, far in (("C1_study_1024rays_K32", 1024, 32, 4.0, 15.0), ("C3_replica_4096rays_K93", 4096, 93, 0.0, 6.5)):
+        torch.manual_seed(3 + cx.rank); np.random.seed(cx.rank)
+        _, ts, img, lab, pose = train_models(cx, k, n, max(3, args.warmup), near, far, H, W, synth.dmsr_camera(H, W, cx.rank))
+        steps = max(10, args.steps)
+        losses = {}
+        cx.sync()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            losses = ts.step(img, pose, lab)
+        b.record()
+        cx.sync()
+        ms = torch.tensor([a.elapsed_time(b) / steps], device=cx.dev, dtype=torch.float64)
+        if cx.world > 1:
+            cx.dist.all_reduce(ms, op=cx.dist.ReduceOp.MAX)
+        ms = float(ms)
+        fl = 2.0 * (3 * macs_per_point(k) - 101248) * (SC + SC + NIMP)          # SURVEY 8(d): fwd + dgrad + wgrad
+        out[tag] = {"value": n * cx.world / (ms / 1000), "unit": "rays/s", "ms_per_step": ms, "rays_per_step_per_gpu": n,
+                    "steps": steps, "loss": float(losses["total"]),
+                    "algorithmic_tflops": fl * n * cx.world / (ms / 1000) / 1e12}
+        del ts
+    return {"metric": "rays/sec train (64+128 samples/ray, fwd+bwd+Adam, penalizer on)", "scaling": "weak",
+            "step": "dm_nerf_b200.train.TrainStep(graph=True): one CUDA-graph replay per step",
+            "parallelism": f"data-parallel ray batches x{cx.world}, one all-reduce of each model's flat gradient per step",
+            "configs": out}
+
+
+def c5_leg(cx: Ctx, models, cpu_arm):
+    """configs[4] mani_demo: one edited view (480x640, K=32, T=1, target_label=[8], rotation about the 'study' object
+    centre, tools/pose_generator.py:137-145) through frame.manipulate_pixels; with N ranks each rank renders its own
+    view of the sweep (views shard, weak scaling; 360 views = 360/N steps)."""
+    from dm_nerf_b200 import ops, synth
+    from dm_nerf_b200.frame import manipulate_pixels
+    import numpy as np
+    torch = cx.torch
+    pe, ve, mc, mf = models
+    Kmat, pose = synth.dmsr_camera(H, W, cx.rank)
+    centre = np.array([-0.519422, -2.16509, 1.07392], dtype=np.float32)
+    yaw = (180.0 * (cx.rank + 1) / max(cx.world, 8)) * math.pi / 180.0
+    t_in, t_out, rot = np.eye(4, dtype=np.float32), np.eye(4, dtype=np.float32), np.eye(4, dtype=np.float32)
+    t_in[:3, 3], t_out[:3, 3] = -centre, centre
+    rot[:2, :2] = [[math.cos(yaw), -math.sin(yaw)], [math.sin(yaw), math.cos(yaw)]]
+    targets = [{"tar_id": 8, "transformation": torch.from_numpy(t_out @ rot @ t_in)}]
+    margs = SimpleNamespace(N_samples=SC, N_importance=NIMP, near=NEAR, far=FAR)
+    bufs = {"rgb": torch.empty((N_RAYS, 3), device=cx.dev), "ins": torch.empty((N_RAYS, K_INS + 1), device=cx.dev),
+            "tar_rgb": torch.empty((N_RAYS, 3), device=cx.dev), "tar_ins": torch.empty((N_RAYS, K_INS + 1), device=cx.dev),
+            "labels": torch.empty((N_RAYS,), dtype=torch.uint8, device=cx.dev)}
+    host = {k: torch.empty(bufs[k].shape, dtype=bufs[k].dtype).pin_memory() for k in ("rgb", "labels")}
+
+    def view():
+        manipulate_pixels(pe, ve, mc, mf, (H, W, Kmat), pose, targets, margs, chunk=16384, out=bufs)
+        for k, v in host.items():
+            v.copy_(bufs[k], non_blocking=True)                   # what the demo writes out (manipulator.py:475-486)
+    torch.manual_seed(7 + cx.rank)
+    view()
+    steps = 2
+    l0 = ops.launches
+    with ops.KernelTimer() as kt:
+        ms = cx.timed(view, steps)
+    totals = kt.totals()
+    launches = cx.sum_int(ops.launches - l0)
+    out = None
+    if cx.rank == 0:
+        peaks = load_peaks()
+        c = K_INS + 5
+        ex_bytes = lambda s: 2 * s * c * 4 + 2 * (K_INS + 1) * 4 + s * c * 4 + s * 16      # SURVEY 8(d) + two int64 label maps
+        ex_ms = sum(v[1] for k, v in totals.items() if k.startswith("dmnerf_exchange"))
+        ex_n = sum(v[0] for k, v in totals.items() if k.startswith("dmnerf_exchange"))
+        ex_s = sorted({int(k.split("S=")[1].rstrip("]")) for k in totals if k.startswith("dmnerf_exchange")})
+        gbps = sum(ex_bytes(s) for s in ex_s) * N_RAYS * steps / (ex_ms / 1000) / 1e9 if ex_ms else None
+        mlp_ms = sum(v[1] for k, v in totals.items() if k.startswith("dmnerf_mlp_fwd"))
+        pts = SC + (SC + NIMP) + SC + (SC + NIMP) + 2 * (SC + 2 * NIMP)                      # 1152 MLP points per ray at T=1
+        out = {"workload": "mani_demo view 480x640, K=32, T=1 (1152 MLP points/ray, 9 compositing passes, 2 exchanges), "
+                           "one view per rank per step, rgb + uint8 label image copied to the host",
+               "value": N_RAYS * cx.world / (ms / 1000), "unit": "rays/s", "ms_per_view": ms, "views_per_step": cx.world,
+               "scaling": "weak (views shard)", "sweep_360_views_s": 360.0 / cx.world * ms / 1000, "gpu_launches": launches,
+               "algorithmic_tflops": flop_per_ray(K_INS, pts) * N_RAYS * cx.world / (ms / 1000) / 1e12,
+               "mlp_share_of_view": mlp_ms / (ms * steps),
+               "roofline_exchange": None if not ex_ms else {
+                   "bound": "hbm", "achieved": gbps, "peak": peaks.get("hbm_gbs", 6400.0), "unit": "GB/s",
+                   "frac": gbps / peaks.get("hbm_gbs", 6400.0), "ms_per_launch": ex_ms / ex_n, "launches": ex_n,
+                   "bytes_per_ray": {f"S={s}": ex_bytes(s) for s in ex_s}},
+               "stage_ms_per_view": {k: round(v[1] / steps, 3) for k, v in totals.items()}}
+        if cpu_arm is not None:
+            try:
+                n_cpu = 1024
+                rps, secs = cpu_arm.manipulate(n_cpu)
+                out["cpu_baseline"] = {"value": rps, "unit": "rays/s", "cores": cpu_arm.cores, "kind": cpu_arm.kind,
+                                       "sample": f"one {n_cpu}-ray chunk of manipulator (T=1), {secs:.1f} s, {cpu_arm.describe()}"}
+            except Exception as e:                                  # pragma: no cover
+                out["cpu_baseline"] = {"value": None, "error": repr(e)}
+    return out
+
+
+def trained_parity(cx: Ctx, job: FrameJob, steps: int):
+    """bf16 tensor mode vs fp32 parity mode on the 640x480 frame of a field trained for ``steps`` steps (1024 rays each,
+    data-parallel over the ranks, so every rank ends with the same weights) on that view."""
+    from dm_nerf_b200 import ops, synth
+    torch = cx.torch
+    lab = synth.block_labels(H, W, K_INS, device=cx.dev)
+    palette = torch.rand(K_INS, 3, generator=torch.Generator().manual_seed(4)).to(cx.dev)
+    yy = torch.linspace(0, 1, H, device=cx.dev)[:, None, None]
+    image = (0.8 * palette[lab] + 0.2 * yy).clamp(0, 1)
+    torch.manual_seed(5 + cx.rank)
+    t0 = time.perf_counter()
+    models, ts, _, _, _ = train_models(cx, K_INS, 1024, steps, NEAR, FAR, H, W, (job.Kmat, job.c2w), image=image, labels=lab)
+    last = ts.step(image, job.c2w[:3, :4].to(cx.dev), lab)
+    cx.sync()
+    train_s = time.perf_counter() - t0
+    del ts
+    tjob = FrameJob(cx, models, H, W, K_INS, NEAR, FAR, (job.Kmat, job.c2w), job.chunk)
+    out = None
+    try:
+        ops.set_mode("bf16"); tjob.step(); cx.sync()
+        got = snapshot(tjob.frame) if cx.rank == 0 else None
+        ops.set_mode("fp32"); tjob.step(); cx.sync()
+        if cx.rank == 0:
+            out = frame_parity(torch, tjob.frame, got)
+            gt_lab = lab.reshape(-1)
+            out.update({"weights": f"trained {steps + 1} steps x 1024 rays x {cx.world} ranks on this view (bf16 mode, TrainStep graph)",
+                        "train_seconds": train_s, "final_loss": {k: float(v) for k, v in last.items()},
+                        "label_accuracy_vs_gt_fp32": float((tjob.frame["ins"].argmax(-1) == gt_lab).float().mean()),
+                        "rgb_psnr_vs_gt_fp32_db": -10.0 * math.log10(float(((tjob.frame["rgb"] - image.reshape(-1, 3)) ** 2).mean()))})
+    finally:
+        ops.set_mode(cx.args.mode)
+    return out
+
+
+def run_gpu(args):
+    cx = Ctx(args)
+    torch = cx.torch
+    from dm_nerf_b200 import ops, _lib, synth
+    from dm_nerf_b200.frame import render_pixels
+    mode = args.mode
+    if mode == "bf16" and _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) <= 0:
+        raise RuntimeError("bf16 tensor-core mode is not built")
+    ops.set_mode(mode)
+    mode_id = _lib.MODE_BF16 if mode == "bf16" else _lib.MODE_FP32
+    models = make_models(torch, K_INS, cx.dev)
+    job = FrameJob(cx, models, H, W, K_INS, NEAR, FAR, synth.dmsr_camera(H, W, 0), args.chunk)
+
+    # ---- headline: one frame, rows sharded over the ranks, gathered on rank 0 --------------------------------------
+    for _ in range(args.warmup):
+        job.step()
+    cx.sync()
+    sampler = ClockSampler(cx.local)
+    sampler.start()
+    l0 = ops.launches
+    with ops.KernelTimer() as kt:
+        ms_step = cx.timed(job.step, args.steps)
+    launches = cx.sum_int(ops.launches - l0)
+    totals = kt.totals()
+    job.prepare_host()
+    job.step_e2e(); cx.sync()
+    ms_e2e = cx.timed(job.step_e2e, args.steps)
+    clocks = sampler.summary()
+    frame_tc = snapshot(job.frame) if cx.rank == 0 else None
+    log(f"headline {ms_step:.2f} ms/frame, e2e {ms_e2e:.2f} ms")
+
+    # ---- the same frame in the fp32 parity mode (CUDA-core FFMA): its cost, and the parity of the headline mode --------
+    fp32_leg = parity = None
+    if mode == "bf16" and not args.no_parity:
+        ops.set_mode("fp32")
+        try:
+            ms_fp32 = cx.timed(job.step, 1)
+            if cx.rank == 0:
+                frame_ref = snapshot(job.frame)
+                fp32_leg = {"kernel": "mlp_fwd_fp32_kernel (CUDA cores, <=1e-4 parity mode)", "ms_per_frame": ms_fp32,
+                            "value": N_RAYS / (ms_fp32 / 1000), "unit": "rays/s",
+                            "algorithmic_tflops": flop_per_ray(K_INS) * N_RAYS / (ms_fp32 / 1000) / 1e12}
+                parity = frame_parity(torch, frame_ref, frame_tc)
+                parity["weights"] = "random-init (the benchmarked frame)"
+                del frame_ref
+        finally:
+            ops.set_mode(mode)
+        log("fp32 frame + parity done")
+
+    # ---- weak figure: one whole frame per rank (a sweep's views shard trivially), no gather ---------------------------
+    weak = None
+    if cx.world > 1 and not args.no_extra:
+        solo_k, solo_pose = synth.dmsr_camera(H, W, cx.rank)
+        solo_out = {"rgb": torch.empty((N_RAYS, 3), device=cx.dev), "depth": torch.empty((N_RAYS,), device=cx.dev),
+                    "ins": torch.empty((N_RAYS, K_INS), device=cx.dev),
+                    "labels": torch.empty((N_RAYS,), dtype=torch.uint8, device=cx.dev)}
+
+        def solo_step():
+            pe, ve, mc, mf = models
+            render_pixels(pe, ve, mc, mf, (H, W, solo_k), solo_pose, NEAR, FAR, SC, NIMP, chunk=args.chunk, out=solo_out)
+        solo_step()
+        ms_weak = cx.timed(solo_step, max(2, min(args.steps, 5)))
+        weak = {"value": N_RAYS * cx.world / (ms_weak / 1000), "unit": "rays/s", "ms_per_step": ms_weak,
+                "workload": "one whole 640x480 frame per rank per step (views of a sweep), no gather"}
+        del solo_out
+
+    # ---- C4: ScanNet-shaped 1296x968 frame, K=16, rows sharded, gathered (rgb + depth + 16-channel map + labels) --------
+    c4 = None
+    if not args.no_extra:
+        m4 = make_models(torch, C4["K"], cx.dev)
+        job4 = FrameJob(cx, m4, C4["H"], C4["W"], C4["K"], C4["near"], C4["far"], synth.scannet_camera(), args.chunk)
+        job4.step()
+        ms4 = cx.timed(job4.step, max(2, min(args.steps, 3)))
+        n4 = C4["H"] * C4["W"]
+        c4 = {"workload": "ScanNet-shaped 1296x968 = 1254528 rays x (64+128) samples, K=16, one frame, rows sharded over the "
+                          "ranks, rgb+depth+16-channel instance map+labels gathered on rank 0",
+              "value": n4 / (ms4 / 1000), "unit": "rays/s", "ms_per_frame": ms4, "scaling": "strong",
+              "gather_bytes": n4 * (12 + 4 + 4 * C4["K"] + 1) * (cx.world - 1) // cx.world,
+              "algorithmic_tflops": flop_per_ray(C4["K"]) * n4 / (ms4 / 1000) / 1e12}
+        del job4, m4
+        log("c4 done")
+
+    train = None
+    if not args.no_train:
+        train = train_leg(cx)
+        log("train leg done")
+
+    # ---- parity of the tensor-core mode on a TRAINED-like field: optimisation steps on one synthetic view (smooth
+    # colour blocks + 32 block labels) make the instance head confident, as a converged model's is ---------------------
+    parity_trained = None
+    if mode == "bf16" and not args.no_parity and args.parity_train_steps > 0:
+        parity_trained = trained_parity(cx, job, args.parity_train_steps)
+        log("trained parity done")
+
+    cpu_arm = CpuArm(torch) if cx.rank == 0 and not args.no_cpu else None
+    c5 = None
+    if not args.no_extra:
+        ops.set_mode(mode)
+        c5 = c5_leg(cx, models, cpu_arm)
+        log("c5 done")
+
+    if cx.rank == 0:
+        emit(headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm,
+                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, weak=weak, c4=c4, c5=c5, train=train)))
+    if cx.world > 1:
+        cx.dist.destroy_process_group()
+
+
+def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, legs):
+    args = cx.args
+    peaks = load_peaks()
+    steps = args.steps
+    rays_rank0 = job.b - job.a                               # rank 0's share: KernelTimer ran on rank 0's launches
+    name = f"dmnerf_mlp_fwd[S={SC + NIMP},mode={mode_id}]"
+    n_launch, ms_kernel = totals.get(name, (0, 0.0))
+    roofline = None
+    if n_launch:
+        flops_total = 2.0 * macs_per_point(K_INS) * (SC + NIMP) * rays_rank0 * steps
+        achieved = flops_total / (ms_kernel / 1000) / 1e12
+        peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        tr = ncu_traffic_bytes() if mode == "bf16" else None
+        rays_per_launch = rays_rank0 * steps / n_launch
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": tr[0] if tr else None,
+                    "traffic_source": (f"{tr[2]} (ncu --set full: dram__bytes_read.sum + dram__bytes_write.sum of a fine-pass "
+                                       f"launch of {tr[1]} rays)") if tr else None,
+                    "kernel": name, "launches": n_launch, "ms_per_launch": ms_kernel / n_launch,
+                    "rays_per_launch": rays_per_launch,
+                    "algorithmic_flop_per_launch": 2.0 * macs_per_point(K_INS) * (SC + NIMP) * rays_per_launch,
+                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (B200_PROFILING.md)",
+                    "frac_of_burst_peak": achieved / peaks.get("bf16_tflops", 1650.0),
+                    "kernel_share_of_step": ms_kernel / (ms_step * steps), "measured_on": "rank 0's launches"}
+    hbm_peak = peaks.get("hbm_gbs", 6400.0)
+    secondary = []
+    for kname, bytes_per_ray in ((f"dmnerf_composite_fwd[S={SC + NIMP}]", 29340), (f"dmnerf_composite_fwd[S={SC}]", 10140),
+                                 ("dmnerf_fine_z", 1280)):
+        cnt, ms_k = totals.get(kname, (0, 0.0))
+        if cnt:
+            gbps = bytes_per_ray * rays_rank0 * steps / (ms_k / 1000) / 1e9
+            secondary.append({"kernel": kname, "bound": "hbm" if "composite" in kname else
+                              "latency (CDF + searches per ray; HBM figure for scale)", "achieved": gbps, "peak": hbm_peak,
+                              "unit": "GB/s", "frac": gbps / hbm_peak, "ms_per_launch": ms_k / cnt})
+    cpu = None
+    train = legs.get("train")
+    if cpu_arm is not None:
+        try:
+            rps, secs = cpu_arm.render(CPU_SAMPLE_RAYS)
+            cpu = {"value": rps, "unit": "rays/s", "cores": cpu_arm.cores, "kind": cpu_arm.kind,
+                   "sample": f"{CPU_SAMPLE_RAYS} of the frame's 307200 rays in tester.py-style 4096-ray chunks, one pass "
+                             f"({secs:.1f} s), {cpu_arm.describe()}; a full frame extrapolates linearly to "
+                             f"{N_RAYS / rps:.0f} s"}
+            if train is not None:
+                t_rps, t_secs, t_anom = cpu_arm.train(1024)
+                train["cpu_baseline"] = {
+                    "value": t_rps, "unit": "rays/s", "cores": cpu_arm.cores, "kind": cpu_arm.kind,
+                    "sample": f"C1 step (1024 rays, K=32: dm_nerf + MSE + Hungarian instance loss + penalizer + backward + Adam), "
+                              f"1 warm-up then mean of 2 steps = {t_secs:.2f} s/step, {cpu_arm.describe()}",
+                    "s_per_step_with_reference_anomaly_detection_on": t_anom}
+        except Exception as e:                                  # pragma: no cover
+            cpu = {"value": None, "error": repr(e)}
+    h2d, d2h = job.io_bytes()
+    line = {
+        "metric": "rays/sec render (64+128 samples/ray)", "value": N_RAYS / (ms_step / 1000), "unit": "rays/s",
+        "n_gpus": cx.world, "steps": steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16" if mode == "bf16" else "f32", "data": "synthetic", "rays_per_step": N_RAYS,
+        "config": {"workload": "DM-SR full-image render 640x480 = 307200 rays x (64+128) samples, K=32, rgb+depth+instance "
+                               "map+labels, one frame per step",
+                   "mode": mode, "chunk_rays": args.chunk, "l2": "flushed between timed iterations (256 MiB write)",
+                   "parallelism": f"the frame's pixel rows sharded x{cx.world} (no data-path collective), point-to-point "
+                                  f"gather of rgb+depth+K-channel map+labels into rank 0's frame buffers inside the timed region"},
+        "e2e": {"value": N_RAYS / (ms_e2e / 1000), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e,
+                "path": "pinned host rays -> each rank's shard H2D -> frame.render_pixels -> gather -> rgb, depth, "
+                        "K-channel instance map and uint8 labels D2H into pinned host buffers on rank 0"},
+        "gpu_launches": launches, "roofline": roofline, "roofline_secondary": secondary, "cpu_baseline": cpu, "clocks": clocks,
+        "stage_ms_per_step": {k: round(v[1] / steps, 3) for k, v in totals.items()},
+    }
+    line.update({k: v for k, v in legs.items() if v is not None})
+    return line
 
 
 def main():
@@ -410,11 +800,18 @@ def main():
     ap.add_argument("--mode", default=os.environ.get("DMNERF_BENCH_MODE", "auto"), choices=["auto", "bf16", "fp32"])
     ap.add_argument("--chunk", type=int, default=32768)
     ap.add_argument("--no-train", action="store_true", help="skip the training-throughput leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the weak / C4 / C5 legs")
+    ap.add_argument("--no-parity", action="store_true", help="skip the fp32-mode frame and the parity blocks")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baselines")
+    ap.add_argument("--parity-train-steps", type=int, default=1500)
     args = ap.parse_args()
     if not (args.gpus > 1 and int(os.environ.get("WORLD_SIZE", "1")) == 1 and args.impl != "reference"):
         quiet_stdout()                                  # (the torchrun relaunch path leaves fd 1 to its children)
     if args.impl == "reference":
         return run_reference(args)
+    if args.warmup < 3:
+        log("warning: fewer than 3 warm-up steps requested; using 3")
+        args.warmup = 3
     if args.mode == "auto":
         from dm_nerf_b200 import _lib
         args.mode = "bf16" if _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) > 0 else "fp32"
