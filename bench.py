@@ -39,6 +39,9 @@ REF_STEP_RAYS = 8192                             # rays per step of the --impl r
 C4 = dict(H=968, W=1296, K=16, near=0.0, far=9.5)            # ScanNet-shaped frame (configs[3])
 
 
+TC_MODES = ("bf16", "fp16")      # tcgen05 chains: bf16 (training + inference) and fp16 (inference only)
+
+
 def macs_per_point(k: int) -> int:
     return 691840 + 128 * k                      # algorithmic, padding not counted
 
@@ -586,6 +589,7 @@ def trained_parity(cx: Ctx, job: FrameJob, steps: int):
     image = (0.8 * palette[lab] + 0.2 * yy).clamp(0, 1)
     torch.manual_seed(5 + cx.rank)
     t0 = time.perf_counter()
+    ops.set_mode("bf16")                                     # the training chain
     models, ts, _, _, _ = train_models(cx, K_INS, 1024, steps, NEAR, FAR, H, W, (job.Kmat, job.c2w), image=image, labels=lab)
     last = ts.step(image, job.c2w[:3, :4].to(cx.dev), lab)
     cx.sync()
@@ -594,11 +598,19 @@ def trained_parity(cx: Ctx, job: FrameJob, steps: int):
     tjob = FrameJob(cx, models, H, W, K_INS, NEAR, FAR, (job.Kmat, job.c2w), job.chunk)
     out = None
     try:
-        ops.set_mode("bf16"); tjob.step(); cx.sync()
-        got = snapshot(tjob.frame) if cx.rank == 0 else None
+        got = {}
+        for m in TC_MODES:                                   # the headline's mode and the other tensor-core mode
+            ops.set_mode(m); tjob.step(); cx.sync()
+            got[m] = snapshot(tjob.frame) if cx.rank == 0 else None
         ops.set_mode("fp32"); tjob.step(); cx.sync()
         if cx.rank == 0:
-            out = frame_parity(torch, tjob.frame, got)
+            out = frame_parity(torch, tjob.frame, got[cx.args.mode])
+            out["mode"] = cx.args.mode
+            for m in TC_MODES:
+                if m != cx.args.mode:
+                    other = frame_parity(torch, tjob.frame, got[m])
+                    out["other_mode"] = {"mode": m, **{k: other[k] for k in (
+                        "psnr_delta_db", "psnr_between_modes_db", "label_agreement", "max_abs_rgb", "mean_abs_depth")}}
             gt_lab = lab.reshape(-1)
             out.update({"weights": f"trained {steps + 1} steps x 1024 rays x {cx.world} ranks on this view (bf16 mode, TrainStep graph)",
                         "train_seconds": train_s, "final_loss": {k: float(v) for k, v in last.items()},
@@ -615,10 +627,10 @@ def run_gpu(args):
     from dm_nerf_b200 import ops, _lib, synth
     from dm_nerf_b200.frame import render_pixels
     mode = args.mode
-    if mode == "bf16" and _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) <= 0:
-        raise RuntimeError("bf16 tensor-core mode is not built")
+    if mode in TC_MODES and _lib.lib().dmnerf_packed_bytes(K_INS, _lib.MODE_BF16) <= 0:
+        raise RuntimeError("tensor-core modes are not built")
     ops.set_mode(mode)
-    mode_id = _lib.MODE_BF16 if mode == "bf16" else _lib.MODE_FP32
+    mode_id = {"bf16": _lib.MODE_BF16, "fp16": _lib.MODE_F16, "fp32": _lib.MODE_FP32}[mode]
     models = make_models(torch, K_INS, cx.dev)
     job = FrameJob(cx, models, H, W, K_INS, NEAR, FAR, synth.dmsr_camera(H, W, 0), args.chunk)
 
@@ -642,7 +654,7 @@ def run_gpu(args):
 
     # ---- the same frame in the fp32 parity mode (CUDA-core FFMA): its cost, and the parity of the headline mode --------
     fp32_leg = parity = None
-    if mode == "bf16" and not args.no_parity:
+    if mode in TC_MODES and not args.no_parity:
         ops.set_mode("fp32")
         try:
             ms_fp32 = cx.timed(job.step, 1)
@@ -693,13 +705,17 @@ def run_gpu(args):
 
     train = None
     if not args.no_train:
-        train = train_leg(cx)
+        ops.set_mode("bf16" if mode in TC_MODES else mode)   # training runs the bf16 chain (fp16 is inference-only)
+        try:
+            train = train_leg(cx)
+        finally:
+            ops.set_mode(mode)
         log("train leg done")
 
     # ---- parity of the tensor-core mode on a TRAINED-like field: optimisation steps on one synthetic view (smooth
     # colour blocks + 32 block labels) make the instance head confident, as a converged model's is ---------------------
     parity_trained = None
-    if mode == "bf16" and not args.no_parity and args.parity_train_steps > 0:
+    if mode in TC_MODES and not args.no_parity and args.parity_train_steps > 0:
         parity_trained = trained_parity(cx, job, args.parity_train_steps)
         log("trained parity done")
 
@@ -729,7 +745,7 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
         flops_total = 2.0 * macs_per_point(K_INS) * (SC + NIMP) * rays_rank0 * steps
         achieved = flops_total / (ms_kernel / 1000) / 1e12
         peak = peaks.get("bf16_tflops_sustained", 1400.0)
-        tr = ncu_traffic_bytes() if mode == "bf16" else None
+        tr = ncu_traffic_bytes() if mode in TC_MODES else None
         rays_per_launch = rays_rank0 * steps / n_launch
         roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                     "traffic": tr[0] if tr else None,
@@ -774,7 +790,7 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
         "metric": "rays/sec render (64+128 samples/ray)", "value": N_RAYS / (ms_step / 1000), "unit": "rays/s",
         "n_gpus": cx.world, "steps": steps, "warmup": args.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "bf16" if mode == "bf16" else "f32", "data": "synthetic", "rays_per_step": N_RAYS,
+        "dtype": {"bf16": "bf16", "fp16": "f16", "fp32": "f32"}[mode], "data": "synthetic", "rays_per_step": N_RAYS,
         "config": {"workload": "DM-SR full-image render 640x480 = 307200 rays x (64+128) samples, K=32, rgb+depth+instance "
                                "map+labels, one frame per step",
                    "mode": mode, "chunk_rays": args.chunk, "l2": "flushed between timed iterations (256 MiB write)",
@@ -797,7 +813,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--mode", default=os.environ.get("DMNERF_BENCH_MODE", "auto"), choices=["auto", "bf16", "fp32"])
+    ap.add_argument("--mode", default=os.environ.get("DMNERF_BENCH_MODE", "auto"), choices=["auto", "bf16", "fp16", "fp32"])
     ap.add_argument("--chunk", type=int, default=32768)
     ap.add_argument("--no-train", action="store_true", help="skip the training-throughput leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the weak / C4 / C5 legs")

@@ -16,7 +16,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 SO_PATH = os.path.join(PKG_DIR, "libdmnerf_b200.so")
 
-MODE_FP32, MODE_BF16 = 0, 1
+MODE_FP32, MODE_BF16, MODE_F16, MODE_TC32 = 0, 1, 2, 3
 COMP_DROP_EMPTY, COMP_RAW_INS = 1, 2
 PEN_ACCUMULATE = 2
 NUM_PARAMS = 30
@@ -131,6 +131,7 @@ _SIGNATURES = {
     "dmnerf_selftest_tmem_read_bw": (_int, [_int, _int, _int, _p, _p]),
     "dmnerf_selftest_umma_rate": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_counters": (_int, [_p]),
+    "dmnerf_debug_counters_tc32": (_int, [_p]),
     "dmnerf_hungarian": (_int, [_p, _int, _i64, _int, _p, _int, _p, _p]),
     "dmnerf_hungarian_infeasible": (_int, [C.POINTER(_int), _p]),
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),

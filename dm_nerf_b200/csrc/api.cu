@@ -28,8 +28,12 @@ int launch_mlp_bwd_fp32(const float* packed, const float* acts, const float* d_r
                         float* const* grads, cudaStream_t st);
 // mlp_tc.cu
 int64_t bf16_image_bytes(int ins_num);
-int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st);
-int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st, bool f16 = false);
+int64_t x3_image_bytes(int ins_num);
+int pack_x3(const float* const* params, int ins_num, void* packed, cudaStream_t st);
+int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st,
+                    bool f16 = false);
 int tc_debug_flags();
 // mlp_tc_bwd.cu
 int64_t bf16_acts_bytes(int64_t n_points);
@@ -72,7 +76,8 @@ static int check_ins(int ins_num, const char* who) {
 extern "C" int64_t dmnerf_packed_bytes(int ins_num, int mode) {
     if (ins_num < 1 || ins_num > kMaxIns) return -1;
     if (mode == DMNERF_MODE_FP32) return fp32_image(ins_num).total_floats * 4;
-    if (mode == DMNERF_MODE_BF16) return bf16_image_bytes(ins_num);
+    if (mode == DMNERF_MODE_BF16 || mode == DMNERF_MODE_F16) return bf16_image_bytes(ins_num);
+    if (mode == DMNERF_MODE_TC32) return x3_image_bytes(ins_num);
     return -1;
 }
 
@@ -82,6 +87,8 @@ extern "C" int dmnerf_weights_pack(const float* const* params, int ins_num, int 
     for (int i = 0; i < kNumParams; ++i) DM_REQUIRE(params[i], DMNERF_EINVAL, "weights_pack: params[%d] is null", i);
     if (mode == DMNERF_MODE_FP32) return pack_fp32(params, ins_num, static_cast<float*>(packed), as_stream(stream));
     if (mode == DMNERF_MODE_BF16) return pack_bf16(params, ins_num, packed, as_stream(stream));
+    if (mode == DMNERF_MODE_F16) return pack_bf16(params, ins_num, packed, as_stream(stream), true);
+    if (mode == DMNERF_MODE_TC32) return pack_x3(params, ins_num, packed, as_stream(stream));
     DM_REQUIRE(false, DMNERF_EUNSUPPORTED, "weights_pack: unknown mode %d", mode);
 }
 
@@ -104,6 +111,8 @@ static int run_mlp(const MlpInput& in, const void* packed, int ins_num, int mode
     if (mode == DMNERF_MODE_BF16) {
         return launch_mlp_bf16(in, packed, ins_num, raw_out, acts, as_stream(stream));
     }
+    if (mode == DMNERF_MODE_F16) return launch_mlp_bf16(in, packed, ins_num, raw_out, acts, as_stream(stream), true);
+    if (mode == DMNERF_MODE_TC32) return launch_mlp_x3(in, packed, ins_num, raw_out, acts, as_stream(stream));
     DM_REQUIRE(false, DMNERF_EUNSUPPORTED, "mlp_fwd: unknown mode %d", mode);
 }
 

@@ -23,6 +23,7 @@
 // epilogue thread owns one row, so one 16-byte store writes 8 consecutive features of the next
 // layer's A operand and a warp's stores are 512 contiguous bytes (conflict-free).
 #include "mlp_tc_common.cuh"
+#include <cuda_fp16.h>
 
 namespace dmnerf {
 
@@ -57,7 +58,14 @@ __global__ void compose_kernel(Params pr, float* __restrict__ scratch) {
 }
 
 // one thread per bf16 element of the chunk stream: layer l, chunk c, k-group g, row n, element e
-__global__ void pack_bf16_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+__device__ __forceinline__ uint16_t half_bits(float v, int f16) {
+    return f16 ? __half_as_ushort(__float2half_rn(v)) : __bfloat16_as_ushort(__float2bfloat16_rn(v));
+}
+__device__ __forceinline__ float half_value(uint16_t b, int f16) {
+    return f16 ? __half2float(__ushort_as_half(b)) : __bfloat162float(__ushort_as_bfloat16(b));
+}
+
+__global__ void pack_bf16_kernel(Params pr, Image im, uint8_t* __restrict__ image, int f16) {
     const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
     const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const int64_t total = im.bias_off / 2;
@@ -73,7 +81,7 @@ __global__ void pack_bf16_kernel(Params pr, Image im, uint8_t* __restrict__ imag
     r -= static_cast<int64_t>(g) * N * 8;
     const int n = static_cast<int>(r >> 3), e = static_cast<int>(r & 7);
     const int k = c * kChunkK + g * 8 + e;
-    reinterpret_cast<__nv_bfloat16*>(image)[idx] = __float2bfloat16_rn(logical_weight(pr, scratch, l, n, k, im.ins_num));
+    reinterpret_cast<uint16_t*>(image)[idx] = half_bits(logical_weight(pr, scratch, l, n, k, im.ins_num), f16);
 }
 
 // dgrad operand B[n = forward input j][k = forward output i] of dgrad layer d (mlp_tc_common.cuh)
@@ -122,15 +130,15 @@ __global__ void pack_f32_kernel(Params pr, Image im, uint8_t* __restrict__ image
 
 // forward bias blocks: layer l = blockIdx.x, element (g, n, e) of a [2][256][8] K-major B operand; k = 0 holds the
 // bf16 head of the bias and k = 1 the bf16 of the remainder (A = ones in both columns), ~16 mantissa bits in all
-__global__ void pack_fwbias_kernel(Params pr, Image im, uint8_t* __restrict__ image) {
+__global__ void pack_fwbias_kernel(Params pr, Image im, uint8_t* __restrict__ image, int f16) {
     const float* scratch = reinterpret_cast<const float*>(image + im.scratch_off);
     const int l = blockIdx.x;
-    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(image + im.fwb_off + static_cast<int64_t>(l) * kFwBiasBlkBytes);
+    uint16_t* dst = reinterpret_cast<uint16_t*>(image + im.fwb_off + static_cast<int64_t>(l) * kFwBiasBlkBytes);
     for (int i = threadIdx.x; i < 2 * 256 * 8; i += blockDim.x) {
         const int g = i / (256 * 8), n = (i >> 3) & 255, e = i & 7, kin = g * 8 + e;
         const float b = l < 8 ? pr.p[2 * l + 1][n] : scratch[65536 + n];
-        const float hi = __bfloat162float(__float2bfloat16_rn(b));
-        dst[i] = __float2bfloat16_rn(kin == 0 ? hi : (kin == 1 ? b - hi : 0.f));
+        const float hi = half_value(half_bits(b, f16), f16);
+        dst[i] = half_bits(kin == 0 ? hi : (kin == 1 ? b - hi : 0.f), f16);
     }
 }
 
@@ -159,7 +167,7 @@ __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ imag
 // a_ready | epilogue warp 0: 3 total, 4 wait acc_ready | producer 5 wait w_empty
 __device__ long long g_dbg1[8];
 
-template <bool kStash>
+template <bool kStash, bool kF16 = false>
 __global__ void __launch_bounds__(kFwThreads, 1)
 mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags,
                     uint8_t* __restrict__ stash) {
@@ -181,7 +189,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
         const float* gb = reinterpret_cast<const float*>(image + im.bias_off);
         for (int i = threadIdx.x; i < 128 + 256 + 1; i += kFwThreads) s_misc[i] = gb[kBiasT9 + i];
         uint32_t* ones = reinterpret_cast<uint32_t*>(smem + kFwSmOnes);
-        for (int i = threadIdx.x; i < 32; i += kFwThreads) ones[i] = (i & 3) == 0 ? 0x3F803F80u : 0u;
+        for (int i = threadIdx.x; i < 32; i += kFwThreads) ones[i] = (i & 3) == 0 ? (kF16 ? 0x3C003C00u : 0x3F803F80u) : 0u;
     }
     ptx::fence_proxy_async_smem();
     ptx::tc_fence_before();
@@ -242,7 +250,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
                 for (int l = 0; l < kLayers; ++l) {
                     const uint32_t N = im.n[l];
-                    const uint32_t idesc = ptx::idesc_bf16(kTile, N);
+                    const uint32_t idesc = kF16 ? ptx::idesc_f16(kTile, N) : ptx::idesc_bf16(kTile, N);
                     const int chunks = layer_k(l) / kFwChunkK, last = chunks - (l == 9);   // T0..T8: + the bias step
                     uint32_t a_lo = a_lo0 + layer_akg0(l) * kKg16;
 #pragma unroll 1
@@ -305,10 +313,10 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
 #pragma unroll
                     for (int c = 0; c < 3; ++c) dir[c] = d[c] * inv;
                 }
-                if (half == 0) embed_to_ext<kPosFreqs, 0, 4>(a_base, row, pos, gst, kStPos);
-                else           embed_to_ext<kPosFreqs, 4, 8>(a_base, row, pos, gst, kStPos);
+                if (half == 0) embed_to_ext<kPosFreqs, 0, 4, kF16>(a_base, row, pos, gst, kStPos);
+                else           embed_to_ext<kPosFreqs, 4, 8, kF16>(a_base, row, pos, gst, kStPos);
             } else {
-                row_to_ext(a_base, row, valid ? in.x + p * 90 : nullptr, 63, half * 4, half * 4 + 4, gst, kStPos);
+                row_to_ext<kF16>(a_base, row, valid ? in.x + p * 90 : nullptr, 63, half * 4, half * 4 + 4, gst, kStPos);
             }
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
@@ -339,7 +347,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                         if constexpr (kStash)
                             mword = store_kg_mask(a_base, cb * 4 + g, row, v, gst, (l == 8 ? kStHid : kStH0 + 32 * l) + cb * 4 + g, g, mword);
                         else
-                            store_kg(a_base, cb * 4 + g, row, v, true);
+                            store_kg<kF16>(a_base, cb * 4 + g, row, v, true);
                     }
                     // one coalesced 128-byte line of sign masks per warp and 32 columns (read by the dgrad chain)
                     if constexpr (kStash) *reinterpret_cast<uint32_t*>(mst + tc_mask_word(sblk, l, half, cb & 3, row & 63)) = mword;
@@ -347,8 +355,8 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 if (l == 7) {
                     // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it)
                     if (half == 0) {
-                        if (in.x == nullptr) embed_to_ext<kDirFreqs, 0, 4>(a_base, row, dir, gst, kStDir);
-                        else row_to_ext(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 0, 4, gst, kStDir);
+                        if (in.x == nullptr) embed_to_ext<kDirFreqs, 0, 4, kF16>(a_base, row, dir, gst, kStDir);
+                        else row_to_ext<kF16>(a_base, row, valid ? in.x + p * 90 + 63 : nullptr, 27, 0, 4, gst, kStDir);
                     } else {
                         dens_part[row] = dens;
                     }
@@ -467,14 +475,17 @@ int launch_mlp_bf16_v4(const MlpInput& in, const void* packed, int ins_num, floa
 int launch_masks_from_acts(void* acts, int64_t n_points, cudaStream_t st);
 int persistent_ctas(int sm_count);
 
-int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
+int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st,
+                    bool f16) {
+    DM_REQUIRE(!(f16 && stash), DMNERF_EUNSUPPORTED,
+               "mlp_fwd(f16): the fp16 chain is inference-only (no activation stash; train in DMNERF_MODE_BF16)");
     // debug bits 2/3/5 select the parked variants of csrc/experimental/ (built only with -DDMNERF_EXPERIMENTAL; all
     // correct, none faster than this kernel -- measurements in DESIGN.md 4.1)
 #ifndef DMNERF_EXPERIMENTAL
     DM_REQUIRE(!(g_tc_debug_flags & (4 | 8 | 32)), DMNERF_EUNSUPPORTED,
                "mlp_fwd(bf16): forward variants are not in this build (compile with -DDMNERF_EXPERIMENTAL)");
 #else
-    if (g_tc_debug_flags & (4 | 8 | 32)) {
+    if (!f16 && (g_tc_debug_flags & (4 | 8 | 32))) {
         const int rc = (g_tc_debug_flags & 4)   ? launch_mlp_bf16_v2(in, packed, ins_num, raw_out, stash, st)
                        : (g_tc_debug_flags & 8) ? launch_mlp_bf16_v3(in, packed, ins_num, raw_out, stash, st)
                                                 : launch_mlp_bf16_v4(in, packed, ins_num, raw_out, stash, st);
@@ -499,6 +510,10 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
         tc::mlp_fwd_bf16_kernel<true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
             in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags,
             static_cast<uint8_t*>(stash));
+    } else if (f16) {
+        DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+        tc::mlp_fwd_bf16_kernel<false, true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
+            in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags, nullptr);
     } else {
         DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
         tc::mlp_fwd_bf16_kernel<false><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
@@ -524,7 +539,7 @@ namespace tc3 { int pack_v3(const float* const* params, int ins_num, void* packe
 
 int64_t bf16_image_bytes(int ins_num) { return tc::make_image(ins_num).total_bytes; }
 
-int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st) {
+int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st, bool f16) {
     const tc::Image im = tc::make_image(ins_num);
     tc::Params pr;
     for (int i = 0; i < kNumParams; ++i) pr.p[i] = params[i];
@@ -532,9 +547,13 @@ int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_
     float* scratch = reinterpret_cast<float*>(image + im.scratch_off);
     tc::compose_kernel<<<(2 * 128 * 256 + 256 + 255) / 256, 256, 0, st>>>(pr, scratch);
     const int64_t elems = im.bias_off / 2;
-    tc::pack_bf16_kernel<<<static_cast<unsigned>((elems + 255) / 256), 256, 0, st>>>(pr, im, image);
+    tc::pack_bf16_kernel<<<static_cast<unsigned>((elems + 255) / 256), 256, 0, st>>>(pr, im, image, f16);
     tc::pack_bias_kernel<<<(tc::kBiasFloats + 255) / 256, 256, 0, st>>>(pr, im, image);
-    tc::pack_fwbias_kernel<<<9, 256, 0, st>>>(pr, im, image);
+    tc::pack_fwbias_kernel<<<9, 256, 0, st>>>(pr, im, image, f16);
+    if (f16) {                      // inference-only image: no dgrad streams, no fp32 copies
+        DM_LAUNCH_CHECK("pack_f16");
+        return DMNERF_OK;
+    }
     const int64_t dg_elems = (im.f32_off - im.dg_off[0]) / 2;
     tc::pack_dgrad_kernel<<<static_cast<unsigned>((dg_elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_f32_kernel<<<(tc::kF32Floats + 255) / 256, 256, 0, st>>>(pr, im, image);

@@ -173,10 +173,11 @@ __device__ __forceinline__ uint64_t op_desc(uint32_t addr, uint32_t lbo, uint32_
 // 8 consecutive features of one row -> one 16-byte store into k-group `kg` of the A operand; when `gst` is
 // given (training; already offset to this thread's row inside its 64-point stash block), the same 16 bytes
 // also go to slab `gkg` of the HBM stash (a warp writes 512 contiguous bytes).
+template <bool F16 = false>
 __device__ __forceinline__ void store_kg(uint32_t a_base, int kg, int row, const float v[8], bool relu,
                                          uint8_t* gst = nullptr, int gkg = 0) {
-    const uint32_t w0 = ptx::pack_bf16(v[0], v[1], relu), w1 = ptx::pack_bf16(v[2], v[3], relu);
-    const uint32_t w2 = ptx::pack_bf16(v[4], v[5], relu), w3 = ptx::pack_bf16(v[6], v[7], relu);
+    const uint32_t w0 = ptx::pack_h2<F16>(v[0], v[1], relu), w1 = ptx::pack_h2<F16>(v[2], v[3], relu);
+    const uint32_t w2 = ptx::pack_h2<F16>(v[4], v[5], relu), w3 = ptx::pack_h2<F16>(v[6], v[7], relu);
     ptx::st_shared_v4(a_base + kg * kKgBytes + row * 16, w0, w1, w2, w3);
     if (gst) *reinterpret_cast<uint4*>(gst + gkg * kStKgBytes) = make_uint4(w0, w1, w2, w3);
 }
@@ -201,7 +202,7 @@ __device__ __forceinline__ uint32_t store_kg_mask(uint32_t a_base, int kg, int r
 // Embedding of a 3-vector into EXT k-groups [KG0, KG1): channel c = [x | f: sin(3) cos(3)], 8 channels per
 // k-group.  The first needed octave uses full-range sincosf on x*2^f (exact scaling); higher octaves follow by
 // angle doubling (error << bf16 resolution).  Channels outside the range are dead code after unrolling.
-template <int F, int KG0, int KG1>
+template <int F, int KG0, int KG1, bool F16 = false>
 __device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const float x[3], uint8_t* gst = nullptr,
                                              int gkg0 = 0) {
     constexpr int CH = 3 + 6 * F;
@@ -229,16 +230,17 @@ __device__ __forceinline__ void embed_to_ext(uint32_t a_base, int row, const flo
         }
     }
 #pragma unroll
-    for (int g = KG0; g < KG1; ++g) store_kg(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false, gst, gkg0 + g);
+    for (int g = KG0; g < KG1; ++g) store_kg<F16>(a_base, kExtKg + g, row, &ch[(g - KG0) * 8], false, gst, gkg0 + g);
 }
 
+template <bool F16 = false>
 __device__ __forceinline__ void row_to_ext(uint32_t a_base, int row, const float* __restrict__ src, int count, int kg0,
                                            int kg1, uint8_t* gst = nullptr, int gkg0 = 0) {
     for (int g = kg0; g < kg1; ++g) {
         float v[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] = (src && g * 8 + e < count) ? __ldg(src + g * 8 + e) : 0.f;
-        store_kg(a_base, kExtKg + g, row, v, false, gst, gkg0 + g);
+        store_kg<F16>(a_base, kExtKg + g, row, v, false, gst, gkg0 + g);
     }
 }
 

@@ -11,9 +11,9 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import MODE_BF16, MODE_FP32, COMP_DROP_EMPTY, COMP_RAW_INS, NUM_PARAMS, check
+from ._lib import MODE_BF16, MODE_F16, MODE_FP32, MODE_TC32, COMP_DROP_EMPTY, COMP_RAW_INS, NUM_PARAMS, check
 
-_MODE_NAMES = {"fp32": MODE_FP32, "bf16": MODE_BF16}
+_MODE_NAMES = {"fp32": MODE_FP32, "bf16": MODE_BF16, "fp16": MODE_F16, "f16": MODE_F16, "tc32": MODE_TC32}
 _default_mode = _MODE_NAMES[os.environ.get("DMNERF_MODE", "fp32").lower()]
 
 # launch counter: how many of OUR kernels-launching C-ABI calls were made (bench reports it)
@@ -144,7 +144,10 @@ def mlp_fwd(rays_o, rays_d, z, packed, ins_num: int, mode: int, stash: bool = Fa
     raw = torch.empty((n, s, ins_num + 5), dtype=torch.float32, device=z.device)
     acts = None
     if stash:
-        acts = _aligned_bytes(_lib.lib().dmnerf_acts_bytes(n * s, ins_num, mode), z.device)
+        nbytes = _lib.lib().dmnerf_acts_bytes(n * s, ins_num, mode)
+        if nbytes < 0:
+            raise RuntimeError(f"mlp_fwd: mode {mode} keeps no activation stash (inference only); train in bf16 or fp32")
+        acts = _aligned_bytes(nbytes, z.device)
     _timed_call(f"dmnerf_mlp_fwd[S={s},mode={mode}]", _lib.lib().dmnerf_mlp_fwd, _ptr(rays_o), _ptr(rays_d), _ptr(z),
                 n, s, _ptr(packed), ins_num, mode, _ptr(raw), _ptr(acts), _stream())
     _count()

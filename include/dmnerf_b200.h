@@ -27,6 +27,12 @@ extern "C" {
 
 #define DMNERF_MODE_FP32     0   /* CUDA-core fp32 FFMA chain: <=1e-4 parity mode            */
 #define DMNERF_MODE_BF16     1   /* tcgen05 bf16 tensor-core chain (fp32 accumulate in TMEM) */
+#define DMNERF_MODE_F16      2   /* same chain with fp16 operands (11-bit significands, 8x finer than bf16; activations
+                                    saturate at 65504): INFERENCE ONLY -- no acts stash, no backward              */
+
+#define DMNERF_MODE_TC32     3   /* fp32-accurate tensor-core chain: every operand an fp16 hi+lo pair, three tcgen05
+                                    products per layer (hi*hi + hi*lo + lo*hi), fp32 accumulate and fp32 embeddings;
+                                    meets the fp32 mode's 1e-4 bound at ~1/3 of the bf16 chain's speed.  INFERENCE ONLY */
 
 #define DMNERF_NUM_PARAMS   30   /* tensors in DM_NeRF.state_dict(), networks/dm_nerf.py:65-78 */
 
@@ -199,6 +205,7 @@ int  dmnerf_selftest_umma_rate(int n, int count, long long* out, void* stream);
  * synchronises the device): MMA issuer total / waiting for weights / waiting for activations, epilogue thread total /
  * waiting for accumulators, producer waiting for a free ring slot. */
 int  dmnerf_debug_counters(long long* host_out8);
+int  dmnerf_debug_counters_tc32(long long* host_out12);   /* same for the DMNERF_MODE_TC32 forward (12 counters) */
 int  dmnerf_selftest_issue_cost(int mode, int count, long long* out2_dev, void* stream);
 /* Bring-up switches for the tensor path (bit0: swap LBO/SBO in the forward's descriptors; bit1: in wgrad's).
  * flags < 0 only queries.  Returns the previous value. */

@@ -438,6 +438,84 @@ def test_mlp_bf16_vs_fp32(k):
         ops.set_mode("fp32")
 
 
+@pytest.mark.parametrize("k", [32, 93])
+def test_mlp_fp16_vs_fp32_and_bf16(k):
+    """DMNERF_MODE_F16: the same tcgen05 chain with fp16 operands (inference only).  11-bit significands against bf16's 8:
+    the raw error against the fp32 mode must come out several times smaller than the bf16 mode's on the same inputs, and
+    asking it for an activation stash (training) must be refused."""
+    from dm_nerf_b200 import ops, _lib
+    m = make_model(k, 11)
+    gen = torch.Generator().manual_seed(4)
+    try:
+        for n, s in ((1, 64), (3, 77), (40, 192)):
+            o = ((torch.rand(n, 3, generator=gen) - 0.5) * 2).to(DEV)
+            d = torch.randn(n, 3, generator=gen).to(DEV)
+            z = torch.sort(torch.rand(n, s, generator=gen) * 11 + 4, -1)[0].to(DEV)
+            with torch.no_grad():
+                ops.set_mode("fp32"); ref = m.query_rays(o, d, z)
+                ops.set_mode("bf16"); b16 = m.query_rays(o, d, z)
+                ops.set_mode("fp16"); f16 = m.query_rays(o, d, z)
+            e16, eb = (f16 - ref).abs(), (b16 - ref).abs()
+            assert float(e16.max()) < 1e-2 and float(e16.mean()) < 1e-3, (float(e16.max()), float(e16.mean()))
+            if n * s >= 128:
+                assert float(e16.mean()) < 0.3 * float(eb.mean()), (float(e16.mean()), float(eb.mean()))
+        x = torch.cat([orc.embed((torch.rand(300, 3, generator=gen) - .5) * 8, 10),
+                       orc.embed(torch.nn.functional.normalize(torch.randn(300, 3, generator=gen), dim=-1), 4)], -1).to(DEV)
+        with torch.no_grad():
+            ops.set_mode("fp32"); ref = m(x)
+            ops.set_mode("fp16"); got = m(x)
+        assert float((got - ref).abs().max()) < 1e-2
+        packed = m.packed(_lib.MODE_F16)
+        with pytest.raises(RuntimeError):
+            ops.mlp_fwd(o, d, z, packed, k, _lib.MODE_F16, stash=True)
+    finally:
+        ops.set_mode("fp32")
+
+
+@pytest.mark.parametrize("k", [32, 16, 93])
+def test_mlp_tc32_meets_the_fp32_bound(k):
+    """DMNERF_MODE_TC32: fp16 hi+lo operand pairs, three tcgen05 products per layer, fp32 accumulate.  The raw MLP output
+    must sit within 1e-5 of the CUDA-core fp32 mode (itself <= 5e-5 of the reference, test_mlp_fp32_embedded) -- i.e. the
+    north_star fp32 bound of 1e-4 holds on the tensor cores -- on ray queries (in-kernel embeddings) and embedded rows."""
+    from dm_nerf_b200 import ops
+    m = make_model(k, 11)
+    gen = torch.Generator().manual_seed(4)
+    try:
+        for n, s in ((1, 64), (5, 192), (3, 77), (40, 192), (300, 192)):
+            o = ((torch.rand(n, 3, generator=gen) - 0.5) * 2).to(DEV)
+            d = torch.randn(n, 3, generator=gen).to(DEV)
+            z = torch.sort(torch.rand(n, s, generator=gen) * 11 + 4, -1)[0].to(DEV)
+            with torch.no_grad():
+                ops.set_mode("fp32"); ref = m.query_rays(o, d, z)
+                ops.set_mode("tc32"); got = m.query_rays(o, d, z)
+            err = (got - ref).abs()
+            assert float(err.max()) <= 1e-5, (n, s, float(err.max()))
+        x = torch.cat([orc.embed((torch.rand(300, 3, generator=gen) - .5) * 8, 10),
+                       orc.embed(torch.nn.functional.normalize(torch.randn(300, 3, generator=gen), dim=-1), 4)], -1).to(DEV)
+        with torch.no_grad():
+            ops.set_mode("fp32"); ref = m(x)
+            ops.set_mode("tc32"); got = m(x)
+        assert float((got - ref).abs().max()) <= 1e-5
+    finally:
+        ops.set_mode("fp32")
+
+
+@pytest.mark.parametrize("k", [32, 16, 93])
+def test_mlp_tc32_embedded_vs_golden(golden, k):
+    """... and directly against the reference-generated golden rows (same fixture and bound as test_mlp_fp32_embedded)."""
+    from dm_nerf_b200 import ops
+    g = golden(f"mlp_k{k}")
+    m = make_model(k, int(g["seed"]))
+    x = torch.cat([orc.embed(T(g["pts"]), 10), orc.embed(T(g["dirs"]), 4)], -1)
+    try:
+        ops.set_mode("tc32")
+        with torch.no_grad():
+            out = m(cu(x))
+    finally:
+        ops.set_mode("fp32")
+    close(out, g["out"], 5e-5)
+
+
 def test_render_bf16_psnr_and_labels():
     """north_star bf16 bound: image PSNR within 0.05 dB and >= 99.9% label agreement (where the fp32
     top-2 margin exceeds 1e-4... evaluated on a 64x48 synthetic frame, peaky heads)."""
