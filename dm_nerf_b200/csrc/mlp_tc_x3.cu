@@ -105,24 +105,39 @@ __device__ __forceinline__ float embed_channel(const float x[3], int c) {
     return r < 3 ? sinf(a) : cosf(a);
 }
 
-// cycle counters of block 0 when debug bit 4 is set: issuer t: [4t+0] total, [4t+1] wait w_full, [4t+2] wait a_ready |
+// cycle counters of block 0 when debug bit 4 is set: issuer [0] total, [1] wait w_full, [2] wait a_ready |
 // epilogue warp 0: [8] total, [9] wait acc_ready | producer [10] wait w_empty
 __device__ long long g_dbg_x3[12];
 
+// mbarriers of this kernel (8 B each, inside the FwBars block): w_full[4] | w_empty[4] | a_ready[4] (one per 64-column
+// quarter of the layer output == 2 K-chunks of the next layer) | acc_ready
+struct X3Bars {
+    uint32_t base;
+    __device__ __forceinline__ uint32_t w_full(int s) const { return base + 8 * s; }
+    __device__ __forceinline__ uint32_t w_empty(int s) const { return base + 8 * (kFwStages + s); }
+    __device__ __forceinline__ uint32_t a_ready(int j) const { return base + 8 * (2 * kFwStages + j); }
+    __device__ __forceinline__ uint32_t acc_ready() const { return base + 8 * (2 * kFwStages + 4); }
+};
+static_assert(kFwSmDens - kFwSmBar >= 8 * (2 * kFwStages + 5) + 8, "barrier block too small for the x3 kernel");
+
+// Pipelining across layers: the accumulator alternates between the two 256-column halves of TMEM (layer l -> half
+// l & 1), and the epilogue walks the layer output in four 64-column quarters, every warp taking 16 columns of each, and
+// signals a_ready[j] after quarter j.  Quarter j is K-chunks 2j, 2j+1 of the next layer, so the next layer's products
+// start one quarter into this layer's epilogue and run under the other three.
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sm0 = ptx::smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const FwBars bars{sm0 + kFwSmBar};
+    const X3Bars bars{sm0 + kFwSmBar};
     float* s_misc = reinterpret_cast<float*>(smem + kFwSmMisc);      // [0,128) T9 bias | [128,384) w_density | [384] b_density
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kFwSmBar + 8 * (2 * kFwStages + 4));
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kFwSmBar + 8 * (2 * kFwStages + 5));
     const int C = im.ins_num + 5;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kFwStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 2); }
-        ptx::mbar_init(bars.a_ready(0), 4 * kTile);
-        for (int t = 0; t < 2; ++t) ptx::mbar_init(bars.acc_ready(t), 1);
+        for (int s = 0; s < kFwStages; ++s) { ptx::mbar_init(bars.w_full(s), 1); ptx::mbar_init(bars.w_empty(s), 1); }
+        for (int j = 0; j < 4; ++j) ptx::mbar_init(bars.a_ready(j), 4 * kTile);
+        ptx::mbar_init(bars.acc_ready(), 1);
         ptx::fence_barrier_init();
     }
     if (warp == kMmaWarp) ptx::tmem_alloc(ptx::smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
@@ -169,62 +184,78 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
                 if (++stage == kFwStages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp >= kMmaWarp) {
-        // ===== issuers: t = 0 accumulates D0 (A_hi against hi, lo and bias stages), t = 1 D1 (A_lo against hi stages) =====
+    } else if (warp == kMmaWarp) {
+        // ===== the issuer: hi stage -> A_hi W_hi, A_lo W_hi; lo stage -> A_hi W_lo; bias stage -> ones x bias =====
         if (lane == 0) {
-            const int t = warp - kMmaWarp;
             int stage = 0; uint32_t phase = 0, a_par = 0;
             constexpr uint32_t kKg16 = kKgBytes >> 4;
             const uint64_t desc_hi = static_cast<uint64_t>(0x4008u) << 32;
-            const uint32_t a_lo0 = ((sm0 + (t == 0 ? kAHi : kALo)) >> 4) | (kKg16 << 16);
+            const uint32_t ah0 = ((sm0 + kAHi) >> 4) | (kKg16 << 16), al0 = ((sm0 + kALo) >> 4) | (kKg16 << 16);
             const uint64_t ones_d = (static_cast<uint64_t>(0x4000u) << 32) | ((sm0 + kFwSmOnes) >> 4);
             const uint32_t ring_lo = (sm0 + kFwSmRing) >> 4;
-            const uint32_t d_tmem = tmem + t * 256;
             long long dbg_f = 0, dbg_a = 0;
             const long long dbg_start = clock64();
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 for (int l = 0; l < kLayers; ++l) {
                     const uint32_t N = im.n[l];
                     const uint32_t idesc = ptx::idesc_f16(kTile, N);
-                    const int parts = 2 * (layer_k(l) / kFwChunkK);
-                    const int steps = parts + (l < 9);                              // + the bias stage
-                    const int last_mine = t == 0 ? steps - 1 : parts - 2;           // D1's last product: the last hi stage
-                    uint32_t a_lo = a_lo0 + layer_akg0(l) * kKg16;
+                    const int chunks = layer_k(l) / kFwChunkK;
+                    const uint32_t d_tmem = tmem + (l & 1) * 256;
+                    uint32_t a_off = layer_akg0(l) * kKg16;
+                    int next_q = 0;                                                  // a_ready quarters not yet waited for
 #pragma unroll 1
-                    for (int c = 0; c < steps; ++c) {
+                    for (int c = 0; c < chunks; ++c, a_off += 4 * kKg16) {
+                        // quarter j feeds chunks 2j, 2j+1; the last chunk of a short layer (T0) collects the rest
+                        const int need = (c == chunks - 1) ? 3 : (c >> 1);
+                        if (next_q <= need) {
+                            const long long w1 = clock64();
+                            for (; next_q <= need && next_q < 4; ++next_q) ptx::mbar_wait(bars.a_ready(next_q), a_par);
+                            dbg_a += clock64() - w1;
+                        }
+                        // hi stage
+                        long long w0 = clock64();
+                        ptx::mbar_wait(bars.w_full(stage), phase);
+                        dbg_f += clock64() - w0;
+                        ptx::tc_fence_after();
+                        uint32_t b_lo = (ring_lo + stage * (kFwStageBytes >> 4)) | (N << 16);
+                        ptx::umma_bf16(d_tmem, desc_hi | (ah0 + a_off), desc_hi | b_lo, idesc, c != 0);
+                        ptx::umma_bf16(d_tmem, desc_hi | (ah0 + a_off + 2 * kKg16), desc_hi | (b_lo + 2 * N), idesc, 1u);
+                        ptx::umma_bf16(d_tmem, desc_hi | (al0 + a_off), desc_hi | b_lo, idesc, 1u);
+                        ptx::umma_bf16(d_tmem, desc_hi | (al0 + a_off + 2 * kKg16), desc_hi | (b_lo + 2 * N), idesc, 1u);
+                        ptx::umma_commit(bars.w_empty(stage));
+                        if (++stage == kFwStages) { stage = 0; phase ^= 1; }
+                        // lo stage
+                        w0 = clock64();
+                        ptx::mbar_wait(bars.w_full(stage), phase);
+                        dbg_f += clock64() - w0;
+                        ptx::tc_fence_after();
+                        b_lo = (ring_lo + stage * (kFwStageBytes >> 4)) | (N << 16);
+                        ptx::umma_bf16(d_tmem, desc_hi | (ah0 + a_off), desc_hi | b_lo, idesc, 1u);
+                        ptx::umma_bf16(d_tmem, desc_hi | (ah0 + a_off + 2 * kKg16), desc_hi | (b_lo + 2 * N), idesc, 1u);
+                        if (l == 9 && c == chunks - 1) ptx::umma_commit(bars.acc_ready());
+                        ptx::umma_commit(bars.w_empty(stage));
+                        if (++stage == kFwStages) { stage = 0; phase ^= 1; }
+                    }
+                    a_par ^= 1;
+                    if (l < 9) {                                                     // bias stage
                         const long long w0 = clock64();
                         ptx::mbar_wait(bars.w_full(stage), phase);
-                        const long long w1 = clock64();
-                        dbg_f += w1 - w0;
-                        if (c == 0) { ptx::mbar_wait(bars.a_ready(0), a_par); a_par ^= 1; dbg_a += clock64() - w1; }
-                        const bool is_bias = c == parts, is_lo = !is_bias && (c & 1);
-                        if (t == 1 && (is_bias || is_lo)) {
-                            ptx::mbar_arrive(bars.w_empty(stage));                  // not mine: release at once
-                        } else {
-                            ptx::tc_fence_after();
-                            const uint32_t b_lo = (ring_lo + stage * (kFwStageBytes >> 4)) | (N << 16);
-                            if (is_bias) {
-                                ptx::umma_bf16(d_tmem, ones_d, desc_hi | b_lo, idesc, 1u);
-                            } else {
-                                ptx::umma_bf16(d_tmem, desc_hi | a_lo, desc_hi | b_lo, idesc, c != 0);
-                                ptx::umma_bf16(d_tmem, desc_hi | (a_lo + 2 * kKg16), desc_hi | (b_lo + 2 * N), idesc, 1u);
-                            }
-                            if (c == last_mine) ptx::umma_commit(bars.acc_ready(t));
-                            ptx::umma_commit(bars.w_empty(stage));
-                        }
-                        if (is_lo) a_lo += 4 * kKg16;                               // next 32 columns of K after the pair
+                        dbg_f += clock64() - w0;
+                        ptx::tc_fence_after();
+                        const uint32_t b_lo = (ring_lo + stage * (kFwStageBytes >> 4)) | (N << 16);
+                        ptx::umma_bf16(d_tmem, ones_d, desc_hi | b_lo, idesc, 1u);
+                        ptx::umma_commit(bars.acc_ready());
+                        ptx::umma_commit(bars.w_empty(stage));
                         if (++stage == kFwStages) { stage = 0; phase ^= 1; }
                     }
                 }
             }
-            if ((flags & 16) && blockIdx.x == 0) {
-                g_dbg_x3[4 * t] = clock64() - dbg_start; g_dbg_x3[4 * t + 1] = dbg_f; g_dbg_x3[4 * t + 2] = dbg_a;
-            }
+            if ((flags & 16) && blockIdx.x == 0) { g_dbg_x3[0] = clock64() - dbg_start; g_dbg_x3[1] = dbg_f; g_dbg_x3[2] = dbg_a; }
         }
-    } else {
-        // ===== epilogue / embedding: 16 warps, thread == (point == TMEM lane, column quarter) =====
-        const int q = warp & 3, cq = warp >> 2, row = q * 32 + lane;
-        const uint32_t t_base = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    } else if (warp < kEpiWarps) {
+        // ===== epilogue / embedding: 16 warps; thread == (point == TMEM lane, 16-column slot wq of every quarter) =====
+        const int q = warp & 3, wq = warp >> 2, row = q * 32 + lane;
+        const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
         float* stage_out = reinterpret_cast<float*>(smem + kAHi);
         float* dens_part = reinterpret_cast<float*>(smem + kAHi + kDensKg * kKgBytes);
         uint32_t acc_par = 0;
@@ -249,9 +280,9 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
 #pragma unroll
                 for (int c = 0; c < 3; ++c) dir[c] = d[c] / nrm;
             }
-            // pos-embedding: 8 k-groups of EXT, two per column quarter
+            // pos-embedding: 8 k-groups of EXT, two per warp slot
 #pragma unroll 1
-            for (int g = 2 * cq; g < 2 * cq + 2; ++g) {
+            for (int g = 2 * wq; g < 2 * wq + 2; ++g) {
                 float v[8];
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
@@ -263,71 +294,71 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
             }
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
-            ptx::mbar_arrive(bars.a_ready(0));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ptx::mbar_arrive(bars.a_ready(j));
 
             float dens = 0.f;
             for (int l = 0; l < kLayers - 1; ++l) {
                 const long long w0 = clock64();
-                ptx::mbar_wait(bars.acc_ready(0), acc_par);
-                ptx::mbar_wait(bars.acc_ready(1), acc_par);
+                ptx::mbar_wait(bars.acc_ready(), acc_par);
                 dbg_acc += clock64() - w0;
                 acc_par ^= 1;
                 ptx::tc_fence_after();
+                const uint32_t t_base = t_lane + (l & 1) * 256;
 #pragma unroll 1
-                for (int cb = 2 * cq; cb < 2 * cq + 2; ++cb) {
-                    uint32_t r0[32], r1[32];
-                    ptx::tmem_ld32(t_base + cb * 32, r0);
-                    ptx::tmem_ld32(t_base + 256 + cb * 32, r1);
+                for (int j = 0; j < 4; ++j) {
+                    const int col0 = 64 * j + 16 * wq;
+                    uint32_t r[16];
+                    ptx::tmem_ld16(t_base + col0, r);
                     ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
+                    for (int g = 0; g < 2; ++g) {
                         float v[8];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r0[g * 8 + e]) + __uint_as_float(r1[g * 8 + e]);
+                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
                         if (l == 7) {
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_misc[128 + cb * 32 + g * 8 + e], dens);
+                            for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_misc[128 + col0 + g * 8 + e], dens);
                         }
-                        store_split(sm0, cb * 4 + g, row, v, true);
+                        store_split(sm0, (col0 >> 3) + g, row, v, true);
                     }
-                }
-                if (l == 7) {
-                    // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it): one k-group per quarter
-                    float v[8];
+                    if (l == 7 && j == 3) {
+                        // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it): one k-group per slot
+                        float v[8];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const int c = cq * 8 + e;
-                        if (in.x == nullptr) v[e] = embed_channel<kDirFreqs>(dir, c);
-                        else v[e] = (valid && c < 27) ? __ldg(in.x + p * 90 + 63 + c) : 0.f;
+                        for (int e = 0; e < 8; ++e) {
+                            const int c = wq * 8 + e;
+                            if (in.x == nullptr) v[e] = embed_channel<kDirFreqs>(dir, c);
+                            else v[e] = (valid && c < 27) ? __ldg(in.x + p * 90 + 63 + c) : 0.f;
+                        }
+                        store_split(sm0, kExtKg + wq, row, v, false);
+                        dens_part[wq * kTile + row] = dens;
                     }
-                    store_split(sm0, kExtKg + cq, row, v, false);
-                    dens_part[cq * kTile + row] = dens;
+                    ptx::fence_proxy_async_smem();
+                    ptx::tc_fence_before();
+                    ptx::mbar_arrive(bars.a_ready(j));
                 }
-                ptx::fence_proxy_async_smem();
-                ptx::tc_fence_before();
-                ptx::mbar_arrive(bars.a_ready(0));
             }
-            // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (column quarter 0) ----
+            // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (warp slot 0) ----
             const long long w9 = clock64();
-            ptx::mbar_wait(bars.acc_ready(0), acc_par);
-            ptx::mbar_wait(bars.acc_ready(1), acc_par);
+            ptx::mbar_wait(bars.acc_ready(), acc_par);
             dbg_acc += clock64() - w9;
             acc_par ^= 1;
             ptx::tc_fence_after();
-            if (cq == 0) dens = (dens_part[row] + dens_part[kTile + row]) + (dens_part[2 * kTile + row] + dens_part[3 * kTile + row]);
-            // the other quarters go on to the next tile's embedding, which overwrites the partials: not before they are read
+            if (wq == 0) dens = (dens_part[row] + dens_part[kTile + row]) + (dens_part[2 * kTile + row] + dens_part[3 * kTile + row]);
+            // the other slots go on to the next tile's embedding, which overwrites the partials: not before they are read
             ptx::named_bar_sync(1, 4 * kTile);
-            if (cq == 0) {
+            if (wq == 0) {
+                const uint32_t t_base = t_lane + 256;                        // T9 is layer 9: the odd half
                 for (int cb = 0; cb * 16 < im.npad; ++cb) {
-                    uint32_t r0[16], r1[16];
-                    ptx::tmem_ld16(t_base + cb * 16, r0);
-                    ptx::tmem_ld16(t_base + 256 + cb * 16, r1);
+                    uint32_t r[16];
+                    ptx::tmem_ld16(t_base + cb * 16, r);
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int e = 0; e < 16; ++e) {
                         const int col = cb * 16 + e;
                         if (col < C) {
-                            float v = (__uint_as_float(r0[e]) + __uint_as_float(r1[e])) + s_misc[col];
+                            float v = __uint_as_float(r[e]) + s_misc[col];
                             if (col == 3) v = dens + s_misc[384];
                             stage_out[row * C + col] = v;
                         }

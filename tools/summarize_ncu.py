@@ -47,7 +47,7 @@ def raw(src, dst):
     out = ["metric,unit," + ",".join(f"launch{i}" for i in range(len(rows) - 2))]
     for i, name in enumerate(hdr):
         if name == "Kernel Name" or any(k in name for k in KEEP):
-            out.append(",".join([name, units[i]] + [r[i].replace(",", "") if name != "Kernel Name" else re.sub(r"\(.*", "", r[i]) for r in rows[2:]]))
+            out.append(",".join([name, units[i]] + [r[i].replace(",", "") if name != "Kernel Name" else re.sub(r"\(.*", "", r[i]).replace(",", ";") for r in rows[2:]]))
     open(dst, "w").write("\n".join(out) + "\n")
     print("\n".join(out))
 

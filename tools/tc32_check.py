@@ -47,8 +47,8 @@ buf = (C.c_longlong * 12)()
 _lib.lib().dmnerf_debug_counters_tc32(buf)
 _lib.lib().dmnerf_debug_flags(0)
 tiles = (n * s / 128) / 148
-names = ["issuer0 total", "issuer0 wait w_full", "issuer0 wait a_ready", "-", "issuer1 total", "issuer1 wait w_full",
-         "issuer1 wait a_ready", "-", "epi total", "epi wait acc_ready", "producer wait w_empty", "-"]
+names = ["issuer total", "issuer wait w_full", "issuer wait a_ready", "-", "-", "-",
+         "-", "-", "epi total", "epi wait acc_ready", "producer wait w_empty", "-"]
 for nm, v in zip(names, buf):
     if nm != "-":
         print(f"  {nm:24s} {v:12d}  per tile {v / tiles:10.0f}")
