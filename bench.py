@@ -37,6 +37,7 @@ sys.path.insert(0, ROOT)
 H, W, K_INS, SC, NIMP = 480, 640, 32, 64, 128
 NEAR, FAR = 4.0, 15.0
 N_RAYS = H * W
+TRAINED_REF_RAYS = 12288                         # rays of the trained frame the reference re-renders on the host (~6 s)
 CPU_SAMPLE_RAYS = 24576                          # ~10-20 s of host work for the cpu_baseline leg
 REF_STEP_RAYS = 8192                             # rays per step of the --impl reference arm (2 tester.py chunks)
 C4 = dict(H=968, W=1296, K=16, near=0.0, far=9.5)            # ScanNet-shaped frame (configs[3])
@@ -147,8 +148,8 @@ class CpuArm:
     def embedders(self):
         return self.R.model.get_embedder(10, 0)[0], self.R.model.get_embedder(4, 0)[0]
 
-    def models(self, k, requires_grad=False):
-        sd_c, sd_f = self.synth.init_state_dict(k, 1), self.synth.init_state_dict(k, 2)
+    def models(self, k, requires_grad=False, state_dicts=None):
+        sd_c, sd_f = state_dicts or (self.synth.init_state_dict(k, 1), self.synth.init_state_dict(k, 2))
         if self.R is None:
             if requires_grad:
                 sd_c = {n: v.requires_grad_(True) for n, v in sd_c.items()}
@@ -170,12 +171,14 @@ class CpuArm:
         sel = torch.linspace(0, N_RAYS - 1, n_rays).long()
         return torch.stack([ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel]], 0).float()
 
-    def render(self, n_rays, repeats=1):
+    def render(self, n_rays, repeats=1, state_dicts=None):
         """tester.py:54-76 on ``n_rays`` of the frame: N_test = 4096 chunks of dm_nerf, perturb = 0.  -> (rays/s, s)"""
         torch = self.torch
-        mc, mf = self.models(K_INS)
+        mc, mf = self.models(K_INS, state_dicts=state_dicts)
         rays = self.sample_rays(n_rays)
         best = None
+        self.last_render = None
+        outs = []
         with torch.no_grad():
             if self.R is not None:
                 pe, ve = self.embedders()
@@ -186,12 +189,16 @@ class CpuArm:
                     b = min(n_rays, a + 4096)
                     if self.R is not None:
                         zc = self.R.helpers.z_val_sample(b - a, NEAR, FAR, SC)
-                        self.R.render.dm_nerf(rays[:, a:b], pe, ve, mc, mf, zc, args)
+                        info = self.R.render.dm_nerf(rays[:, a:b], pe, ve, mc, mf, zc, args)
                     else:
                         zc = self.orc.z_val_sample(b - a, NEAR, FAR, SC)
-                        self.orc.dm_nerf(rays[:, a:b], mc, mf, zc, perturb=0.0, n_importance=NIMP)
+                        info = self.orc.dm_nerf(rays[:, a:b], mc, mf, zc, perturb=0.0, n_importance=NIMP)
+                    outs.append({k: info[k + "_fine"] for k in ("rgb", "depth", "ins")})      # what tester.py:73-76 keeps
                 dt = time.perf_counter() - t0
                 best = dt if best is None else min(best, dt)
+                if self.last_render is None:
+                    self.last_render = {k: torch.cat([o[k] for o in outs], 0) for k in ("rgb", "depth", "ins")}
+                outs = []
         return n_rays / best, best
 
     def train(self, n_rays, timed=2):
@@ -432,6 +439,33 @@ def snapshot(frame):
     return {k: v.clone() for k, v in frame.items()}
 
 
+def sample_pixels(torch, frame, n_rays=CPU_SAMPLE_RAYS):
+    """The frame at the pixels the CPU arm renders (CpuArm.sample_rays: every 12.5th pixel), on the host."""
+    sel = torch.linspace(0, N_RAYS - 1, n_rays).long().to(frame["rgb"].device)
+    return {k: frame[k][sel].float().cpu() for k in ("rgb", "depth", "ins")}
+
+
+def parity_vs_reference(torch, ref, got):
+    """A mode's frame against the UNMODIFIED reference's own output (torch CPU fp32) on the CPU arm's sample of the
+    benchmarked frame's rays: north_star's fp32 clause is rgb/depth within 1e-4."""
+    e_rgb = (got["rgb"] - ref["rgb"]).abs().amax(-1)
+    e_dep = (got["depth"] - ref["depth"]).abs()
+    e_ins = (got["ins"] - ref["ins"]).abs().amax(-1)
+    top2 = torch.topk(ref["ins"], 2, dim=-1).values
+    sure = (top2[:, 0] - top2[:, 1]) > 1e-4
+    agree = got["ins"].argmax(-1) == ref["ins"].argmax(-1)
+    return {"rays": int(e_rgb.numel()), "max_abs_rgb": float(e_rgb.max()), "max_abs_depth": float(e_dep.max()),
+            "max_abs_ins": float(e_ins.max()), "median_abs_rgb": float(e_rgb.median()),
+            "rays_within_1e-4_rgb": float((e_rgb <= 1e-4).float().mean()),
+            "rays_within_1e-4_depth": float((e_dep <= 1e-4).float().mean()),
+            "rays_within_1e-4_rgb_depth_ins": float(((e_rgb <= 1e-4) & (e_dep <= 1e-4) & (e_ins <= 1e-4)).float().mean()),
+            "worst_ray": int(e_rgb.argmax()),
+            "psnr_between_db": -10.0 * math.log10(max(float(((got["rgb"] - ref["rgb"]) ** 2).mean()), 1e-20)),
+            "label_agreement": float(agree.float().mean()),
+            "label_agreement_margin_1e-4": float(agree[sure].float().mean()) if int(sure.sum()) else None,
+            "rays_margin_1e-4": float(sure.float().mean())}
+
+
 def frame_parity(torch, ref, got, gt_noise_seed=0):
     """``got`` (tensor-core mode) against ``ref`` (fp32 parity mode), both whole frames on the device: north_star's
     bf16 clause (PSNR within 0.05 dB, label agreement >= 99.9 %) evaluated on the frame the bench times."""
@@ -581,7 +615,7 @@ def c5_leg(cx: Ctx, models, cpu_arm):
     return out
 
 
-def trained_parity(cx: Ctx, job: FrameJob, steps: int):
+def trained_parity(cx: Ctx, job: FrameJob, steps: int, cpu_arm=None):
     """bf16 tensor mode vs fp32 parity mode on the 640x480 frame of a field trained for ``steps`` steps (1024 rays each,
     data-parallel over the ranks, so every rank ends with the same weights) on that view."""
     from dm_nerf_b200 import ops, synth
@@ -616,6 +650,19 @@ def trained_parity(cx: Ctx, job: FrameJob, steps: int):
                     out["other_modes"].append({"mode": m, **{k: other[k] for k in (
                         "psnr_delta_db", "psnr_between_modes_db", "label_agreement", "max_abs_rgb", "max_abs_depth",
                         "mean_abs_depth", "max_abs_ins")}})
+            if cpu_arm is not None:
+                # ... and every mode against the UNMODIFIED reference run on the trained weights (CPU, a ray sample)
+                try:
+                    sds = tuple({k: v.detach().float().cpu().clone() for k, v in m.state_dict().items()} for m in models[2:])
+                    cpu_arm.render(TRAINED_REF_RAYS, state_dicts=sds)
+                    ref = cpu_arm.last_render
+                    frames = dict(got); frames["fp32"] = tjob.frame
+                    out["vs_reference"] = {
+                        "what": f"each mode's frame of the trained field against the {cpu_arm.describe()} with the same "
+                                f"trained weights on {TRAINED_REF_RAYS} rays of the frame",
+                        **{m: parity_vs_reference(torch, ref, sample_pixels(torch, fr, TRAINED_REF_RAYS)) for m, fr in frames.items()}}
+                except Exception as e:                           # pragma: no cover
+                    out["vs_reference"] = {"error": repr(e)}
             gt_lab = lab.reshape(-1)
             out.update({"weights": f"trained {steps + 1} steps x 1024 rays x {cx.world} ranks on this view (bf16 mode, TrainStep graph)",
                         "train_seconds": train_s, "final_loss": {k: float(v) for k, v in last.items()},
@@ -655,6 +702,7 @@ def run_gpu(args):
     ms_e2e = cx.timed(job.step_e2e, args.steps)
     clocks = sampler.summary()
     frame_tc = snapshot(job.frame) if cx.rank == 0 else None
+    samples = {mode: sample_pixels(torch, frame_tc)} if cx.rank == 0 else {}
     log(f"headline {ms_step:.2f} ms/frame, e2e {ms_e2e:.2f} ms")
 
     # ---- the same frame in the fp32 parity mode (CUDA-core FFMA): its cost, and the parity of the headline mode --------
@@ -665,6 +713,7 @@ def run_gpu(args):
             ms_fp32 = cx.timed(job.step, 1)
             if cx.rank == 0:
                 frame_ref = snapshot(job.frame)
+                samples["fp32"] = sample_pixels(torch, frame_ref)
                 fp32_leg = {"kernel": "mlp_fwd_fp32_kernel (CUDA cores, <=1e-4 parity mode)", "ms_per_frame": ms_fp32,
                             "value": N_RAYS / (ms_fp32 / 1000), "unit": "rays/s",
                             "algorithmic_tflops": flop_per_ray(K_INS) * N_RAYS / (ms_fp32 / 1000) / 1e12}
@@ -679,6 +728,7 @@ def run_gpu(args):
                 if cx.rank == 0:
                     n32, ms32 = kt32.totals().get(f"dmnerf_mlp_fwd[S={SC + NIMP},mode={_lib.MODE_TC32}]", (0, 0.0))
                     p32 = frame_parity(torch, frame_ref, job.frame)
+                    samples["tc32"] = sample_pixels(torch, job.frame)
                     tc32_leg = {"kernel": "mlp_fwd_x3_kernel (tcgen05, fp16 hi+lo split x3, fp32 accumulate)",
                                 "ms_per_frame": ms_tc32, "value": N_RAYS / (ms_tc32 / 1000), "unit": "rays/s",
                                 "algorithmic_tflops": flop_per_ray(K_INS) * N_RAYS / (ms_tc32 / 1000) / 1e12,
@@ -725,6 +775,7 @@ def run_gpu(args):
         del job4, m4
         log("c4 done")
 
+    cpu_arm = CpuArm(torch) if cx.rank == 0 and not args.no_cpu else None
     train = None
     if not args.no_train:
         ops.set_mode("bf16" if mode in TC_MODES else mode)   # training runs the bf16 chain (fp16 is inference-only)
@@ -738,10 +789,9 @@ def run_gpu(args):
     # colour blocks + 32 block labels) make the instance head confident, as a converged model's is ---------------------
     parity_trained = None
     if mode in TC_MODES and not args.no_parity and args.parity_train_steps > 0:
-        parity_trained = trained_parity(cx, job, args.parity_train_steps)
+        parity_trained = trained_parity(cx, job, args.parity_train_steps, cpu_arm)
         log("trained parity done")
 
-    cpu_arm = CpuArm(torch) if cx.rank == 0 and not args.no_cpu else None
     c5 = None
     if not args.no_extra:
         ops.set_mode(mode)
@@ -749,13 +799,13 @@ def run_gpu(args):
         log("c5 done")
 
     if cx.rank == 0:
-        emit(headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm,
+        emit(headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, samples,
                       dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, weak=weak, c4=c4, c5=c5, train=train)))
     if cx.world > 1:
         cx.dist.destroy_process_group()
 
 
-def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, legs):
+def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, samples, legs):
     args = cx.args
     peaks = load_peaks()
     steps = args.steps
@@ -798,6 +848,12 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
                    "sample": f"{CPU_SAMPLE_RAYS} of the frame's 307200 rays in tester.py-style 4096-ray chunks, one pass "
                              f"({secs:.1f} s), {cpu_arm.describe()}; a full frame extrapolates linearly to "
                              f"{N_RAYS / rps:.0f} s"}
+            if cpu_arm.last_render is not None and samples:
+                # the CPU arm's own output doubles as the checker: every mode's frame against the reference on those rays
+                legs["parity_vs_reference"] = {
+                    "what": f"each mode's 640x480 frame against the {cpu_arm.describe()} on the cpu_baseline's "
+                            f"{CPU_SAMPLE_RAYS} rays of that frame (same weights, same camera; rays from the reference's get_rays_k)",
+                    **{m: parity_vs_reference(cx.torch, cpu_arm.last_render, fr) for m, fr in samples.items()}}
             if train is not None:
                 t_rps, t_secs, t_anom = cpu_arm.train(1024)
                 train["cpu_baseline"] = {

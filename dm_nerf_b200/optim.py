@@ -56,8 +56,11 @@ class FlatAdam:
         """One flat gradient tensor per model, in the parameter buffer's layout.  The MLP backward hands autograd
         views of one zero-initialised flat buffer, which is then used in place; gradients that arrived any other way
         are gathered into a buffer of the same layout."""
-        out = []
-        for g in self.groups:
+        return [self.grad_buffer(i) for i in range(len(self.groups))]
+
+    def grad_buffer(self, i: int) -> torch.Tensor:
+        """The flat gradient tensor of model ``i`` alone (ready as soon as THAT model's backward has run)."""
+        for g in (self.groups[i],):
             grads = [p.grad for p in g["params"]]
             if any(x is None for x in grads):
                 raise RuntimeError("FlatAdam: a parameter has no gradient (call backward() first)")
@@ -72,8 +75,7 @@ class FlatAdam:
                     g["gather"] = torch.zeros(g["total"], dtype=torch.float32, device=g["p"].device)
                 flat = g["gather"]
                 torch._foreach_copy_([flat[o:o + n] for o, n in zip(g["offsets"], g["sizes"])], [x.reshape(-1) for x in grads])
-            out.append(flat)
-        return out
+            return flat
 
     def step(self, grad_buffers: Optional[List[torch.Tensor]] = None, grad_scale: float = 1.0) -> None:
         bufs = grad_buffers if grad_buffers is not None else self.grad_buffers()

@@ -53,6 +53,7 @@ class TrainStep:
         self.overlap = bool(self.graph_mode if overlap_assignment is None else overlap_assignment) and device_assignment
         self.reserved_sms = 1
         self._side = None
+        self._early_reduce = {}                # model index -> (flat gradient, pending all-reduce) started before _finish
         self._draw_step = self._draw_seed = None
         self._graph = self._static = self._static_out = None
         self._K_dev = None
@@ -139,10 +140,14 @@ class TrainStep:
             # ONE all-reduce per model on the backward's own flat gradient buffer (no gather / scatter copies); the
             # 1/world of the mean is applied inside the update
             world = dist.get_world_size() if dist.is_initialized() else 1
-            bufs = self.opt.grad_buffers()
+            early, self._early_reduce = self._early_reduce, {}
+            bufs = [early[i][0] if i in early else self.opt.grad_buffer(i) for i in range(len(self.opt.groups))]
             if world > 1:
-                for b in bufs:
-                    dist.all_reduce(b, op=dist.ReduceOp.SUM)
+                for i, b in enumerate(bufs):
+                    if i in early:
+                        early[i][1].wait()                    # started right after that model's backward (see below)
+                    else:
+                        dist.all_reduce(b, op=dist.ReduceOp.SUM)
             self.opt.step(bufs, grad_scale=1.0 / world)
         else:
             if self.flat is None:
@@ -204,6 +209,11 @@ class TrainStep:
         part_c = rgb_c if pen_c is None else rgb_c + pen_c
         self.opt.zero_grad(set_to_none=True)
         torch.autograd.backward([part_c, info["ins_coarse"]], [None, g_ins_c])
+        # the coarse model's gradient is complete here (render.py:68 detaches the fine samples): its all-reduce starts
+        # now, on NCCL's stream, and hides under the three-times-larger fine backward
+        if isinstance(self.opt, FlatAdam) and dist.is_initialized() and dist.get_world_size() > 1:
+            buf = self.opt.grad_buffer(0)
+            self._early_reduce[0] = (buf, dist.all_reduce(buf, op=dist.ReduceOp.SUM, async_op=True))
         rgb_f = img2mse(info["rgb_fine"], target_c)
         pen_f = info.get("emptiness_fine")
         main.wait_stream(side_f)
