@@ -586,7 +586,10 @@ def c5_leg(cx: Ctx, models, cpu_arm):
     if cx.rank == 0:
         peaks = load_peaks()
         c = K_INS + 5
-        ex_bytes = lambda s: 2 * s * c * 4 + 2 * (K_INS + 1) * 4 + s * c * 4 + s * 16      # SURVEY 8(d) + two int64 label maps
+        # both fields read, the edited field rewritten (an upper bound: only exchanged rows are written);
+        # the int64 label maps are no longer written on this path (manipulator drops them)
+        ex_bytes = lambda s: 2 * s * c * 4 + 2 * (K_INS + 1) * 4 + s * c * 4
+        ex_read = lambda s: 2 * s * c * 4 + 2 * (K_INS + 1) * 4
         ex_ms = sum(v[1] for k, v in totals.items() if k.startswith("dmnerf_exchange"))
         ex_n = sum(v[0] for k, v in totals.items() if k.startswith("dmnerf_exchange"))
         ex_s = sorted({int(k.split("S=")[1].rstrip("]")) for k in totals if k.startswith("dmnerf_exchange")})
@@ -602,7 +605,9 @@ def c5_leg(cx: Ctx, models, cpu_arm):
                "roofline_exchange": None if not ex_ms else {
                    "bound": "hbm", "achieved": gbps, "peak": peaks.get("hbm_gbs", 6400.0), "unit": "GB/s",
                    "frac": gbps / peaks.get("hbm_gbs", 6400.0), "ms_per_launch": ex_ms / ex_n, "launches": ex_n,
-                   "bytes_per_ray": {f"S={s}": ex_bytes(s) for s in ex_s}},
+                   "bytes_per_ray": {f"S={s}": ex_bytes(s) for s in ex_s},
+                   "frac_counting_reads_only": sum(ex_read(s) for s in ex_s) * N_RAYS * steps / (ex_ms / 1000) / 1e9
+                                               / peaks.get("hbm_gbs", 6400.0)},
                "stage_ms_per_view": {k: round(v[1] / steps, 3) for k, v in totals.items()}}
         if cpu_arm is not None:
             try:

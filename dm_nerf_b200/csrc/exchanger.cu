@@ -58,6 +58,11 @@ __device__ __forceinline__ int row_argmax_sigmoid(const float* row, int cnt) {
     return idx;
 }
 
+// kAsync: both chunks go global -> shared as 16-byte asynchronous copies (LDGSTS), every one of a warp's ~20 in flight
+// at once -- one DRAM round trip per chunk instead of five -- into rows of C floats.  Needs C odd (a lane scanning row
+// `lane` then hits bank (C*lane + j) mod 32, conflict-free without the padding column that would break the 16-byte
+// destination alignment) and 16-byte aligned ray blocks (S*C a multiple of 4).  Other shapes take the register path.
+template <bool kAsync>
 __global__ void __launch_bounds__(kExWarps * 32)
 exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, const float* __restrict__ ori_acc,
                 const float* __restrict__ tar_acc, int m, int first_label, int64_t n, int S, int C,
@@ -70,7 +75,7 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     const int64_t ray = item / chunks;
     const int c0 = static_cast<int>(item % chunks) * 32;
     const int cnt = min(32, S - c0);
-    const int CP = C | 1;
+    const int CP = kAsync ? C : (C | 1);
     const int L = C - 4;
     float* t_ori = smem + warp * (2 * 32 * CP + 32);
     float* t_tar = t_ori + 32 * CP;
@@ -82,6 +87,19 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     // staging: 8 elements of each field per lane in flight (a plain one-load-per-trip loop left every warp waiting on
     // ~37 dependent DRAM round trips per chunk: the kernel ran at 0.3 of the HBM roofline)
     constexpr int U = 8;
+    if constexpr (kAsync) {
+        const uint32_t so = static_cast<uint32_t>(__cvta_generic_to_shared(t_ori));
+        const uint32_t st = static_cast<uint32_t>(__cvta_generic_to_shared(t_tar));
+        for (int i = lane * 4; i < total; i += 128) {
+            if (i + 4 <= total) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(so + i * 4), "l"(g_ori + i) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(st + i * 4), "l"(g_tar + i) : "memory");
+            } else {                          // ragged last chunk (S not a multiple of 32): never read past the field
+                for (int j = i; j < total; ++j) { t_ori[j] = g_ori[j]; t_tar[j] = __ldg(g_tar + j); }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    } else
     for (int base = 0; base < total; base += 32 * U) {
         float va[U], vb[U];
 #pragma unroll
@@ -104,6 +122,7 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     // per-ray labels from the accumulated maps without their last ("empty") channel
     const int pix = warp_argmax_sigmoid(ori_acc + ray * L, L - 1, lane);
     const int t_pix = warp_argmax_sigmoid(tar_acc + ray * L, L - 1, lane);
+    if constexpr (kAsync) asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     int a = 0;
     if (lane < cnt) {
@@ -116,8 +135,8 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
         const int code = (t_lab == m ? 1 : 0) + (lab == m ? 2 : 0);
         if (fill || code == 1 || code == 3) a = 1;
         else if (code == 2) a = 2;
-        ori_label[at] = lab;
-        tar_label[at] = t_lab;
+        if (ori_label) ori_label[at] = lab;
+        if (tar_label) tar_label[at] = t_lab;
     }
     act[lane] = a;
     __syncwarp();
@@ -235,18 +254,26 @@ extern "C" int dmnerf_exchange(float* ori_raw, const float* tar_raw, const float
                                int move_label, int first_label, int64_t n, int s, int c, int64_t* ori_label,
                                int64_t* tar_label, void* stream) {
     if (n <= 0) return DMNERF_OK;
-    DM_REQUIRE(ori_raw && tar_raw && ori_acc && tar_acc && ori_label && tar_label, DMNERF_EINVAL,
-               "exchange: null pointer");
+    DM_REQUIRE(ori_raw && tar_raw && ori_acc && tar_acc, DMNERF_EINVAL, "exchange: null pointer");
+    DM_REQUIRE(ori_label || first_label, DMNERF_EINVAL, "exchange: ori_label may only be NULL when first_label != 0");
     DM_REQUIRE(s >= 1 && c >= 7 && c <= 128, DMNERF_EUNSUPPORTED, "exchange: n_samples %d / channels %d unsupported",
                s, c);
     if (n <= 0) return DMNERF_OK;
-    const int CP = c | 1;
+    const bool fast = (c & 1) && (static_cast<int64_t>(s) * c) % 4 == 0 &&
+                      ((reinterpret_cast<uintptr_t>(ori_raw) | reinterpret_cast<uintptr_t>(tar_raw)) & 15) == 0;
+    const int CP = fast ? c : (c | 1);
     const size_t smem = static_cast<size_t>(kExWarps) * (2 * 32 * CP + 32) * sizeof(float);
-    DM_CUDA(cudaFuncSetAttribute(exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t items = n * ((s + 31) / 32);
     const unsigned grid = static_cast<unsigned>((items + kExWarps - 1) / kExWarps);
-    exchange_kernel<<<grid, kExWarps * 32, smem, as_stream(stream)>>>(ori_raw, tar_raw, ori_acc, tar_acc, move_label,
-                                                                     first_label, n, s, c, ori_label, tar_label);
+    if (fast) {
+        DM_CUDA(cudaFuncSetAttribute(exchange_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        exchange_kernel<true><<<grid, kExWarps * 32, smem, as_stream(stream)>>>(ori_raw, tar_raw, ori_acc, tar_acc, move_label,
+                                                                               first_label, n, s, c, ori_label, tar_label);
+    } else {
+        DM_CUDA(cudaFuncSetAttribute(exchange_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        exchange_kernel<false><<<grid, kExWarps * 32, smem, as_stream(stream)>>>(ori_raw, tar_raw, ori_acc, tar_acc, move_label,
+                                                                                first_label, n, s, c, ori_label, tar_label);
+    }
     DM_LAUNCH_CHECK("exchange_kernel");
     return DMNERF_OK;
 }

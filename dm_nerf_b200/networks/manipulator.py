@@ -7,14 +7,18 @@ from .. import ops
 from .render import _query
 
 
-def exchanger(ori_raw, tar_raws, ori_raw_pred, tar_raw_preds, move_labels):
+def exchanger(ori_raw, tar_raws, ori_raw_pred, tar_raw_preds, move_labels, want_labels: bool = True):
     """manipulator.py:18-83.  Edits ``ori_raw`` in place, one kernel launch per move label (the
-    reference's label-order dependence is carried through the running per-sample label tensor)."""
+    reference's label-order dependence is carried through the running per-sample label tensor).
+    ``want_labels=False`` (``manipulator``, which drops them: :177, :201): the int64 label maps are only kept where a
+    later move label needs them, the returned ones are None."""
     if isinstance(move_labels, int):
         move_labels = [move_labels]
     ori_label, tar_label = None, None
+    last = len(move_labels) - 1
     for idx, m in enumerate(move_labels):
-        ori_label, tar_label = ops.exchange(ori_raw, tar_raws[idx], ori_raw_pred, tar_raw_preds[idx], int(m), ori_label)
+        ori_label, tar_label = ops.exchange(ori_raw, tar_raws[idx], ori_raw_pred, tar_raw_preds[idx], int(m), ori_label,
+                                            want_ori_label=want_labels or idx < last, want_tar_label=want_labels)
     return ori_raw, tar_raws, ori_label, tar_label
 
 
@@ -70,7 +74,7 @@ def manipulator(position_embedder, view_embedder, model_coarse, model_fine, ori_
         t_raw, t_z, tar_rgb, t_s, tar_acc = stage1(tar_rays)
         tar_raws.append(t_raw); tar_zs.append(t_z); tar_samples.append(t_s); tar_accs.append(tar_acc)
 
-    ori_raw, _, _, _ = exchanger(ori_raw, tar_raws, ori_acc, tar_accs, labels)
+    ori_raw, _, _, _ = exchanger(ori_raw, tar_raws, ori_acc, tar_accs, labels, want_labels=False)
 
     # stage 2: re-sample on the edited coarse field, merge every sample set, query the fine field
     _, ori_w, _, _ = manipulator_render(ori_raw, ori_z, ori_rays[1])
@@ -83,6 +87,6 @@ def manipulator(position_embedder, view_embedder, model_coarse, model_fine, ori_
             ori_raw2, _ = manipulator_nerf(ori_rays, pe, ve, model_fine, z_vals=ori_z_all)
         t_z_all = ops.sort_cat([tar_zs[idx], ori_s] + tar_samples)
         tar_raws[idx], _ = manipulator_nerf(tar_rays, pe, ve, model_fine, z_vals=t_z_all)
-    ori_raw2, _, _, _ = exchanger(ori_raw2, tar_raws, ori_acc, tar_accs, labels)
+    ori_raw2, _, _, _ = exchanger(ori_raw2, tar_raws, ori_acc, tar_accs, labels, want_labels=False)
     final_rgb, _, _, final_ins = manipulator_render(ori_raw2, ori_z_all, ori_rays[1])
     return final_rgb, final_ins, tar_rgb, tar_acc

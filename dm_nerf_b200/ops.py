@@ -452,16 +452,18 @@ def composite_penalized(raw, z, rays_d, flags: int, ins_detach: bool, tolerance:
 # ---------------------------------------------------------------------------------------------------
 
 
-def exchange(ori_raw, tar_raw, ori_acc, tar_acc, move_label: int, ori_label: Optional[torch.Tensor]):
-    """One move label, in place on ori_raw.  Returns (ori_label, tar_label) int64 [n,s]."""
+def exchange(ori_raw, tar_raw, ori_acc, tar_acc, move_label: int, ori_label: Optional[torch.Tensor],
+             want_ori_label: bool = True, want_tar_label: bool = True):
+    """One move label, in place on ori_raw.  Returns (ori_label, tar_label) int64 [n,s]; a label tensor the caller
+    does not want (``want_*_label=False``; ori only on the first label) is neither allocated nor written."""
     if not (ori_raw.is_cuda and ori_raw.dtype == torch.float32 and ori_raw.is_contiguous()):
         raise RuntimeError("exchanger: ori_raw must be a contiguous fp32 CUDA tensor (it is edited in place)")
     tar_raw, ori_acc, tar_acc = _f32(tar_raw, "tar_raw"), _f32(ori_acc, "ori_raw_pred"), _f32(tar_acc, "tar_raw_pred")
     n, s, c = ori_raw.shape
     first = ori_label is None
-    if first:
+    if first and want_ori_label:
         ori_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device)
-    tar_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device)
+    tar_label = torch.empty((n, s), dtype=torch.int64, device=ori_raw.device) if want_tar_label else None
     _timed_call(f"dmnerf_exchange[S={s}]", _lib.lib().dmnerf_exchange, _ptr(ori_raw), _ptr(tar_raw), _ptr(ori_acc),
                 _ptr(tar_acc), int(move_label), int(first), n, s, c, _ptr(ori_label), _ptr(tar_label), _stream())
     _count()

@@ -154,7 +154,8 @@ int  dmnerf_penalizer_bwd(const float* raw, const float* z, const float* depth, 
  * order (the reference's in-place order dependence is preserved through ori_label).
  * ori_raw [n,s,c] is edited in place; tar_raw [n,s,c]; ori_acc/tar_acc [n,c-4] (already sigmoided
  * accumulated maps); ori_label int64 [n,s] in/out (first_label!=0: initialise it from ori_raw);
- * tar_label int64 [n,s] out. */
+ * tar_label int64 [n,s] out.  A caller that does not keep the labels (manipulator, manipulator.py:177,201, drops them)
+ * may pass tar_label = NULL, and ori_label = NULL when first_label != 0: the 16 bytes per sample are then not written. */
 int  dmnerf_exchange(float* ori_raw, const float* tar_raw, const float* ori_acc, const float* tar_acc,
                      int move_label, int first_label, int64_t n, int s, int c, int64_t* ori_label,
                      int64_t* tar_label, void* stream);

