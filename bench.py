@@ -201,6 +201,55 @@ class CpuArm:
                 outs = []
         return n_rays / best, best
 
+    def stages_c(self, n_rays=32768):
+        """Stage-level CPU baseline: the plain-C restatement of compositing (render.py:6-28) and sample_pdf
+        (helpers.py:123-155), oracle/libdmnerf_oracle.so, on every host core -- one thread per core on disjoint ray
+        ranges (ctypes releases the GIL; rays are independent).  -> {stage: (rays/s, seconds)} or None when not built."""
+        import ctypes as C
+        from concurrent.futures import ThreadPoolExecutor
+        so = os.path.join(ROOT, "oracle", "libdmnerf_oracle.so")
+        if not os.path.exists(so):
+            return None
+        lib = C.CDLL(so)
+        p, i64, i32 = C.c_void_p, C.c_int64, C.c_int
+        lib.oracle_sample_pdf.argtypes = [p, p, p, i64, i64, i32, i32, p, p]
+        lib.oracle_sample_pdf.restype = None
+        lib.oracle_composite.argtypes = [p, p, p, i64, i32, i32, i32, p, p, p, p]
+        lib.oracle_composite.restype = None
+        torch = self.torch
+        g = torch.Generator().manual_seed(0)
+        s, c = SC + NIMP, K_INS + 5
+        raw = torch.randn(n_rays, s, c, generator=g)
+        z = torch.sort(torch.rand(n_rays, s, generator=g) * (FAR - NEAR) + NEAR, -1)[0].contiguous()
+        rd = torch.randn(n_rays, 3, generator=g)
+        rgb, dep, w, ins = torch.empty(n_rays, 3), torch.empty(n_rays), torch.empty(n_rays, s), torch.empty(n_rays, K_INS)
+        bins = torch.sort(torch.rand(n_rays, SC - 1, generator=g), -1)[0].contiguous()
+        wts = torch.rand(n_rays, SC - 2, generator=g)
+        u = torch.linspace(0, 1, NIMP)
+        zs = torch.empty(n_rays, NIMP)
+        cuts = [n_rays * i // self.cores for i in range(self.cores + 1)]
+
+        def comp(i):
+            a, b = cuts[i], cuts[i + 1]
+            lib.oracle_composite(raw[a:b].data_ptr(), z[a:b].data_ptr(), rd[a:b].data_ptr(), b - a, s, c, 1,
+                                 rgb[a:b].data_ptr(), dep[a:b].data_ptr(), w[a:b].data_ptr(), ins[a:b].data_ptr())
+
+        def samp(i):
+            a, b = cuts[i], cuts[i + 1]
+            lib.oracle_sample_pdf(bins[a:b].data_ptr(), wts[a:b].data_ptr(), u.data_ptr(), 0, b - a, SC - 1, NIMP,
+                                  zs[a:b].data_ptr(), None)
+
+        out = {}
+        with ThreadPoolExecutor(self.cores) as ex:
+            for name, fn in (("composite_fine_S192", comp), ("sample_pdf_128", samp)):
+                list(ex.map(fn, range(self.cores)))                       # warm-up (page faults)
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    list(ex.map(fn, range(self.cores)))
+                dt = (time.perf_counter() - t0) / 3
+                out[name] = (n_rays / dt, dt)
+        return out
+
     def train(self, n_rays, timed=2):
         """train_dmsr.py:30-66 on the host: dm_nerf (perturb = 1) + MSE + Hungarian instance loss + emptiness penalizer,
         backward, Adam.  One untimed warm-up step, then ``timed`` steps.  -> (rays/s, s/step, s/step with the
@@ -853,6 +902,19 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
                    "sample": f"{CPU_SAMPLE_RAYS} of the frame's 307200 rays in tester.py-style 4096-ray chunks, one pass "
                              f"({secs:.1f} s), {cpu_arm.describe()}; a full frame extrapolates linearly to "
                              f"{N_RAYS / rps:.0f} s"}
+            try:
+                st = cpu_arm.stages_c()
+                if st:
+                    gpu = {"composite_fine_S192": totals.get(f"dmnerf_composite_fwd[S={SC + NIMP}]"), "sample_pdf_128": totals.get("dmnerf_fine_z")}
+                    cpu["stages_c"] = {
+                        "what": f"plain-C restatement (oracle/dmnerf_oracle_c.c, gcc -O2, no FMA contraction) on {cpu_arm.cores} host "
+                                "threads, 32768 rays per call, best-effort mean of 3; the GPU figure beside it is this run's kernel "
+                                "(fine_z = CDF + 128 searches + merge for sample_pdf)",
+                        **{k: {"cpu_rays_per_s": v[0], "cpu_ms_per_32768_rays": v[1] * 1e3,
+                               "gpu_rays_per_s": (rays_rank0 * steps / (gpu[k][1] / 1000)) if gpu.get(k) and gpu[k][1] else None}
+                           for k, v in st.items()}}
+            except Exception as e:                              # pragma: no cover
+                cpu["stages_c"] = {"error": repr(e)}
             if cpu_arm.last_render is not None and samples:
                 # the CPU arm's own output doubles as the checker: every mode's frame against the reference on those rays
                 legs["parity_vs_reference"] = {

@@ -149,6 +149,8 @@ extern "C" int dmnerf_mlp_bwd(const void* packed, const void* acts, const float*
     if (mode == DMNERF_MODE_BF16)
         return launch_mlp_bwd_bf16(packed, acts, d_raw, n_points, ins_num, grads, workspace, tc_debug_flags(),
                                    as_stream(stream));
+    DM_REQUIRE(mode != DMNERF_MODE_F16 && mode != DMNERF_MODE_TC32, DMNERF_EUNSUPPORTED,
+               "mlp_bwd: mode %d is an inference-only chain (train in DMNERF_MODE_BF16 or DMNERF_MODE_FP32)", mode);
     DM_REQUIRE(mode == DMNERF_MODE_FP32, DMNERF_EUNSUPPORTED, "mlp_bwd: unknown mode %d", mode);
     return launch_mlp_bwd_fp32(static_cast<const float*>(packed), static_cast<const float*>(acts), d_raw, n_points,
                                ins_num, grads, as_stream(stream));

@@ -14,8 +14,10 @@
 /* helpers.py:123-155; bins [n,nb], weights [n,nb-1], u [n,ns] (u_stride 0 = shared row). */
 void oracle_sample_pdf(const float* bins, const float* weights, const float* u, int64_t u_stride, int64_t n,
                        int nb, int ns, float* z_out, int64_t* inds_out) {
-    float cdf[1024], w[1024];
+    /* rays are independent and the function keeps no state outside its stack: bench.py's stage-level CPU baseline calls
+     * it from one host thread per core on disjoint ray ranges (ctypes releases the GIL; libgomp is not in this image) */
     for (int64_t r = 0; r < n; ++r) {
+        float cdf[1024], w[1024];
         const float* b = bins + r * nb;
         double tot = 0.0;
         for (int j = 0; j < nb - 1; ++j) { w[j] = weights[r * (nb - 1) + j] + 1e-5f; tot += (double)w[j]; }   /* :125 */

@@ -125,3 +125,46 @@ def test_hungarian_without_assignment_is_defined():
     for b in (1, 2):
         assert col[b].tolist() == list(range(k))
     assert ((col >= 0) & (col < k)).all()
+
+
+def test_inference_only_modes_refuse_training_calls():
+    """DMNERF_MODE_F16 / DMNERF_MODE_TC32 are inference chains: size queries for a stash or a backward workspace say -1,
+    a forward that is handed an activation stash and a backward in those modes return DMNERF_EUNSUPPORTED with a message,
+    an unknown mode is refused everywhere, and the stream keeps working afterwards.  exchange: ori_label may be NULL
+    only on the first label."""
+    from dm_nerf_b200 import _lib
+    lib = _lib.lib()
+    codes = _codes()
+    einval, eunsup = codes["DMNERF_EINVAL"], codes["DMNERF_EUNSUPPORTED"]
+    k, n, s = 8, 4, 16
+    sd = orc.init_params(k, 3)
+    params = [sd[name].to(DEV).contiguous() for name in __import__("dm_nerf_b200.ops", fromlist=["PARAM_ORDER"]).PARAM_ORDER]
+    arr = (C.c_void_p * len(params))(*[p.data_ptr() for p in params])
+    o, d = torch.rand(n, 3, device=DEV), torch.randn(n, 3, device=DEV)
+    z = torch.sort(torch.rand(n, s, device=DEV) * 5 + 2, -1)[0]
+    raw = torch.empty(n, s, k + 5, device=DEV)
+    scratch = torch.empty(1 << 20, dtype=torch.uint8, device=DEV)
+    for mode in (_lib.MODE_F16, _lib.MODE_TC32):
+        nbytes = lib.dmnerf_packed_bytes(k, mode)
+        assert nbytes > 0
+        assert lib.dmnerf_acts_bytes(n * s, k, mode) == -1 and lib.dmnerf_bwd_workspace_bytes(n * s, k, mode) == -1
+        packed = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+        assert lib.dmnerf_weights_pack(arr, k, mode, _p(packed), _st()) == 0
+        rc = lib.dmnerf_mlp_fwd(_p(o), _p(d), _p(z), n, s, _p(packed), k, mode, _p(raw), _p(scratch), _st())
+        assert rc == eunsup and "inference" in _lib.last_error().lower(), (rc, _lib.last_error())
+        rc = lib.dmnerf_mlp_bwd(_p(packed), _p(scratch), _p(raw), n * s, k, mode, arr, _p(None), _st())
+        assert rc == eunsup and _lib.last_error(), (rc, _lib.last_error())
+        assert lib.dmnerf_mlp_fwd(_p(o), _p(d), _p(z), n, s, _p(packed), k, mode, _p(raw), _p(None), _st()) == 0
+        torch.cuda.synchronize()
+        assert bool(torch.isfinite(raw).all())
+    assert lib.dmnerf_packed_bytes(k, 7) == -1
+    rc = lib.dmnerf_mlp_fwd(_p(o), _p(d), _p(z), n, s, _p(scratch), k, 7, _p(raw), _p(None), _st())
+    assert rc == eunsup and "mode" in _lib.last_error().lower()
+    # exchange without label maps: tar_label NULL is fine, ori_label NULL only with first_label != 0
+    c = k + 5
+    ori, tar = torch.randn(n, s, c, device=DEV), torch.randn(n, s, c, device=DEV)
+    acc = torch.rand(n, k + 1, device=DEV)
+    assert lib.dmnerf_exchange(_p(ori), _p(tar), _p(acc), _p(acc), 1, 1, n, s, c, _p(None), _p(None), _st()) == 0
+    rc = lib.dmnerf_exchange(_p(ori), _p(tar), _p(acc), _p(acc), 1, 0, n, s, c, _p(None), _p(None), _st())
+    assert rc == einval and "ori_label" in _lib.last_error(), (rc, _lib.last_error())
+    torch.cuda.synchronize()
