@@ -547,6 +547,29 @@ def test_render_bf16_psnr_and_labels():
     assert float((a["depth"] - b["depth"]).abs().mean()) < 2e-2
 
 
+@pytest.mark.parametrize("k", [1, 5, 123])
+def test_tensor_modes_at_the_edges_of_the_shape_contract(k):
+    """ins_num = 1 (C = 6, head layer padded to 16 columns), 5, and 123 (C = 128: the widest head layer, a 64 KB output
+    stage per tile), on ragged point counts (tile tails inside a ray, a single point): fp16 and tc32 against the fp32 mode."""
+    from dm_nerf_b200 import ops
+    m = make_model(k, 31)
+    gen = torch.Generator().manual_seed(9)
+    try:
+        for n, s in ((1, 1), (2, 65), (7, 37), (129, 3)):
+            o = ((torch.rand(n, 3, generator=gen) - 0.5) * 2).to(DEV)
+            d = torch.randn(n, 3, generator=gen).to(DEV)
+            z = torch.sort(torch.rand(n, s, generator=gen) * 11 + 4, -1)[0].to(DEV)
+            with torch.no_grad():
+                ops.set_mode("fp32"); ref = m.query_rays(o, d, z)
+                ops.set_mode("tc32"); t32 = m.query_rays(o, d, z)
+                ops.set_mode("fp16"); f16 = m.query_rays(o, d, z)
+            assert t32.shape == ref.shape == (n, s, k + 5)
+            assert float((t32 - ref).abs().max()) <= 1e-5, (k, n, s, float((t32 - ref).abs().max()))
+            assert float((f16 - ref).abs().max()) <= 1e-2, (k, n, s, float((f16 - ref).abs().max()))
+    finally:
+        ops.set_mode("fp32")
+
+
 def test_render_tensor_modes_on_a_trained_field():
     """north_star's reduced-precision clause (PSNR within 0.05 dB, label agreement >= 99.9 %), WITHOUT a margin filter,
     on a 160x120 frame of a field trained here (600 graph steps on a 16-block synthetic view make the instance head
