@@ -10,6 +10,7 @@
 //   fill    :  pix == m && lab != m                                    (:40-42)
 //   code    :  [tar_lab == m] + 2*[lab == m]; 1,3 -> take target row, 2 -> zero row   (:64-81)
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace dmnerf {
 
@@ -58,10 +59,12 @@ __device__ __forceinline__ int row_argmax_sigmoid(const float* row, int cnt) {
     return idx;
 }
 
-// kAsync: both chunks go global -> shared as 16-byte asynchronous copies (LDGSTS), every one of a warp's ~20 in flight
-// at once -- one DRAM round trip per chunk instead of five -- into rows of C floats.  Needs C odd (a lane scanning row
-// `lane` then hits bank (C*lane + j) mod 32, conflict-free without the padding column that would break the 16-byte
-// destination alignment) and 16-byte aligned ray blocks (S*C a multiple of 4).  Other shapes take the register path.
+// kAsync: both chunks go global -> shared as ONE bulk asynchronous copy each (cp.async.bulk, the TMA engine; lane 0
+// issues, the warp waits on its own mbarrier) into rows of C floats: one DRAM round trip per chunk instead of five,
+// two instructions instead of ~80 per lane, and no L1 miss-queue limit on what an SM has in flight (the 16-byte LDGSTS
+// variant of this path stopped at 0.47 of the HBM peak on exactly that).  Needs C odd (a lane scanning row `lane` then
+// hits bank (C*lane + j) mod 32, conflict-free without the padding column that would break the 16-byte alignment)
+// and 16-byte aligned ray blocks (S*C a multiple of 4).  Other shapes take the register path.
 template <bool kAsync>
 __global__ void __launch_bounds__(kExWarps * 32)
 exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, const float* __restrict__ ori_acc,
@@ -70,16 +73,29 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     extern __shared__ float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int chunks = (S + 31) / 32;
-    const int64_t item = static_cast<int64_t>(blockIdx.x) * kExWarps + warp;
-    if (item >= n * chunks) return;
+    // a warp walks (ray, chunk) items grid-stride: the grid is sized to what is resident at once, so a warp's shared
+    // memory slot is reused instead of a new 128-thread block being scheduled for every four chunks
+    const int64_t n_items = n * chunks, stride = static_cast<int64_t>(gridDim.x) * kExWarps;
+    uint32_t bar_phase = 0;
+    if constexpr (kAsync) {
+        if (lane == 0) {
+            const int cp0 = C;
+            ptx::mbar_init(static_cast<uint32_t>(__cvta_generic_to_shared(smem + warp * (2 * 32 * cp0 + 36) + 2 * 32 * cp0 + 32)), 1);
+            ptx::fence_barrier_init();
+        }
+        __syncwarp();
+    }
+  for (int64_t item = static_cast<int64_t>(blockIdx.x) * kExWarps + warp; item < n_items; item += stride) {
+    __syncwarp();                                             // the previous item's readers are done with the slot
     const int64_t ray = item / chunks;
     const int c0 = static_cast<int>(item % chunks) * 32;
     const int cnt = min(32, S - c0);
     const int CP = kAsync ? C : (C | 1);
     const int L = C - 4;
-    float* t_ori = smem + warp * (2 * 32 * CP + 32);
+    float* t_ori = smem + warp * (2 * 32 * CP + 36);
     float* t_tar = t_ori + 32 * CP;
     int* act = reinterpret_cast<int*>(t_tar + 32 * CP);
+    const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(act + 32));     // this warp's mbarrier (kAsync)
     float* g_ori = ori_raw + (ray * S + c0) * static_cast<int64_t>(C);
     const float* g_tar = tar_raw + (ray * S + c0) * static_cast<int64_t>(C);
     const int total = cnt * C;
@@ -90,15 +106,15 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     if constexpr (kAsync) {
         const uint32_t so = static_cast<uint32_t>(__cvta_generic_to_shared(t_ori));
         const uint32_t st = static_cast<uint32_t>(__cvta_generic_to_shared(t_tar));
-        for (int i = lane * 4; i < total; i += 128) {
-            if (i + 4 <= total) {
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(so + i * 4), "l"(g_ori + i) : "memory");
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(st + i * 4), "l"(g_tar + i) : "memory");
-            } else {                          // ragged last chunk (S not a multiple of 32): never read past the field
-                for (int j = i; j < total; ++j) { t_ori[j] = g_ori[j]; t_tar[j] = __ldg(g_tar + j); }
-            }
+        const int whole = total & ~3;                         // bulk copies move multiples of 16 bytes
+        if (lane == 0) {
+            ptx::fence_proxy_async_smem();                    // the previous item's generic reads of the slot come first
+            ptx::mbar_arrive_expect_tx(bar, 2u * whole * 4u);
+            ptx::bulk_g2s(so, g_ori, whole * 4u, bar);
+            ptx::bulk_g2s(st, g_tar, whole * 4u, bar);
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        // ragged last chunk (S not a multiple of 32): the odd floats by hand, never reading past the field
+        for (int j = whole + lane; j < total; j += 32) { t_ori[j] = g_ori[j]; t_tar[j] = __ldg(g_tar + j); }
     } else
     for (int base = 0; base < total; base += 32 * U) {
         float va[U], vb[U];
@@ -122,7 +138,7 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     // per-ray labels from the accumulated maps without their last ("empty") channel
     const int pix = warp_argmax_sigmoid(ori_acc + ray * L, L - 1, lane);
     const int t_pix = warp_argmax_sigmoid(tar_acc + ray * L, L - 1, lane);
-    if constexpr (kAsync) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if constexpr (kAsync) { ptx::mbar_wait(bar, bar_phase); bar_phase ^= 1u; }
     __syncwarp();
     int a = 0;
     if (lane < cnt) {
@@ -143,7 +159,7 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
     // rows that keep their values are not touched; most chunks have none to rewrite
     int any = 0;
     if (lane < cnt) any = act[lane];
-    if (__ballot_sync(0xffffffffu, any != 0) == 0u) return;
+    if (__ballot_sync(0xffffffffu, any != 0) == 0u) continue;
     for (int i = lane; i < total; i += 32) {
         const int r = static_cast<int>(__umulhi(static_cast<unsigned>(i), magic));
         const int col = i - r * C;
@@ -151,6 +167,7 @@ exchange_kernel(float* __restrict__ ori_raw, const float* __restrict__ tar_raw, 
         if (ar == 1) g_ori[i] = t_tar[r * CP + col];
         else if (ar == 2) g_ori[i] = t_ori[r * CP + col] * 0.0f;
     }
+  }
 }
 
 __global__ void label_argmax_kernel(const float* __restrict__ ins, int64_t n, int K, uint8_t* __restrict__ labels) {
@@ -262,9 +279,17 @@ extern "C" int dmnerf_exchange(float* ori_raw, const float* tar_raw, const float
     const bool fast = (c & 1) && (static_cast<int64_t>(s) * c) % 4 == 0 &&
                       ((reinterpret_cast<uintptr_t>(ori_raw) | reinterpret_cast<uintptr_t>(tar_raw)) & 15) == 0;
     const int CP = fast ? c : (c | 1);
-    const size_t smem = static_cast<size_t>(kExWarps) * (2 * 32 * CP + 32) * sizeof(float);
+    const size_t smem = static_cast<size_t>(kExWarps) * (2 * 32 * CP + 36) * sizeof(float);
     const int64_t items = n * ((s + 31) / 32);
-    const unsigned grid = static_cast<unsigned>((items + kExWarps - 1) / kExWarps);
+    static int sm_count = 0;
+    if (sm_count == 0) {
+        int dev = 0;
+        DM_CUDA(cudaGetDevice(&dev));
+        DM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int64_t resident = static_cast<int64_t>(sm_count) * (smem ? (220 * 1024) / static_cast<int64_t>(smem) : 1);
+    const int64_t blocks = (items + kExWarps - 1) / kExWarps;
+    const unsigned grid = static_cast<unsigned>(blocks < resident ? blocks : resident);
     if (fast) {
         DM_CUDA(cudaFuncSetAttribute(exchange_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         exchange_kernel<true><<<grid, kExWarps * 32, smem, as_stream(stream)>>>(ori_raw, tar_raw, ori_acc, tar_acc, move_label,
