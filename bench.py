@@ -796,6 +796,19 @@ def run_gpu(args):
             ops.set_mode(mode)
         log("fp32 frame + parity done")
 
+    # ---- the same frame with bf16 operands (round 1's headline mode, the training chain): speed only -- its parity is in
+    # parity_trained.other_modes; it misses the label clause, which is why it is not the headline ---------------------------
+    bf16_leg = None
+    if mode == "fp16" and not args.no_extra:
+        ops.set_mode("bf16")
+        try:
+            job.step()
+            ms_b = cx.timed(job.step, max(2, min(args.steps, 5)))
+            bf16_leg = {"ms_per_frame": ms_b, "value": N_RAYS / (ms_b / 1000), "unit": "rays/s",
+                        "note": "same kernel template, bf16 operands; 99.7 % label agreement on the trained field (clause: 99.9 %)"}
+        finally:
+            ops.set_mode(mode)
+
     # ---- weak figure: one whole frame per rank (a sweep's views shard trivially), no gather ---------------------------
     weak = None
     if cx.world > 1 and not args.no_extra:
@@ -854,7 +867,7 @@ def run_gpu(args):
 
     if cx.rank == 0:
         emit(headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, samples,
-                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, weak=weak, c4=c4, c5=c5, train=train)))
+                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, bf16_mode=bf16_leg, weak=weak, c4=c4, c5=c5, train=train)))
     if cx.world > 1:
         cx.dist.destroy_process_group()
 
