@@ -14,6 +14,7 @@
 
 namespace dmnerf {
 
+int tc_debug_flags();
 constexpr int kExWarps = 4;
 
 // argmax over sigmoid(v[0..cnt)) spread across the warp (lane j holds channels j, j+32, ...).
@@ -40,13 +41,22 @@ __device__ __forceinline__ int warp_argmax_sigmoid(const float* v, int cnt, int 
 // tie or win; with s == 1.0f (saturation, x >~ 17.33: the reference's tie case) every logit >= 16 is a candidate, no other
 // can round to 1.  Typically one candidate per row instead of K+1 expf + IEEE divisions.
 __device__ __forceinline__ int row_argmax_sigmoid(const float* row, int cnt) {
-    float xmax = row[0];
-    for (int j = 1; j < cnt; ++j) xmax = fmaxf(xmax, row[j]);
+    // one pass for the largest logit (first index) and the runner-up; the candidate pass below only runs when the
+    // runner-up can reach the largest sigmoid VALUE (ties, saturation) -- otherwise the first maximum is the answer
+    float xmax = row[0], x2 = -INFINITY;
+    int i1 = 0;
+#pragma unroll 4
+    for (int j = 1; j < cnt; ++j) {
+        const float x = row[j];
+        if (x > xmax) { x2 = xmax; xmax = x; i1 = j; }
+        else x2 = fmaxf(x2, x);
+    }
     const float smax = sigmoidf_ref(xmax);
     // xmax < -80: sigmoid(xmax) is denormal or 0 and the ulp argument above does not hold -> every channel is a
     // candidate (all-zero rows then give index 0, like the reference's argmax over zeros)
     const float thr = xmax < -80.0f ? -INFINITY
                       : (smax >= 1.0f ? fminf(16.0f, xmax) : xmax - 1.9073486e-6f / (1.0f - smax));
+    if (x2 < thr) return i1;
     float best = -1.0f;
     int idx = 0;
     for (int j = 0; j < cnt; ++j) {
