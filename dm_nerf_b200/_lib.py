@@ -134,6 +134,10 @@ _SIGNATURES = {
     "dmnerf_debug_counters_tc32": (_int, [_p]),
     "dmnerf_hungarian": (_int, [_p, _int, _i64, _int, _p, _int, _p, _p]),
     "dmnerf_hungarian_infeasible": (_int, [C.POINTER(_int), _p]),
+    "dmnerf_segment_sum": (_int, [_p, _p, _i64, _int, _int, _p, _p]),
+    "dmnerf_segment_sum3": (_int, [_p, _p, _p, _i64, _int, _int, _p, _p]),
+    "dmnerf_assign_scores": (_int, [_p, _p, _i64, _int, _p, _p, _p, _p, _p]),
+    "dmnerf_assign_loss_grad": (_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _int, _p, _p, _p, _p]),
     "dmnerf_selftest_issue_cost": (_int, [_int, _int, _p, _p]),
     "dmnerf_debug_flags": (_int, [_int]),
     "dmnerf_reserve_sms": (_int, [_int]),

@@ -149,6 +149,212 @@ hungarian_kernel(const float* __restrict__ scores, int64_t mat_stride, int ld, c
 
 using namespace dmnerf;
 
+// ---- label-wise sums for the assignment costs --------------------------------------------------------------------
+// The reference's cost matrices (evaluator.py:55-63) reduce a [K_gt, K_pred, N] broadcast over the rays; with a ONE-HOT
+// ground truth that is, per predicted channel, the sum of a per-ray quantity over the rays of each ground-truth slot:
+//   out[g][j] = sum over rays n with slot[n] == g of x[n][j]
+// (N*K additions instead of the N*K*K multiply-adds of a dense [K,N]x[N,K] product -- this runs on the ONE SM the
+// persistent MLP kernels leave free, where the dense product took 0.46 ms at K = 93).  One block per 32 channels; its
+// eight warps take an eighth of the rays each into their own shared-memory accumulators, which are then added in a fixed
+// order: the result does not depend on scheduling.  Column sums of x are sum_g out[g][j] (every ray has one slot).
+namespace dmnerf {
+constexpr int kSegWarps = 8;
+__global__ void __launch_bounds__(kSegWarps * 32)
+segment_sum_kernel(const float* __restrict__ x, const int64_t* __restrict__ slot, int64_t n, int k, int n_slots,
+                   float* __restrict__ out) {
+    extern __shared__ float s_acc[];             // [kSegWarps][n_slots][32]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x * 32 + lane;
+    float* acc = s_acc + static_cast<size_t>(warp) * n_slots * 32;
+    for (int g = 0; g < n_slots; ++g) acc[g * 32 + lane] = 0.f;
+    const int64_t per = (n + kSegWarps - 1) / kSegWarps;
+    const int64_t lo = warp * per, hi = lo + per < n ? lo + per : n;
+    constexpr int U = 16;                                          // loads in flight per lane
+    for (int64_t r = lo; r < hi; r += U) {
+        float v[U];
+        int g[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const bool ok = r + u < hi;
+            g[u] = ok ? static_cast<int>(__ldg(slot + r + u)) : -1;
+            v[u] = (ok && j < k) ? __ldg(x + (r + u) * k + j) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (g[u] >= 0 && g[u] < n_slots) acc[g[u] * 32 + lane] += v[u];    // in ray order: a defined summation order
+    }
+    __syncthreads();
+    if (j < k) {
+        for (int g = warp; g < n_slots; g += kSegWarps) {
+            float t = s_acc[g * 32 + lane];
+            for (int w = 1; w < kSegWarps; ++w) t += s_acc[(static_cast<size_t>(w) * n_slots + g) * 32 + lane];
+            out[static_cast<int64_t>(g) * k + j] = t;
+        }
+    }
+}
+
+// The three label-wise sums the assignment costs need of ONE prediction map p [n,k] in one pass:
+//   out[0][g][j] = sum p,  out[1][g][j] = sum log(p + 1e-8),  out[2][g][j] = sum log(1 - p + 1e-8)   (evaluator.py:55-66)
+// over the rays of slot g, which the caller lists: perm [n] = ray indices ordered by slot (stable), offs [n_slots + 1] =
+// where each slot's rays start.  One warp per slot walks its rays in that order, lanes = channels: every (slot, channel)
+// sum is an independent chain in a defined order, n_slots warps run in parallel, nothing is staged.  Same logf as ATen's
+// log kernel.
+constexpr int kSeg3Warps = 4;
+__global__ void __launch_bounds__(kSeg3Warps * 32)
+segment_sum3_kernel(const float* __restrict__ p, const int64_t* __restrict__ perm, const int64_t* __restrict__ offs, int k,
+                    int n_slots, float* __restrict__ out) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * kSeg3Warps + warp;
+    if (g >= n_slots) return;
+    const int64_t lo = __ldg(offs + g), hi = __ldg(offs + g + 1);
+    const int64_t plane = static_cast<int64_t>(n_slots) * k;
+    for (int j = lane; j < k; j += 32) {
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+        constexpr int U = 8;
+        for (int64_t r = lo; r < hi; r += U) {
+            float v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) v[u] = r + u < hi ? __ldg(p + __ldg(perm + r + u) * k + j) : -1.f;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (v[u] >= 0.f) {                 // probabilities: the padding marker cannot occur in the data
+                    a0 += v[u];
+                    a1 += logf(v[u] + 1e-8f);
+                    a2 += logf(1.0f - v[u] + 1e-8f);
+                }
+            }
+        }
+        out[static_cast<int64_t>(g) * k + j] = a0;
+        out[plane + static_cast<int64_t>(g) * k + j] = a1;
+        out[2 * plane + static_cast<int64_t>(g) * k + j] = a2;
+    }
+}
+
+}  // namespace dmnerf
+using namespace dmnerf;
+
+extern "C" int dmnerf_segment_sum3(const float* p, const int64_t* perm, const int64_t* offs, int64_t n, int k, int n_slots,
+                                   float* out, void* stream) {
+    DM_REQUIRE(p && perm && offs && out, DMNERF_EINVAL, "segment_sum3: null pointer");
+    DM_REQUIRE(n >= 0 && k >= 1 && n_slots >= 1, DMNERF_EUNSUPPORTED, "segment_sum3: k=%d n_slots=%d", k, n_slots);
+    segment_sum3_kernel<<<(n_slots + kSeg3Warps - 1) / kSeg3Warps, kSeg3Warps * 32, 0, as_stream(stream)>>>(p, perm, offs, k,
+                                                                                                         n_slots, out);
+    DM_LAUNCH_CHECK("segment_sum3_kernel");
+    return DMNERF_OK;
+}
+
+// ---- the instance loss around the assignment, as three launches instead of ~130 small ATen kernels ------------------
+// (networks/evaluator.py:19-37, 55-74 with a one-hot ground truth).  s3 = [tp | sum log p | sum log(1-p)] per (slot, channel)
+// from segment_sum3_kernel; cnt[g] = rays of slot g.
+namespace dmnerf {
+
+// scores[g][j] = ce + siou (evaluator.py:64-66, 68-73), also kept separately for the loss; colsum[0][j] = sum_n p[n][j],
+// colsum[1][j] = sum_n log(1 - p[n][j] + 1e-8) (both as sums over the slots: every ray has exactly one).
+__global__ void __launch_bounds__(128)
+assign_scores_kernel(const float* __restrict__ s3, const float* __restrict__ cnt, float n, int k, float* __restrict__ scores,
+                     float* __restrict__ ce, float* __restrict__ siou, float* __restrict__ colsum) {
+    const int g = blockIdx.x;
+    const int64_t plane = static_cast<int64_t>(k) * k;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        float P = 0.f, Q = 0.f;
+        for (int r = 0; r < k; ++r) { P += s3[r * k + j]; Q += s3[2 * plane + r * k + j]; }
+        if (g == 0) { colsum[j] = P; colsum[k + j] = Q; }
+        const float tp = s3[g * k + j];
+        const float c = -((s3[plane + g * k + j] - s3[2 * plane + g * k + j]) + Q) / n;
+        const float fp = P - tp, fn = cnt[g] - tp;
+        const float si = 1.0f - tp / (tp + fp + fn + 1e-6f);
+        ce[g * k + j] = c;
+        siou[g * k + j] = si;
+        scores[g * k + j] = c + si;
+    }
+}
+
+// losses = {total, valid_ce, invalid_ce, valid_siou} (evaluator.py:27-37) for the assignment col (the first n_valid entries:
+// column matched to row r; the rest: the unmatched columns); rowof[j] = the row column j is matched to, or -1.
+__global__ void __launch_bounds__(128)
+assign_loss_kernel(const float* __restrict__ ce, const float* __restrict__ siou, const float* __restrict__ colsum,
+                   const int* __restrict__ col, const int* __restrict__ n_valid_ptr, float n, int k, float* __restrict__ losses,
+                   int* __restrict__ rowof) {
+    const int nv = *n_valid_ptr;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) rowof[j] = -1;
+    __syncthreads();
+    for (int r = threadIdx.x; r < nv && r < k; r += blockDim.x) rowof[col[r]] = r;
+    if (threadIdx.x == 0) {
+        float a = 0.f, b = 0.f, c = 0.f;
+        for (int r = 0; r < nv && r < k; ++r) { a += ce[r * k + col[r]]; b += siou[r * k + col[r]]; }
+        for (int r = nv; r < k; ++r) c += colsum[col[r]];
+        const float vce = a / static_cast<float>(nv), vsi = b / static_cast<float>(nv);
+        const float ice = k > nv ? c / (n * static_cast<float>(k - nv)) : 0.f;
+        losses[0] = vce + ice + vsi; losses[1] = vce; losses[2] = ice; losses[3] = vsi;
+    }
+}
+
+// d(total loss) / d p[n][j]
+__global__ void __launch_bounds__(256)
+assign_grad_kernel(const float* __restrict__ p, const int64_t* __restrict__ slot, const float* __restrict__ s3,
+                   const float* __restrict__ colsum, const float* __restrict__ cnt, const int* __restrict__ rowof,
+                   const int* __restrict__ n_valid_ptr, int64_t n, int k, float* __restrict__ grad) {
+    const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= n * k) return;
+    const int64_t ray = idx / k;
+    const int j = static_cast<int>(idx - ray * k);
+    const int nv = *n_valid_ptr;
+    const int r = rowof[j];
+    const float fn_ = static_cast<float>(n);
+    float g;
+    if (r < 0) {
+        g = k > nv ? 1.0f / (fn_ * static_cast<float>(k - nv)) : 0.f;
+    } else {
+        const float pv = p[idx];
+        const bool m = static_cast<int>(slot[ray]) == r;
+        const float pe = pv + 1e-8f, qe = 1.0f - pv + 1e-8f;
+        const float d_ce = -((m ? 1.0f / pe + 1.0f / qe : 0.f) - 1.0f / qe) / fn_;
+        const float tp = s3[r * k + j];
+        const float D = tp + (colsum[j] - tp) + (cnt[r] - tp) + 1e-6f;
+        const float d_si = -((m ? D : 0.f) - tp * (m ? 0.f : 1.0f)) / (D * D);
+        g = (d_ce + d_si) / static_cast<float>(nv);
+    }
+    grad[idx] = g;
+}
+
+}  // namespace dmnerf
+
+extern "C" int dmnerf_assign_scores(const float* s3, const float* cnt, int64_t n, int k, float* scores, float* ce, float* siou,
+                                    float* colsum, void* stream) {
+    DM_REQUIRE(s3 && cnt && scores && ce && siou && colsum, DMNERF_EINVAL, "assign_scores: null pointer");
+    DM_REQUIRE(k >= 1 && k <= kHungMaxN && n >= 1, DMNERF_EUNSUPPORTED, "assign_scores: k=%d n=%lld", k, (long long)n);
+    assign_scores_kernel<<<k, 128, 0, as_stream(stream)>>>(s3, cnt, static_cast<float>(n), k, scores, ce, siou, colsum);
+    DM_LAUNCH_CHECK("assign_scores_kernel");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_assign_loss_grad(const float* p, const int64_t* slot, const float* s3, const float* ce, const float* siou,
+                                       const float* colsum, const float* cnt, const int* col, const int* n_valid, int64_t n,
+                                       int k, float* losses, int* rowof, float* grad, void* stream) {
+    DM_REQUIRE(p && slot && s3 && ce && siou && colsum && cnt && col && n_valid && losses && rowof, DMNERF_EINVAL,
+               "assign_loss_grad: null pointer");
+    DM_REQUIRE(k >= 1 && k <= kHungMaxN && n >= 1, DMNERF_EUNSUPPORTED, "assign_loss_grad: k=%d n=%lld", k, (long long)n);
+    assign_loss_kernel<<<1, 128, 0, as_stream(stream)>>>(ce, siou, colsum, col, n_valid, static_cast<float>(n), k, losses, rowof);
+    if (grad) {
+        const int64_t total = n * k;
+        assign_grad_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, as_stream(stream)>>>(p, slot, s3, colsum, cnt,
+                                                                                                  rowof, n_valid, n, k, grad);
+    }
+    DM_LAUNCH_CHECK("assign_loss_grad");
+    return DMNERF_OK;
+}
+
+extern "C" int dmnerf_segment_sum(const float* x, const int64_t* slot, int64_t n, int k, int n_slots, float* out, void* stream) {
+    DM_REQUIRE(x && slot && out, DMNERF_EINVAL, "segment_sum: null pointer");
+    DM_REQUIRE(n >= 0 && k >= 1 && n_slots >= 1 && n_slots <= 128, DMNERF_EUNSUPPORTED,
+               "segment_sum: k=%d n_slots=%d (need k >= 1, 1 <= n_slots <= 128)", k, n_slots);
+    const size_t smem = static_cast<size_t>(kSegWarps) * n_slots * 32 * sizeof(float);
+    DM_CUDA(cudaFuncSetAttribute(segment_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    segment_sum_kernel<<<(k + 31) / 32, kSegWarps * 32, smem, as_stream(stream)>>>(x, slot, n, k, n_slots, out);
+    DM_LAUNCH_CHECK("segment_sum_kernel");
+    return DMNERF_OK;
+}
+
 extern "C" int dmnerf_hungarian_infeasible(int* count_out, void* stream) {
     DM_REQUIRE(count_out, DMNERF_EINVAL, "hungarian_infeasible: null pointer");
     DM_CUDA(cudaStreamSynchronize(as_stream(stream)));

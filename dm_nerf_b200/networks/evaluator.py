@@ -44,11 +44,20 @@ def hungarian(pred_ins, gt_ins, valid_ins_num, ins_num):
     return cost_ce, cost_siou, row, col
 
 
-def _ins_costs(pred_ins, gt_t, gt_count, n):
-    log_p, log_q = torch.log(pred_ins + 1e-8), torch.log(1 - pred_ins + 1e-8)
-    cost_ce = -(gt_t @ (log_p - log_q) + log_q.sum(0)[None, :]) / n
-    tp = gt_t @ pred_ins
-    fp = pred_ins.sum(0)[None, :] - tp
+def _ins_costs(pred_ins, gt_t, gt_count, n, slot=None, perm=None, offs=None):
+    """Cost matrices of evaluator.py:55-74.  With ``slot`` (the one-hot's column per ray, device int64) the two
+    [K,N]x[N,K] products become label-wise row sums (``ops.segment_sum``: N*K additions instead of N*K*K multiply-adds;
+    the assignment runs on the one SM the persistent MLP kernels leave free) and the column sums come from them."""
+    if slot is not None and pred_ins.is_cuda:
+        from .. import ops
+        tp, seg_p, seg_q = ops.segment_sum3(pred_ins, slot, perm, offs, gt_t.shape[0])
+        cost_ce = -(seg_p - seg_q + seg_q.sum(0)[None, :]) / n
+        fp = tp.sum(0)[None, :] - tp
+    else:
+        log_p, log_q = torch.log(pred_ins + 1e-8), torch.log(1 - pred_ins + 1e-8)
+        cost_ce = -(gt_t @ (log_p - log_q) + log_q.sum(0)[None, :]) / n
+        tp = gt_t @ pred_ins
+        fp = pred_ins.sum(0)[None, :] - tp
     fn = gt_count[:, None] - tp
     return cost_ce, 1.0 - tp / (tp + fp + fn + 1e-6)
 
@@ -99,6 +108,10 @@ def ins_label_prep(gt_labels, ins_num, max_label=None, dtype=torch.float32):
     gt_ins = torch.zeros((n, ins_num), device=dev, dtype=dtype).scatter_(1, slot[:, None], 1.0)
     ar = torch.arange(ins_num, device=dev)
     return {"n": n, "ins_num": int(ins_num), "gt_t": gt_ins.t(), "gt_count": gt_ins.sum(0), "n_valid": n_valid,
+            "slot": slot.contiguous(), "perm": torch.sort(slot, stable=True)[1].contiguous(),
+            "offs": torch.cat([torch.zeros(1, dtype=torch.int64, device=dev),
+                               torch.cumsum(torch.zeros(ins_num, dtype=torch.int64, device=dev).scatter_add_(
+                                   0, slot, torch.ones_like(slot)), 0)]).contiguous(),
             "n_valid_i32": n_valid.to(torch.int32), "ar": ar, "row_mask": (ar < n_valid).to(dtype),
             "n_inv": ins_num - n_valid}
 
@@ -109,7 +122,7 @@ def ins_criterion_prepped(preds, prep):
     from .. import ops
     n, ins_num, ar, row_mask, n_valid, n_inv = (prep[k] for k in ("n", "ins_num", "ar", "row_mask", "n_valid", "n_inv"))
     dev, dt = preds[0].device, preds[0].dtype
-    costs = [_ins_costs(p, prep["gt_t"], prep["gt_count"], n) for p in preds]
+    costs = [_ins_costs(p, prep["gt_t"], prep["gt_count"], n, prep.get("slot"), prep.get("perm"), prep.get("offs")) for p in preds]
     with torch.no_grad():
         scores = torch.stack([ce + siou for ce, siou in costs])
         col = ops.hungarian(scores, prep["n_valid_i32"]).long()                      # [B, K]
@@ -123,6 +136,16 @@ def ins_criterion_prepped(preds, prep):
         invalid_ce = torch.where(n_inv > 0, inv_sum / (n * torch.clamp(n_inv, min=1.0)), torch.zeros((), device=dev, dtype=dt))
         out.append((valid_ce + invalid_ce + valid_siou, valid_ce, invalid_ce, valid_siou))
     return out
+
+
+def ins_loss_and_grad_fused(pred_ins, prep):
+    """``ins_criterion_prepped([pred])[0][0]`` and its gradient with respect to ``pred_ins`` in five launches
+    (``ops.ins_assign_loss_grad``): what the overlapped training step runs on its side streams, where every small tensor op
+    shares ONE SM with the others.  Returns (total loss [scalar tensor], losses [4], grad [N,K])."""
+    from .. import ops
+    losses, grad = ops.ins_assign_loss_grad(pred_ins, prep["slot"], prep["perm"], prep["offs"], prep["gt_count"],
+                                            prep["n_valid_i32"])
+    return losses[0], losses, grad
 
 
 def ins_criterion_device(preds, gt_labels, ins_num, max_label=None):

@@ -32,18 +32,26 @@ def _query(model, rays_o, rays_d, z_vals, position_embedder, view_embedder):
 
 
 def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_vals_coarse, args,
-            t_rand=None, u=None, on_coarse=None, penalizer=None):
+            t_rand=None, u=None, on_coarse=None, penalizer=None, on_fine=None):
     """render.py:31-96.  ``t_rand`` [N,Sc] / ``u`` [N,N_importance] inject the uniforms; when absent
     they are drawn with torch.rand in the reference's order (jitter first, then u).  ``on_coarse(ins_coarse)``, if
     given, is called as soon as the coarse pass is composited (the training step starts the coarse instance
-    assignment on a side stream there, beside the fine pass).  ``penalizer=(tolerance, deta_w)`` evaluates
+    assignment on a side stream there, beside the fine pass); ``on_fine(ins_fine)`` likewise right after the fine
+    compositing launch, before the fine penalizer's (grad mode may be off inside it).  ``penalizer=(tolerance, deta_w)`` evaluates
     ``ins_penalizer`` (penalizer.py:58-62) of both passes inside the compositing nodes and adds ``emptiness_coarse`` /
     ``emptiness_fine`` to the returned dict (same values as calling ``ins_penalizer`` on the outputs; one fused
     backward per pass instead of two gradients of ``raw`` that autograd then sums)."""
-    def composite(raw, z):
+    def sliced(fn):
+        if fn is None:
+            return None
+        return lambda ins: fn(ins[-args.N_ins:] if (args.is_train and args.N_ins is not None) else ins)
+
+    def composite(raw, z, hook=None):
         if penalizer is not None and torch.is_grad_enabled() and raw.requires_grad:
-            return ops.composite_penalized(raw, z, rays_d, COMP_DROP_EMPTY, True, penalizer[0], penalizer[1])
+            return ops.composite_penalized(raw, z, rays_d, COMP_DROP_EMPTY, True, penalizer[0], penalizer[1], hook)
         out = render_train(raw, z, rays_d)
+        if hook is not None:
+            hook(out[3])
         if penalizer is not None:
             return out + (ops.penalizer(raw, z, out[2].detach(), rays_d, penalizer[0], penalizer[1]),)
         return out + (None,)
@@ -69,7 +77,7 @@ def dm_nerf(rays, position_embedder, view_embedder, model_coarse, model_fine, z_
         u_arg = u if u is not None else torch.rand([n, args.N_importance], device=rays_d.device)
     z_vals_fine = ops.fine_z(z_vals_coarse, weights_coarse.detach(), int(args.N_importance), u_arg)
     raw_fine = _query(model_fine, rays_o, rays_d, z_vals_fine, position_embedder, view_embedder)
-    rgb_fine, weights_fine, depth_fine, ins_fine, pen_fine = composite(raw_fine, z_vals_fine)
+    rgb_fine, weights_fine, depth_fine, ins_fine, pen_fine = composite(raw_fine, z_vals_fine, sliced(on_fine))
     if args.is_train and args.N_ins is not None:
         ins_fine = ins_fine[-args.N_ins:]
         ins_coarse = ins_coarse[-args.N_ins:]

@@ -258,6 +258,91 @@ def hungarian(scores, n_valid):
     return col
 
 
+class _SegmentSum(torch.autograd.Function):
+    """out[g, j] = sum_{n: slot[n] == g} x[n, j]  (``gt_one_hot.t() @ x`` without the dense product); backward is a gather."""
+
+    @staticmethod
+    def forward(ctx, x, slot, n_slots):
+        x = _f32(x, "x")
+        n, k = x.shape
+        out = torch.empty((n_slots, k), dtype=torch.float32, device=x.device)
+        check(_lib.lib().dmnerf_segment_sum(_ptr(x), _ptr(slot), n, k, n_slots, _ptr(out), _stream()), "dmnerf_segment_sum")
+        _count()
+        ctx.save_for_backward(slot)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (slot,) = ctx.saved_tensors
+        return g.index_select(0, slot), None, None
+
+
+class _SegmentSum3(torch.autograd.Function):
+    """(sum p, sum log(p + 1e-8), sum log(1 - p + 1e-8)) per ground-truth slot, one pass over p."""
+
+    @staticmethod
+    def forward(ctx, p, slot, perm, offs, n_slots):
+        p = _f32(p, "pred_ins")
+        n, k = p.shape
+        out = torch.empty((3, n_slots, k), dtype=torch.float32, device=p.device)
+        check(_lib.lib().dmnerf_segment_sum3(_ptr(p), _ptr(perm), _ptr(offs), n, k, n_slots, _ptr(out), _stream()),
+              "dmnerf_segment_sum3")
+        _count()
+        ctx.save_for_backward(p, slot)
+        return out[0], out[1], out[2]
+
+    @staticmethod
+    def backward(ctx, g_tp, g_lp, g_lq):
+        p, slot = ctx.saved_tensors
+        g = g_tp.index_select(0, slot) + g_lp.index_select(0, slot) / (p + 1e-8) - g_lq.index_select(0, slot) / (1 - p + 1e-8)
+        return g, None, None, None, None
+
+
+def segment_sum3(p, slot, perm, offs, n_slots: int):
+    """(tp, sum log p, sum log(1-p)) label-wise for one prediction map (see ``dmnerf_segment_sum3``); differentiable in p.
+    ``slot`` int64 [N] (the one-hot's column per ray), ``perm`` = its stable argsort, ``offs`` int64 [n_slots+1] = segment
+    starts in ``perm`` -- all on the device, contiguous."""
+    for name, t in (("slot", slot), ("perm", perm), ("offs", offs)):
+        if t.dtype != torch.int64 or not t.is_cuda or not t.is_contiguous():
+            raise RuntimeError(f"segment_sum3: {name} must be a contiguous int64 CUDA tensor")
+    return _SegmentSum3.apply(p, slot, perm, offs, int(n_slots))
+
+
+def ins_assign_loss_grad(p, slot, perm, offs, cnt, n_valid_i32, want_grad: bool = True):
+    """The instance loss of ONE prediction map and its gradient as five launches (label-wise sums -> score matrices ->
+    device Hungarian -> loss terms -> gradient) instead of ~130 tensor ops + autograd: evaluator.py:19-74 with a one-hot
+    ground truth.  p [N,K] probabilities; slot/perm/offs/cnt/n_valid_i32 from ``ins_label_prep``.
+    Returns (losses [4] = total, valid_ce, invalid_ce, valid_siou; grad [N,K] = d total / d p or None)."""
+    p = _f32(p.detach(), "pred_ins")
+    n, k = p.shape
+    dev = p.device
+    lib = _lib.lib()
+    s3 = torch.empty((3, k, k), dtype=torch.float32, device=dev)
+    check(lib.dmnerf_segment_sum3(_ptr(p), _ptr(perm), _ptr(offs), n, k, k, _ptr(s3), _stream()), "dmnerf_segment_sum3")
+    mats = torch.empty((3, k, k), dtype=torch.float32, device=dev)               # scores | ce | siou
+    colsum = torch.empty((2, k), dtype=torch.float32, device=dev)
+    cnt = _f32(cnt, "gt_count")
+    check(lib.dmnerf_assign_scores(_ptr(s3), _ptr(cnt), n, k, _ptr(mats[0]), _ptr(mats[1]), _ptr(mats[2]), _ptr(colsum),
+                                   _stream()), "dmnerf_assign_scores")
+    col = hungarian(mats[:1], n_valid_i32)[0]
+    losses = torch.empty(4, dtype=torch.float32, device=dev)
+    rowof = torch.empty(k, dtype=torch.int32, device=dev)
+    grad = torch.empty((n, k), dtype=torch.float32, device=dev) if want_grad else None
+    check(lib.dmnerf_assign_loss_grad(_ptr(p), _ptr(slot), _ptr(s3), _ptr(mats[1]), _ptr(mats[2]), _ptr(colsum), _ptr(cnt),
+                                      _ptr(col), _ptr(n_valid_i32), n, k, _ptr(losses), _ptr(rowof), _ptr(grad), _stream()),
+          "dmnerf_assign_loss_grad")
+    _count(3)
+    return losses, grad
+
+
+def segment_sum(x, slot, n_slots: int):
+    """Label-wise row sums of x [N,K] (evaluator.py:55-63 with a one-hot ground truth): [n_slots, K].  ``slot`` int64 [N]
+    on the device.  Differentiable in x."""
+    if slot.dtype != torch.int64 or not slot.is_cuda or not slot.is_contiguous():
+        raise RuntimeError("segment_sum: slot must be a contiguous int64 CUDA tensor")
+    return _SegmentSum.apply(x, slot, int(n_slots))
+
+
 def hungarian_infeasible() -> int:
     """Launches of ``hungarian`` since the last call whose score matrix had no assignment (a row of NaN / inf; scipy
     raises ValueError there).  Synchronises the current stream -- call it outside captured graphs."""
@@ -422,9 +507,11 @@ class _CompositePenalizedFn(torch.autograd.Function):
     own into it in place (DMNERF_PEN_ACCUMULATE) -- no zero-filled second gradient, no [N,S,C] gradient-sum pass."""
 
     @staticmethod
-    def forward(ctx, raw, z, rays_d, flags, ins_detach, tolerance, deta_w):
+    def forward(ctx, raw, z, rays_d, flags, ins_detach, tolerance, deta_w, after_composite=None):
         raw, z, rays_d = _f32(raw, "raw"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
         rgb, weights, depth, ins, trans = composite_fwd(raw, z, rays_d, flags, want_trans=True)
+        if after_composite is not None:
+            after_composite(ins)          # the composited map exists; the penalizer kernel has not been enqueued yet
         ctx.pen_flags = 0
         loss, partials = penalizer_fwd(raw, z, depth, rays_d, tolerance, deta_w, 0)
         ctx.save_for_backward(raw, z, rays_d, depth, partials, weights, trans, ins)
@@ -439,12 +526,13 @@ class _CompositePenalizedFn(torch.autograd.Function):
         if d_loss is not None:
             d_loss = _f32(d_loss, "d_loss").reshape(1)
             penalizer_bwd(raw, z, depth, rays_d, ctx.tol, ctx.dw, ctx.pen_flags | _lib.PEN_ACCUMULATE, partials, d_loss, d_raw)
-        return d_raw, None, None, None, None, None, None
+        return d_raw, None, None, None, None, None, None, None
 
 
-def composite_penalized(raw, z, rays_d, flags: int, ins_detach: bool, tolerance: float, deta_w: float):
-    """(rgb, weights, depth, ins, emptiness_loss); see _CompositePenalizedFn."""
-    return _CompositePenalizedFn.apply(raw, z, rays_d, flags, ins_detach, float(tolerance), float(deta_w))
+def composite_penalized(raw, z, rays_d, flags: int, ins_detach: bool, tolerance: float, deta_w: float, after_composite=None):
+    """(rgb, weights, depth, ins, emptiness_loss); see _CompositePenalizedFn.  ``after_composite(ins)`` is called between
+    the compositing launch and the penalizer launch (grad mode is off there)."""
+    return _CompositePenalizedFn.apply(raw, z, rays_d, flags, ins_detach, float(tolerance), float(deta_w), after_composite)
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -13,7 +13,8 @@ import torch.distributed as dist
 from . import parallel
 from .optim import FlatAdam
 from . import ops
-from .networks.evaluator import img2mse, ins_criterion_device, ins_criterion_multi, ins_criterion_prepped, ins_label_prep
+from .networks.evaluator import (img2mse, ins_criterion_device, ins_criterion_multi, ins_criterion_prepped, ins_label_prep,
+                                 ins_loss_and_grad_fused)
 from .networks.helpers import get_select_crop, get_select_full, z_val_sample
 from .networks.render import dm_nerf
 
@@ -52,6 +53,9 @@ class TrainStep:
         # while the persistent MLP kernels leave `reserved_sms` SMs free for them (dmnerf_reserve_sms).
         self.overlap = bool(self.graph_mode if overlap_assignment is None else overlap_assignment) and device_assignment
         self.reserved_sms = 1
+        # the instance loss and its gradient as five launches (ops.ins_assign_loss_grad) instead of ~130 tensor ops +
+        # autograd.grad on the side streams; False keeps the tensor-op formulation (same values, tested)
+        self.fused_ins_loss = True
         self._side = None
         self._early_reduce = {}                # model index -> (flat gradient, pending all-reduce) started before _finish
         self._draw_step = self._draw_seed = None
@@ -186,9 +190,13 @@ class TrainStep:
         def ins_loss_and_grad(ins_map):
             # the instance loss AND its gradient w.r.t. the composited map, both on the side stream: the ~100 small
             # kernels of that backward then run beside the ray kernels instead of in front of the compositing backward
-            leaf = ins_map.detach().requires_grad_(True)
-            loss = ins_criterion_prepped([leaf], prep)[0][0]
-            (grad,) = torch.autograd.grad(loss, leaf)
+            if self.fused_ins_loss:
+                loss, _, grad = ins_loss_and_grad_fused(ins_map, prep)
+                return loss, grad
+            with torch.enable_grad():                  # (the fine hook runs inside an autograd node's forward)
+                leaf = ins_map.detach().requires_grad_(True)
+                loss = ins_criterion_prepped([leaf], prep)[0][0]
+                (grad,) = torch.autograd.grad(loss, leaf)
             return loss.detach(), grad
 
         def on_coarse(ins_coarse):
@@ -196,11 +204,18 @@ class TrainStep:
             with torch.cuda.stream(side_c):
                 got["c"] = ins_loss_and_grad(ins_coarse)
 
+        def on_fine(ins_fine):
+            # ... and the fine assignment the moment the fine pass is composited, ahead of the fine penalizer launch: its
+            # chain (label-wise sums, the one-warp Hungarian, ~100 small kernels of loss gradient) is longer than the
+            # coarse model's backward it runs beside
+            side_f.wait_stream(main)
+            with torch.cuda.stream(side_f):
+                got["f"] = ins_loss_and_grad(ins_fine)
+
         pen = (a.tolerance, a.deta_w) if self.penalize else None     # emptiness loss inside the compositing nodes
-        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, on_coarse=on_coarse, penalizer=pen)
-        side_f.wait_stream(main)
-        with torch.cuda.stream(side_f):
-            ins_f, g_ins_f = ins_loss_and_grad(info["ins_fine"])
+        info = dm_nerf(rays, self.pe, self.ve, self.mc, self.mf, self.z_coarse, a, on_coarse=on_coarse, penalizer=pen,
+                       on_fine=on_fine)
+        ins_f, g_ins_f = got["f"]
         # coarse model: losses and backward on the main stream while the fine assignment runs on its side stream
         rgb_c = img2mse(info["rgb_coarse"], target_c)
         pen_c = info.get("emptiness_coarse")

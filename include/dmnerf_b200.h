@@ -187,6 +187,25 @@ int  dmnerf_hungarian(const float* scores, int n_mats, int64_t mat_stride, int l
  * ValueError (evaluator.py:45).  The kernel then writes the identity permutation (every slot defined and in range) and
  * counts the launch.  This call SYNCHRONISES the stream, returns the count since the last query and resets it. */
 int  dmnerf_hungarian_infeasible(int* count_out, void* stream);
+/* Label-wise sums for the assignment's cost matrices (networks/evaluator.py:55-63: the [K_gt, K_pred, N] broadcast over
+ * a one-hot ground truth): out[g][j] = sum over rays n with slot[n] == g of x[n][j].  x [n,k]; slot int64 [n] (values
+ * outside [0,n_slots) are skipped); out [n_slots,k] is overwritten.  Fixed summation order (reproducible). */
+int  dmnerf_segment_sum(const float* x, const int64_t* slot, int64_t n, int k, int n_slots, float* out, void* stream);
+/* The three sums the cost matrices need of one prediction map p [n,k] (probabilities) in one pass: out [3,n_slots,k] =
+ * label-wise sums of p, log(p + 1e-8), log(1 - p + 1e-8) (evaluator.py:55-66).  perm int64 [n]: ray indices ordered by
+ * slot; offs int64 [n_slots+1]: first position of each slot in perm (offs[n_slots] = n).  One warp per slot, fixed order. */
+int  dmnerf_segment_sum3(const float* p, const int64_t* perm, const int64_t* offs, int64_t n, int k, int n_slots,
+                         float* out, void* stream);
+/* The instance loss around the assignment (networks/evaluator.py:19-37, 55-74) without its ~130 small tensor ops:
+ * dmnerf_assign_scores: s3 [3,k,k] (dmnerf_segment_sum3), cnt [k] rays per slot -> scores = ce + siou [k,k] (the
+ * Hungarian's input), ce, siou [k,k], colsum [2,k] (column sums of p and of log(1-p+1e-8)).
+ * dmnerf_assign_loss_grad: given the assignment col int32 [k] (dmnerf_hungarian's output) and n_valid (device int32):
+ * losses[4] = {total, valid_ce, invalid_ce, valid_siou}; rowof int32 [k] scratch; grad [n,k] = d total / d p (NULL: loss only). */
+int  dmnerf_assign_scores(const float* s3, const float* cnt, int64_t n, int k, float* scores, float* ce, float* siou,
+                          float* colsum, void* stream);
+int  dmnerf_assign_loss_grad(const float* p, const int64_t* slot, const float* s3, const float* ce, const float* siou,
+                             const float* colsum, const float* cnt, const int* col, const int* n_valid, int64_t n, int k,
+                             float* losses, int* rowof, float* grad, void* stream);
 
 /* ---- self test of the tcgen05 building blocks (used by tests/) ---------------------------------------
  * D[128,n] = A[128,k] * B[n,k]^T in bf16 with fp32 accumulate; a,b fp32 in, d fp32 out. */

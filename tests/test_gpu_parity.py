@@ -873,6 +873,28 @@ def test_ins_criterion_device_vs_golden(golden, tag):
     np.testing.assert_allclose(float(out[1][0].detach()), float(host[0]), rtol=5e-6)
 
 
+@pytest.mark.parametrize("k,n,n_present", [(32, 1024, 32), (93, 4096, 57), (16, 333, 5), (8, 64, 1)])
+def test_fused_instance_loss_and_gradient_match_the_tensor_op_formulation(k, n, n_present):
+    """``ins_loss_and_grad_fused`` (label-wise sums -> scores -> device Hungarian -> loss -> gradient, five launches) against
+    ``ins_criterion_prepped`` + autograd (itself pinned to the reference's golden values): same assignment, loss terms
+    within 2e-6 relative, gradient within 2e-6 of its largest entry -- with labels that leave channels unmatched, a single
+    label, and ray counts that are not a multiple of anything."""
+    from dm_nerf_b200.networks import evaluator as ev
+    gen = torch.Generator().manual_seed(k * 1000 + n)
+    present = torch.randperm(k, generator=gen)[:n_present]
+    labels = cu(present[torch.randint(0, n_present, (n,), generator=gen)])
+    pred = cu(torch.rand(n, k, generator=gen) * 0.98 + 0.01)
+    prep = ev.ins_label_prep(labels, k, max_label=k)
+    leaf = pred.clone().requires_grad_(True)
+    ref = ev.ins_criterion_prepped([leaf], prep)[0]
+    (g_ref,) = torch.autograd.grad(ref[0], leaf)
+    total, losses, grad = ev.ins_loss_and_grad_fused(pred, prep)
+    for a, b in zip(losses.tolist(), [float(x) for x in ref]):
+        assert abs(a - b) <= 2e-6 * max(1.0, abs(b)), (losses.tolist(), [float(x) for x in ref])
+    assert float((grad - g_ref).abs().max()) <= 2e-6 * float(g_ref.abs().max()) + 1e-12, \
+        (float((grad - g_ref).abs().max()), float(g_ref.abs().max()))
+
+
 def test_train_step_cuda_graph_replay():
     """TrainStep(graph=True): the captured step (pixel draw, both passes, losses, device Hungarian, backward, Adam)
     replays with new inputs; every replay moves the weights, the loss stays finite, the step counter drives the

@@ -51,3 +51,60 @@ tot = sum(v[1] for v in by.values())
 print(f"sum of kernel time over all streams: {tot / steps / 1000:.3f} ms/step, {sum(v[0] for v in by.values()) / steps:.0f} kernels/step")
 for nm, (c, t) in sorted(by.items(), key=lambda x: -x[1][1])[:28]:
     print(f"  {t / steps:9.1f} us  x{c / steps:5.1f}  {nm}")
+
+# ---- per-stream timeline of the LAST profiled step: gaps on the busiest (main) stream ----
+kin = [e for e in prof.profiler.kineto_results.events() if e.device_type() == torch.autograd.DeviceType.CUDA and e.duration_ns() > 0]
+kin.sort(key=lambda e: e.start_ns())
+by_stream = {}
+for e in kin:
+    by_stream.setdefault(e.device_resource_id(), []).append(e)
+main_id = max(by_stream, key=lambda s: sum(e.duration_ns() for e in by_stream[s]))
+main = by_stream[main_id]
+t_end = main[-1].start_ns() + main[-1].duration_ns()
+span = a.elapsed_time(b) / steps * 1e6        # ns per step
+last = [e for e in main if e.start_ns() >= t_end - span]
+print(f"main stream {main_id}: last step has {len(last)} kernels, busy {sum(e.duration_ns() for e in last) / 1e3:.0f} us of {span / 1e3:.0f} us")
+prev_end = None
+for e in last:
+    if prev_end is not None and e.start_ns() - prev_end > 15000:
+        print(f"  gap {(e.start_ns() - prev_end) / 1e3:7.1f} us before {e.name()[:60]}  (at +{(e.start_ns() - last[0].start_ns()) / 1e3:.0f} us)")
+    prev_end = e.start_ns() + e.duration_ns()
+for sid, evs in by_stream.items():
+    if sid == main_id: continue
+    ev = [e for e in evs if e.start_ns() >= t_end - span]
+    if ev:
+        print(f"  stream {sid}: {len(ev)} kernels, busy {sum(e.duration_ns() for e in ev) / 1e3:.0f} us, from +{(ev[0].start_ns() - last[0].start_ns()) / 1e3:.0f} to +{(ev[-1].start_ns() + ev[-1].duration_ns() - last[0].start_ns()) / 1e3:.0f} us")
+
+# ---- what surrounds the largest main-stream gap ----
+gaps = []
+for i in range(1, len(last)):
+    pe_ = last[i - 1].start_ns() + last[i - 1].duration_ns()
+    gaps.append((last[i].start_ns() - pe_, i))
+g, gi = max(gaps)
+t0 = last[0].start_ns()
+print(f"largest gap {g / 1e3:.0f} us; main stream around it:")
+for e in last[max(0, gi - 5):gi + 4]:
+    print(f"   +{(e.start_ns() - t0) / 1e3:7.0f} us {e.duration_ns() / 1e3:7.1f} us  {e.name()[:80]}")
+lo, hi = last[gi - 1].start_ns() + last[gi - 1].duration_ns(), last[gi].start_ns()
+for sid, evs in by_stream.items():
+    if sid == main_id: continue
+    ev = [e for e in evs if e.start_ns() + e.duration_ns() > lo - 50000 and e.start_ns() < hi + 50000]
+    print(f"  stream {sid} during the gap ({len(ev)} kernels):")
+    for e in ev[:6] + ev[-10:]:
+        print(f"   +{(e.start_ns() - t0) / 1e3:7.0f} us {e.duration_ns() / 1e3:7.1f} us  {e.name()[:80]}")
+
+# ---- the heavy kernels of the last step in time order, with the idle time (no kernel on ANY stream) in front of each ----
+allk = [e for e in kin if e.start_ns() >= t_end - span]
+allk.sort(key=lambda e: e.start_ns())
+cover_end = allk[0].start_ns()
+idle_total = 0
+marks = []
+for e in allk:
+    idle = max(0, e.start_ns() - cover_end)
+    idle_total += idle
+    if e.duration_ns() > 30000 or idle > 10000:
+        marks.append((e.start_ns(), e.duration_ns(), idle, e.name()[:64], e.device_resource_id()))
+    cover_end = max(cover_end, e.start_ns() + e.duration_ns())
+print(f"all streams: {len(allk)} kernels, idle (no kernel anywhere) {idle_total / 1e3:.0f} us of {span / 1e3:.0f} us")
+for st, du, idle, nm, sid in marks:
+    print(f"   +{(st - allk[0].start_ns()) / 1e3:7.0f} us {du / 1e3:7.1f} us  idle-before {idle / 1e3:6.1f}  s{sid:<4d} {nm}")
