@@ -407,7 +407,7 @@ int pack_x3(const float* const* params, int ins_num, void* packed, cudaStream_t 
     for (int i = 0; i < kNumParams; ++i) pr.p[i] = params[i];
     uint8_t* image = static_cast<uint8_t*>(packed);
     float* scratch = reinterpret_cast<float*>(image + im.scratch_off);
-    tc::compose_kernel<<<(2 * 128 * 256 + 256 + 255) / 256, 256, 0, st>>>(pr, scratch);
+    tc::compose_kernel<<<dim3(16, 8, 3), 256, 0, st>>>(pr, scratch);
     const int64_t elems = im.bias_off / 2;
     tc::x3::pack_chunks_kernel<<<static_cast<unsigned>((elems + 255) / 256), 256, 0, st>>>(pr, im, image);
     tc::pack_bias_kernel<<<(tc::kBiasFloats + 255) / 256, 256, 0, st>>>(pr, im, image);

@@ -183,8 +183,14 @@ class TrainStep:
         with torch.cuda.stream(side_c):
             self.mc.packed(ops.get_mode()); self.mf.packed(ops.get_mode())
         target_c, target_i, rays = get_select_full(image, pose, K, labels, a.N_train, idx=self._draw(image))
-        prep = ins_label_prep(target_i, a.ins_num, self.max_label)
         main.wait_stream(side_c)
+        # the label side of the instance loss (one-hot slots, their sort, counts: ~20 small kernels) is not needed before
+        # the coarse pass is composited: it runs on the coarse side stream, beside the coarse forward
+        side_c.wait_stream(main)
+        with torch.cuda.stream(side_c):
+            prep = ins_label_prep(target_i, a.ins_num, self.max_label)
+            prep_done = torch.cuda.Event()
+            prep_done.record(side_c)
         got = {}
 
         def ins_loss_and_grad(ins_map):
@@ -209,6 +215,7 @@ class TrainStep:
             # chain (label-wise sums, the one-warp Hungarian, ~100 small kernels of loss gradient) is longer than the
             # coarse model's backward it runs beside
             side_f.wait_stream(main)
+            side_f.wait_event(prep_done)
             with torch.cuda.stream(side_f):
                 got["f"] = ins_loss_and_grad(ins_fine)
 
