@@ -102,7 +102,7 @@ marks = []
 for e in allk:
     idle = max(0, e.start_ns() - cover_end)
     idle_total += idle
-    if e.duration_ns() > 30000 or idle > 10000:
+    if e.duration_ns() > 7000 or idle > 5000:
         marks.append((e.start_ns(), e.duration_ns(), idle, e.name()[:64], e.device_resource_id()))
     cover_end = max(cover_end, e.start_ns() + e.duration_ns())
 print(f"all streams: {len(allk)} kernels, idle (no kernel anywhere) {idle_total / 1e3:.0f} us of {span / 1e3:.0f} us")
