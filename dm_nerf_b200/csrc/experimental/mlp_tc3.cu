@@ -96,6 +96,10 @@ __device__ long long g_dbg3[8];
 // second issuer runs through a stage that has not been loaded yet and the launch faults).  Measured: 7.0 ms with one
 // issuer, 7.7 ms with two (the guard + spills cost more than the parallel issue gains), so one it is.
 constexpr bool kTwoIssuers = false;
+// Round-2 experiment: LOCKSTEP instead of ping-pong -- every chunk is streamed once per layer and feeds both tiles of both
+// CTAs (8 pair-MMAs per ring step) before it is released, as in mlp_tc.cu but with the B operand split across the pair
+// (half the weight bytes per SM, a ring three K=64 chunks deep).
+constexpr bool kLockstep = false;     // measured: 6.85 ms vs 6.06 ms (default kernel), see DESIGN.md 4.1b
 
 struct Bars3 {
     uint32_t base;
@@ -177,7 +181,7 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
             const uint8_t* src = image + im.v3_off[rank];
             for (int64_t quad = cluster_id; quad < n_quads; quad += n_clusters) {
                 for (int l = 0; l < kLayers; ++l) {
-                    for (int t = 0; t < 2; ++t) {
+                    for (int t = 0; t < (kLockstep ? 1 : 2); ++t) {
                         for (int c = layer_start[l]; c < layer_start[l + 1]; ++c) {
                             const Chunk ck = sched[c];
                             const uint32_t bytes = static_cast<uint32_t>(ck.ksteps) * 16 * ck.rows * 2;
@@ -218,6 +222,46 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
                 for (int l = 0; l < kLayers; ++l) {
                     const int c0 = layer_start[l], c1 = layer_start[l + 1];
                     const uint32_t g_layer = g;
+                    if (kLockstep) {
+                        g += c1 - c0;
+                        uint32_t stage = g_layer % kStagesV3, phase = (g_layer / kStagesV3) & 1u;
+#pragma unroll 1
+                        for (int c = c0; c < c1; ++c) {
+                            const uint4 r = recs[c];
+                            const long long w0 = clock64();
+                            ptx::mbar_wait(bars.w_full(stage), phase);
+                            const long long w1 = clock64();
+                            if (r.y & kFirst) {
+                                for (int t = 0; t < 2; ++t) {
+                                    ptx::mbar_wait(bars.a_ready(t), a_par2[t]);
+                                    a_par2[t] ^= 1;
+                                    ptx::mbar_arrive_expect_tx(bars.a_ready(t), kSigBytes3);
+                                }
+                            }
+                            dbg_f += w1 - w0; dbg_a += clock64() - w1;
+                            ptx::tc_fence_after();
+                            const uint32_t nh = r.y >> 16, ksteps = (r.y >> 8) & 15;
+                            const uint32_t b_lo = ring_lo + stage * (kSlotBytes >> 4) + (nh << 16);
+                            for (int t = 0; t < 2; ++t) {
+                                const uint32_t d = tmem + t * 256;
+                                if (r.y & kOnes) {
+                                    ptx::umma2_bf16(d, ones_d, desc_hi | b_lo, r.z, 1u);
+                                } else {
+                                    const uint32_t a_lo = (((sm0 + kSm3A + t * kABytes) >> 4) | lbo_a) + r.x;
+                                    ptx::umma2_bf16(d, desc_hi | a_lo, desc_hi | b_lo, r.z, (r.y & kFirst) ? 0u : 1u);
+                                    ptx::umma2_bf16(d, desc_hi | (a_lo + 2 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 2), r.z, 1u);
+                                    if (ksteps > 2) {
+                                        ptx::umma2_bf16(d, desc_hi | (a_lo + 4 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 4), r.z, 1u);
+                                        ptx::umma2_bf16(d, desc_hi | (a_lo + 6 * (kKgBytes >> 4)), desc_hi | (b_lo + nh * 6), r.z, 1u);
+                                    }
+                                }
+                                if (r.y & kLast) ptx::umma_commit2(bars.acc_ready(t), 3);
+                            }
+                            ptx::umma_commit2(bars.w_empty(stage), 3);
+                            if (++stage == kStagesV3) { stage = 0; phase ^= 1; }
+                        }
+                        continue;
+                    }
                     g += 2 * (c1 - c0);
                   for (int t = t_first; t <= t_last; ++t) {
                     const uint32_t a_base_lo = ((sm0 + kSm3A + t * kABytes) >> 4) | lbo_a;
@@ -277,7 +321,7 @@ mlp_fwd_bf16_v3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im,
             const uint32_t remote_sig0 = ptx::mapa(sm0 + kSm3Sig + 2 * kEpiWarps * 4, 0);
             for (int64_t quad = cluster_id; quad < n_quads; quad += n_clusters) {
                 for (int l = 0; l < kLayers; ++l) {
-                    const int cnt = 2 * (layer_start[l + 1] - layer_start[l]);
+                    const int cnt = (kLockstep ? 1 : 2) * (layer_start[l + 1] - layer_start[l]);
                     for (int c = 0; c < cnt; ++c) {
                         ptx::mbar_wait(bars.w_full(stage), phase);
                         ptx::st_async_signal(remote_sig0 + 4 * stage, remote_bar0 + 8 * stage, 1u);
