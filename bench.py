@@ -898,7 +898,8 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
                     "kernel": name, "launches": n_launch, "ms_per_launch": ms_kernel / n_launch,
                     "rays_per_launch": rays_per_launch,
                     "algorithmic_flop_per_launch": 2.0 * macs_per_point(K_INS) * (SC + NIMP) * rays_per_launch,
-                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (B200_PROFILING.md)",
+                    "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (B200_PROFILING.md)")
+                                   + " (kind::f16 MMAs: fp16 and bf16 operands share one dense peak)",
                     "frac_of_burst_peak": achieved / peaks.get("bf16_tflops", 1650.0),
                     "kernel_share_of_step": ms_kernel / (ms_step * steps), "measured_on": "rank 0's launches"}
     hbm_peak = peaks.get("hbm_gbs", 6400.0)
