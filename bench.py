@@ -429,13 +429,15 @@ class FrameJob:
         self.frame = bufs if cx.rank == 0 else None
         self.local = {kk: v[self.a:self.b] for kk, v in bufs.items()} if cx.rank == 0 else bufs
         self.host_rays = self.host_out = None
+        self.lean = True           # render_pixels' default: density-only coarse pass (same frame bit for bit)
 
     def step(self, rays=None):
         from dm_nerf_b200.frame import render_pixels
         from dm_nerf_b200.parallel import gather_frame
         pe, ve, mc, mf = self.models
         render_pixels(pe, ve, mc, mf, (self.hw[0], self.hw[1], self.Kmat), self.c2w, self.near, self.far, SC, NIMP,
-                      pix0=self.a, count=self.b - self.a, chunk=self.chunk, rays=rays, out=self.local)
+                      pix0=self.a, count=self.b - self.a, chunk=self.chunk, rays=rays, out=self.local,
+                      lean_coarse=self.lean)
         gather_frame(self.local, self.frame, self.total, self.KEYS)
 
     def prepare_host(self):
@@ -801,6 +803,23 @@ def run_gpu(args):
             ops.set_mode(mode)
         log("fp32 frame + parity done")
 
+    # ---- the same frame with the coarse pass evaluated in full (colours and instance logits too, as a literal transcription
+    # of render.py:54-62 does although no render caller reads them): speed, and that the frame is the same bit for bit ------
+    full_coarse = None
+    if mode in TC_MODES and not args.no_extra:
+        job.lean = False
+        try:
+            job.step()
+            ms_full = cx.timed(job.step, max(2, min(args.steps, 5)))
+            if cx.rank == 0:
+                same = all(bool(torch.equal(job.frame[kk], frame_tc[kk])) for kk in FrameJob.KEYS)
+                full_coarse = {"ms_per_frame": ms_full, "value": N_RAYS / (ms_full / 1000), "unit": "rays/s",
+                               "frame_bit_identical_to_headline": same,
+                               "note": "headline: frame.render_pixels evaluates the density trunk only in the coarse pass "
+                                       "(dmnerf_mlp_density); this leg: the full coarse MLP + compositing"}
+        finally:
+            job.lean = True
+
     # ---- the same frame with bf16 operands (round 1's headline mode, the training chain): speed only -- its parity is in
     # parity_trained.other_modes; it misses the label clause, which is why it is not the headline ---------------------------
     bf16_leg = None
@@ -872,7 +891,7 @@ def run_gpu(args):
 
     if cx.rank == 0:
         emit(headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, samples,
-                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, bf16_mode=bf16_leg, weak=weak, c4=c4, c5=c5, train=train)))
+                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, bf16_mode=bf16_leg, full_coarse_pass=full_coarse, weak=weak, c4=c4, c5=c5, train=train)))
     if cx.world > 1:
         cx.dist.destroy_process_group()
 
@@ -912,6 +931,13 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
             secondary.append({"kernel": kname, "bound": "hbm" if "composite" in kname else
                               "latency (CDF + searches per ray; HBM figure for scale)", "achieved": gbps, "peak": hbm_peak,
                               "unit": "GB/s", "frac": gbps / hbm_peak, "ms_per_launch": ms_k / cnt})
+    dname = f"dmnerf_mlp_density[S={SC},mode={mode_id}]"
+    cnt_d, ms_d = totals.get(dname, (0, 0.0))
+    if cnt_d:
+        # the coarse pass: trunk mlps.0..7 + density_linear = 491,264 MAC per point (dm_nerf.py:82-92)
+        tf = 2.0 * 491264 * SC * rays_rank0 * steps / (ms_d / 1000) / 1e12
+        secondary.append({"kernel": dname, "bound": "tensor", "achieved": tf, "peak": peaks.get("bf16_tflops_sustained", 1400.0),
+                          "unit": "TFLOP/s", "frac": tf / peaks.get("bf16_tflops_sustained", 1400.0), "ms_per_launch": ms_d / cnt_d})
     cpu = None
     train = legs.get("train")
     if cpu_arm is not None:
@@ -957,7 +983,10 @@ def headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, 
         "dtype": {"bf16": "bf16", "fp16": "f16", "fp32": "f32"}[mode], "data": "synthetic", "rays_per_step": N_RAYS,
         "config": {"workload": "DM-SR full-image render 640x480 = 307200 rays x (64+128) samples, K=32, rgb+depth+instance "
                                "map+labels, one frame per step",
-                   "mode": mode, "chunk_rays": args.chunk, "l2": "flushed between timed iterations (256 MiB write)",
+                   "mode": mode, "chunk_rays": args.chunk,
+                   "coarse_pass": "density trunk only (its colours / instance logits are dead values in a render, "
+                                  "tester.py:73-76); the rendered frame is bit-identical to the full coarse pass, "
+                                  "timed beside as full_coarse_pass", "l2": "flushed between timed iterations (256 MiB write)",
                    "parallelism": f"the frame's pixel rows sharded x{cx.world} (no data-path collective), point-to-point "
                                   f"gather of rgb+depth+K-channel map+labels into rank 0's frame buffers inside the timed region"},
         "e2e": {"value": N_RAYS / (ms_e2e / 1000), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

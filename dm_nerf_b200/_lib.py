@@ -106,6 +106,8 @@ _SIGNATURES = {
     "dmnerf_weights_pack": (_int, [C.POINTER(_p), _int, _int, _p, _p]),
     "dmnerf_mlp_fwd": (_int, [_p, _p, _p, _i64, _int, _p, _int, _int, _p, _p, _p]),
     "dmnerf_mlp_fwd_embedded": (_int, [_p, _i64, _p, _int, _int, _p, _p, _p]),
+    "dmnerf_mlp_density": (_int, [_p, _p, _p, _i64, _int, _p, _int, _int, _p, _p]),
+    "dmnerf_weights_from_sigma": (_int, [_p, _p, _p, _i64, _int, _int, _p, _p]),
     "dmnerf_acts_bytes": (_i64, [_i64, _int, _int]),
     "dmnerf_mlp_bwd": (_int, [_p, _p, _p, _i64, _int, _int, C.POINTER(_p), _p, _p]),
     "dmnerf_bwd_workspace_bytes": (_i64, [_i64, _int, _int]),

@@ -33,7 +33,7 @@ int64_t x3_image_bytes(int ins_num);
 int pack_x3(const float* const* params, int ins_num, void* packed, cudaStream_t st);
 int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st,
-                    bool f16 = false);
+                    bool f16 = false, bool dens = false);
 int tc_debug_flags();
 // mlp_tc_bwd.cu
 int64_t bf16_acts_bytes(int64_t n_points);
@@ -124,6 +124,20 @@ extern "C" int dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const fl
                "mlp_fwd: n_samples %d outside [1,4096]", n_samples);
     MlpInput in{rays_o, rays_d, z, nullptr, n_rays * n_samples, n_samples};
     return run_mlp(in, packed, ins_num, mode, raw_out, acts, stream);
+}
+
+extern "C" int dmnerf_mlp_density(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
+                                  const void* packed, int ins_num, int mode, float* sigma_out, void* stream) {
+    if (n_rays == 0) return DMNERF_OK;
+    DM_REQUIRE(rays_o && rays_d && z && packed && sigma_out, DMNERF_EINVAL, "mlp_density: null pointer");
+    DM_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 4096, DMNERF_EUNSUPPORTED,
+               "mlp_density: n_samples %d outside [1,4096]", n_samples);
+    if (int rc = check_ins(ins_num, "mlp_density")) return rc;
+    DM_REQUIRE(mode == DMNERF_MODE_BF16 || mode == DMNERF_MODE_F16, DMNERF_EUNSUPPORTED,
+               "mlp_density: mode %d (the density-only trunk exists for DMNERF_MODE_BF16 / DMNERF_MODE_F16; take raw[...,3] "
+               "of dmnerf_mlp_fwd in the other modes)", mode);
+    MlpInput in{rays_o, rays_d, z, nullptr, n_rays * n_samples, n_samples};
+    return launch_mlp_bf16(in, packed, ins_num, sigma_out, nullptr, as_stream(stream), mode == DMNERF_MODE_F16, true);
 }
 
 extern "C" int dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int ins_num, int mode,

@@ -698,6 +698,49 @@ composite_bwd_rev_kernel(const float* __restrict__ raw, const float* __restrict_
 
 using namespace dmnerf;
 
+// weights [n,s] of render_train (render.py:9-14) from the density alone: the same dists / alpha / transmittance scan as the
+// compositing kernels, chunked like them (CH samples per scan step), so the result is bit-identical to their `weights`.
+namespace dmnerf {
+__global__ void __launch_bounds__(128)
+weights_from_sigma_kernel(const float* __restrict__ sigma, const float* __restrict__ z, const float* __restrict__ rays_d,
+                          int64_t n, int S, int CH, float* __restrict__ weights) {
+    const int lane = threadIdx.x & 31;
+    const int64_t ray = static_cast<int64_t>(blockIdx.x) * 4 + (threadIdx.x >> 5);
+    if (ray >= n) return;
+    const float dx = __ldg(rays_d + ray * 3 + 0), dy = __ldg(rays_d + ray * 3 + 1), dz = __ldg(rays_d + ray * 3 + 2);
+    const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
+    const float* zrow = z + ray * S;
+    float carry = 1.0f;
+    for (int c0 = 0; c0 < S; c0 += CH) {
+        const int cnt = min(CH, S - c0);
+        const int s = c0 + lane;
+        const bool valid = lane < cnt;
+        float dist = 0.f, sg = 0.f;
+        if (valid) {
+            const float zc = __ldg(zrow + s);
+            dist = ((s + 1 < S) ? (__ldg(zrow + s + 1) - zc) : 1e10f) * norm;
+            sg = __ldg(sigma + ray * S + s);
+        }
+        float alpha, trans, w;
+        scan_chunk(sg, dist, valid, lane, carry, alpha, trans, w);
+        if (valid) weights[ray * S + s] = w;
+    }
+}
+}  // namespace dmnerf
+
+extern "C" int dmnerf_weights_from_sigma(const float* sigma, const float* z, const float* rays_d, int64_t n, int s, int c,
+                                         float* weights, void* stream) {
+    if (n == 0) return DMNERF_OK;
+    DM_REQUIRE(sigma && z && rays_d && weights, DMNERF_EINVAL, "weights_from_sigma: null pointer");
+    DM_REQUIRE(n >= 0 && s >= 1 && s <= 1024 && c >= 6 && c <= 128, DMNERF_EUNSUPPORTED,
+               "weights_from_sigma: n_samples %d / channels %d unsupported", s, c);
+    // the scan step dmnerf_composite_fwd would use for raw [n,s,c] (16 samples for wide rows on its bulk path)
+    const int ch = (c > 64 && (static_cast<int64_t>(s) * c) % 4 == 0) ? 16 : 32;
+    weights_from_sigma_kernel<<<static_cast<unsigned>((n + 3) / 4), 128, 0, as_stream(stream)>>>(sigma, z, rays_d, n, s, ch, weights);
+    DM_LAUNCH_CHECK("weights_from_sigma_kernel");
+    return DMNERF_OK;
+}
+
 extern "C" int dmnerf_composite_fwd(const float* raw, const float* z, const float* rays_d, int64_t n, int s, int c,
                                     int flags, float* rgb, float* depth, float* weights, float* ins, float* trans,
                                     void* stream) {

@@ -186,7 +186,10 @@ __global__ void pack_bias_kernel(Params pr, Image im, uint8_t* __restrict__ imag
 // a_ready | epilogue warp 0: 3 total, 4 wait acc_ready | producer 5 wait w_empty
 __device__ long long g_dbg1[8];
 
-template <bool kStash, bool kF16 = false>
+// kDens (inference): DENSITY ONLY -- the trunk T0..T7 and the density dot product, raw_out = sigma [n_points].  What a
+// coarse render pass needs (its colours and instance logits are never looked at: tester.py:73-76 keeps *_fine only); the
+// colour / instance layers T8, T9, the direction embedding and the [n_points, C] output are skipped.
+template <bool kStash, bool kF16 = false, bool kDens = false>
 __global__ void __launch_bounds__(kFwThreads, 1)
 mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags,
                     uint8_t* __restrict__ stash) {
@@ -224,7 +227,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             int stage = 0; uint32_t phase = 0;
             long long dbg_w = 0;
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-                for (int l = 0; l < kLayers; ++l) {
+                for (int l = 0; l < (kDens ? 8 : kLayers); ++l) {
                     const uint32_t bytes = kFwChunkK * im.n[l] * 2;
                     const int chunks = layer_k(l) / kFwChunkK;
                     const uint8_t* src = image + im.chunk_off[l];
@@ -267,7 +270,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
             const uint32_t ring_lo = (sm0 + kFwSmRing) >> 4;
             const uint32_t d_tmem = tmem + t * 256;
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-                for (int l = 0; l < kLayers; ++l) {
+                for (int l = 0; l < (kDens ? 8 : kLayers); ++l) {
                     const uint32_t N = im.n[l];
                     const uint32_t idesc = kF16 ? ptx::idesc_f16(kTile, N) : ptx::idesc_bf16(kTile, N);
                     const int chunks = layer_k(l) / kFwChunkK, last = chunks - (l == 9);   // T0..T8: + the bias step
@@ -365,13 +368,21 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                         }
                         if constexpr (kStash)
                             mword = store_kg_mask(a_base, cb * 4 + g, row, v, gst, (l == 8 ? kStHid : kStH0 + 32 * l) + cb * 4 + g, g, mword);
-                        else
+                        else if (!(kDens && l == 7))          // density only: nobody reads h7 as an operand
                             store_kg<kF16>(a_base, cb * 4 + g, row, v, true);
                     }
                     // one coalesced 128-byte line of sign masks per warp and 32 columns (read by the dgrad chain)
                     if constexpr (kStash) *reinterpret_cast<uint32_t*>(mst + tc_mask_word(sblk, l, half, cb & 3, row & 63)) = mword;
                 }
-                if (l == 7) {
+                if constexpr (kDens) {
+                    if (l == 7) {
+                        // sigma = w_density . relu(h7) + b_density: the two column halves meet in shared memory
+                        if (half == 1) dens_part[row] = dens;
+                        ptx::named_bar_sync(1 + t, 2 * kTile);
+                        if (half == 0 && valid) raw_out[p] = (dens + dens_part[row]) + s_misc[384];
+                        break;                                  // T8 / T9 are not evaluated
+                    }
+                } else if (l == 7) {
                     // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it)
                     if (half == 0) {
                         if (in.x == nullptr) embed_to_ext<kDirFreqs, 0, 4, kF16>(a_base, row, dir, gst, kStDir);
@@ -384,6 +395,7 @@ mlp_fwd_bf16_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, fl
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(bars.a_ready(t));
             }
+            if constexpr (kDens) continue;
             // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (half 0) ----
             const long long w9 = clock64();
             ptx::mbar_wait(bars.acc_ready(t), acc_par);
@@ -495,7 +507,8 @@ int launch_masks_from_acts(void* acts, int64_t n_points, cudaStream_t st);
 int persistent_ctas(int sm_count);
 
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st,
-                    bool f16) {
+                    bool f16, bool dens) {
+    DM_REQUIRE(!(dens && stash), DMNERF_EUNSUPPORTED, "mlp_density: inference only (no activation stash)");
     DM_REQUIRE(!(f16 && stash), DMNERF_EUNSUPPORTED,
                "mlp_fwd(f16): the fp16 chain is inference-only (no activation stash; train in DMNERF_MODE_BF16)");
     // debug bits 2/3/5 select the parked variants of csrc/experimental/ (built only with -DDMNERF_EXPERIMENTAL; all
@@ -529,6 +542,16 @@ int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* 
         tc::mlp_fwd_bf16_kernel<true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
             in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags,
             static_cast<uint8_t*>(stash));
+    } else if (dens) {
+        if (f16) {
+            DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+            tc::mlp_fwd_bf16_kernel<false, true, true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
+                in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags, nullptr);
+        } else {
+            DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+            tc::mlp_fwd_bf16_kernel<false, false, true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(
+                in, static_cast<const uint8_t*>(packed), tc::make_image(ins_num), raw_out, g_tc_debug_flags, nullptr);
+        }
     } else if (f16) {
         DM_CUDA(cudaFuncSetAttribute(tc::mlp_fwd_bf16_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
         tc::mlp_fwd_bf16_kernel<false, true><<<grid, tc::kFwThreads, tc::kFwSmTotal, st>>>(

@@ -12,7 +12,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from .._lib import MODE_BF16, MODE_FP32
+from .._lib import MODE_BF16, MODE_F16, MODE_FP32
 
 
 class Embedder:
@@ -100,6 +100,14 @@ class DM_NeRF(nn.Module):
             self._dirty = True
             return ops._MlpFn.apply(rays_o, rays_d, z_vals, None, self.ins_num, mode, packed, *self._ordered_params())
         return ops.mlp_fwd(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)[0]
+
+    def query_density(self, rays_o, rays_d, z_vals) -> torch.Tensor:
+        """sigma[N,S] = ``query_rays(...)[..., 3]`` (same bits), inference only.  In the tensor-core modes the trunk and
+        ``density_linear`` alone are evaluated (dm_nerf.py:82-92); the other modes take the column of the full query."""
+        mode = ops.get_mode()
+        if mode in (MODE_BF16, MODE_F16):
+            return ops.mlp_density(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)
+        return ops.mlp_fwd(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)[0][..., 3].contiguous()
 
     def forward(self, x):
         """x[..., 90] already embedded (dm_nerf.py:80-106)."""

@@ -154,6 +154,29 @@ def mlp_fwd(rays_o, rays_d, z, packed, ins_num: int, mode: int, stash: bool = Fa
     return raw, acts
 
 
+def mlp_density(rays_o, rays_d, z, packed, ins_num: int, mode: int) -> torch.Tensor:
+    """sigma [N,S] = raw[..., 3] of ``mlp_fwd`` (same bits) from the trunk + density_linear alone (tensor-core modes)."""
+    rays_o, rays_d, z = _f32(rays_o, "rays_o"), _f32(rays_d, "rays_d"), _f32(z, "z")
+    n, s = z.shape
+    sigma = torch.empty((n, s), dtype=torch.float32, device=z.device)
+    _timed_call(f"dmnerf_mlp_density[S={s},mode={mode}]", _lib.lib().dmnerf_mlp_density, _ptr(rays_o), _ptr(rays_d), _ptr(z),
+                n, s, _ptr(packed), ins_num, mode, _ptr(sigma), _stream())
+    _count()
+    return sigma
+
+
+def weights_from_sigma(sigma, z, rays_d, channels: int) -> torch.Tensor:
+    """The ``weights`` output of ``composite`` (render.py:9-14) from the density alone; ``channels`` = 5 + ins_num of the
+    model picks the scan step the compositing kernel would use, so the bits are the same."""
+    sigma, z, rays_d = _f32(sigma, "sigma"), _f32(z, "z_vals"), _f32(rays_d, "rays_d")
+    n, s = sigma.shape
+    w = torch.empty((n, s), dtype=torch.float32, device=sigma.device)
+    _timed_call(f"dmnerf_weights_from_sigma[S={s}]", _lib.lib().dmnerf_weights_from_sigma, _ptr(sigma), _ptr(z), _ptr(rays_d),
+                n, s, int(channels), _ptr(w), _stream())
+    _count()
+    return w
+
+
 def mlp_fwd_embedded(x, packed, ins_num: int, mode: int, stash: bool = False):
     x = _f32(x, "x")
     if x.shape[-1] != 90:

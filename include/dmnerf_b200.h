@@ -68,6 +68,16 @@ int  dmnerf_mlp_fwd(const float* rays_o, const float* rays_d, const float* z, in
  * tools/mesh_generator.py:45). */
 int  dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int ins_num, int mode,
                              float* raw_out, void* acts, void* stream);
+/* Density only (inference): sigma_out [n_rays, n_samples] = raw[..., 3] of dmnerf_mlp_fwd, bit for bit, from the trunk
+ * mlps.0..7 + density_linear alone (networks/dm_nerf.py:82-92); the colour / instance layers are not evaluated.  What a
+ * coarse RENDER pass needs: its rgb / instance outputs are never read (networks/tester.py:73-76 keeps *_fine), only its
+ * weights steer the fine samples (render.py:63-70).  DMNERF_MODE_BF16 / DMNERF_MODE_F16 only. */
+int  dmnerf_mlp_density(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
+                        const void* packed, int ins_num, int mode, float* sigma_out, void* stream);
+/* weights [n,s] of render_train (render.py:9-14: dists, alpha, transmittance, w = alpha T) from sigma [n,s] alone -- the same
+ * bits as the `weights` output of dmnerf_composite_fwd on a raw [n,s,c] with that density (c = 5 + ins_num picks its scan step). */
+int  dmnerf_weights_from_sigma(const float* sigma, const float* z, const float* rays_d, int64_t n, int s, int c,
+                               float* weights, void* stream);
 int64_t dmnerf_acts_bytes(int64_t n_points, int ins_num, int mode);
 /* a12: parameter gradients of the MLP given d(raw) [n_points, 5+ins_num] (the autograd of
  * networks/dm_nerf.py:80-106 that total_loss.backward() runs, train_dmsr.py:63).  packed: the image of

@@ -570,6 +570,41 @@ def test_tensor_modes_at_the_edges_of_the_shape_contract(k):
         ops.set_mode("fp32")
 
 
+@pytest.mark.parametrize("mode", ["fp16", "bf16", "tc32", "fp32"])
+def test_lean_coarse_pass_renders_the_same_frame(mode):
+    """``frame.render_pixels`` evaluates only the density trunk in the coarse pass (``dmnerf_mlp_density`` +
+    ``dmnerf_weights_from_sigma``: the coarse colours / instance logits are never read by a render caller,
+    tester.py:73-76).  The frame must be bit-identical to the one driven through ``dm_nerf`` (full coarse pass), the density
+    must equal raw[..., 3] and the weights the compositing kernel's, for K below and above its wide-row threshold."""
+    from dm_nerf_b200 import ops, synth
+    from dm_nerf_b200.frame import render_pixels
+    from dm_nerf_b200.networks.render import render_train
+    H, W = 24, 40
+    try:
+        ops.set_mode(mode)
+        for k in (32, 93):
+            mc, mf = make_model(k, 41, 8.0), make_model(k, 42, 8.0)
+            pe, ve = embedders()
+            Kmat, c2w = synth.dmsr_camera(H, W, 3)
+            a = {k_: v.clone() for k_, v in render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0, lean_coarse=False).items()}
+            b = render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0, lean_coarse=True)
+            for key in ("rgb", "depth", "ins", "labels"):
+                assert torch.equal(a[key], b[key]), (mode, k, key)
+            gen = torch.Generator().manual_seed(k)
+            n, s = 37, 64
+            o = ((torch.rand(n, 3, generator=gen) - 0.5) * 2).to(DEV)
+            d = torch.randn(n, 3, generator=gen).to(DEV)
+            z = torch.sort(torch.rand(n, s, generator=gen) * 11 + 4, -1)[0].to(DEV)
+            with torch.no_grad():
+                raw = mc.query_rays(o, d, z)
+                sigma = mc.query_density(o, d, z)
+                assert torch.equal(sigma, raw[..., 3]), (mode, k)
+                w_ref = render_train(raw, z, d)[1]
+                assert torch.equal(ops.weights_from_sigma(sigma, z, d, k + 5), w_ref), (mode, k)
+    finally:
+        ops.set_mode("fp32")
+
+
 def test_render_tensor_modes_on_a_trained_field():
     """north_star's reduced-precision clause (PSNR within 0.05 dB, label agreement >= 99.9 %), WITHOUT a margin filter,
     on a 160x120 frame of a field trained here (600 graph steps on a 16-block synthetic view make the instance head
