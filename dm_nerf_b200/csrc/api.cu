@@ -31,7 +31,8 @@ int64_t bf16_image_bytes(int ins_num);
 int pack_bf16(const float* const* params, int ins_num, void* packed, cudaStream_t st, bool f16 = false);
 int64_t x3_image_bytes(int ins_num);
 int pack_x3(const float* const* params, int ins_num, void* packed, cudaStream_t st);
-int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st);
+int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st,
+                  bool dens = false);
 int launch_mlp_bf16(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st,
                     bool f16 = false, bool dens = false);
 int tc_debug_flags();
@@ -133,10 +134,11 @@ extern "C" int dmnerf_mlp_density(const float* rays_o, const float* rays_d, cons
     DM_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 4096, DMNERF_EUNSUPPORTED,
                "mlp_density: n_samples %d outside [1,4096]", n_samples);
     if (int rc = check_ins(ins_num, "mlp_density")) return rc;
-    DM_REQUIRE(mode == DMNERF_MODE_BF16 || mode == DMNERF_MODE_F16, DMNERF_EUNSUPPORTED,
-               "mlp_density: mode %d (the density-only trunk exists for DMNERF_MODE_BF16 / DMNERF_MODE_F16; take raw[...,3] "
-               "of dmnerf_mlp_fwd in the other modes)", mode);
+    DM_REQUIRE(mode == DMNERF_MODE_BF16 || mode == DMNERF_MODE_F16 || mode == DMNERF_MODE_TC32, DMNERF_EUNSUPPORTED,
+               "mlp_density: mode %d (the density-only trunk exists for the tensor-core modes; take raw[...,3] of "
+               "dmnerf_mlp_fwd in DMNERF_MODE_FP32)", mode);
     MlpInput in{rays_o, rays_d, z, nullptr, n_rays * n_samples, n_samples};
+    if (mode == DMNERF_MODE_TC32) return launch_mlp_x3(in, packed, ins_num, sigma_out, nullptr, as_stream(stream), true);
     return launch_mlp_bf16(in, packed, ins_num, sigma_out, nullptr, as_stream(stream), mode == DMNERF_MODE_F16, true);
 }
 

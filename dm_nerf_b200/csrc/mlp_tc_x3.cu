@@ -124,6 +124,8 @@ static_assert(kFwSmDens - kFwSmBar >= 8 * (2 * kFwStages + 5) + 8, "barrier bloc
 // l & 1), and the epilogue walks the layer output in four 64-column quarters, every warp taking 16 columns of each, and
 // signals a_ready[j] after quarter j.  Quarter j is K-chunks 2j, 2j+1 of the next layer, so the next layer's products
 // start one quarter into this layer's epilogue and run under the other three.
+// kDens: density only (raw_out = sigma [n_points]): the trunk T0..T7 and the density dot product, as in mlp_tc.cu.
+template <bool kDens>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, float* __restrict__ raw_out, int flags) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -160,7 +162,7 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
             int stage = 0; uint32_t phase = 0;
             long long dbg_w = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                for (int l = 0; l < kLayers; ++l) {
+                for (int l = 0; l < (kDens ? 8 : kLayers); ++l) {
                     const uint32_t bytes = kFwChunkK * im.n[l] * 2;
                     const int parts = 2 * (layer_k(l) / kFwChunkK);
                     const uint8_t* src = image + im.chunk_off[l];
@@ -196,7 +198,7 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
             long long dbg_f = 0, dbg_a = 0;
             const long long dbg_start = clock64();
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                for (int l = 0; l < kLayers; ++l) {
+                for (int l = 0; l < (kDens ? 8 : kLayers); ++l) {
                     const uint32_t N = im.n[l];
                     const uint32_t idesc = ptx::idesc_f16(kTile, N);
                     const int chunks = layer_k(l) / kFwChunkK;
@@ -320,7 +322,17 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
 #pragma unroll
                             for (int e = 0; e < 8; ++e) dens = fmaf(fmaxf(v[e], 0.f), s_misc[128 + col0 + g * 8 + e], dens);
                         }
-                        store_split(sm0, (col0 >> 3) + g, row, v, true);
+                        if (!(kDens && l == 7)) store_split(sm0, (col0 >> 3) + g, row, v, true);
+                    }
+                    if constexpr (kDens) {
+                        if (l == 7) {
+                            if (j < 3) continue;                       // nothing is handed on: no operand, no a_ready
+                            dens_part[wq * kTile + row] = dens;
+                            ptx::named_bar_sync(1, 4 * kTile);
+                            if (wq == 0 && valid)
+                                raw_out[p] = ((dens_part[row] + dens_part[kTile + row]) + (dens_part[2 * kTile + row] + dens_part[3 * kTile + row])) + s_misc[384];
+                            break;
+                        }
                     }
                     if (l == 7 && j == 3) {
                         // dir-embedding replaces the pos-embedding in EXT (T5 is long done with it): one k-group per slot
@@ -338,7 +350,11 @@ mlp_fwd_x3_kernel(MlpInput in, const uint8_t* __restrict__ image, Image im, floa
                     ptx::tc_fence_before();
                     ptx::mbar_arrive(bars.a_ready(j));
                 }
+                if constexpr (kDens) {
+                    if (l == 7) break;                                 // T8 / T9 are not evaluated
+                }
             }
+            if constexpr (kDens) continue;
             // ---- T9: heads -> fp32 raw row [rgb3 | sigma | ins K+1], staged in smem, bulk-stored (warp slot 0) ----
             const long long w9 = clock64();
             ptx::mbar_wait(bars.acc_ready(), acc_par);
@@ -416,7 +432,7 @@ int pack_x3(const float* const* params, int ins_num, void* packed, cudaStream_t 
     return DMNERF_OK;
 }
 
-int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st) {
+int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* raw_out, void* stash, cudaStream_t st, bool dens) {
     DM_REQUIRE(!stash, DMNERF_EUNSUPPORTED,
                "mlp_fwd(tc32): the split-fp16 chain is inference-only (no activation stash; train in DMNERF_MODE_BF16 or FP32)");
     static int sm_count = 0;
@@ -430,9 +446,15 @@ int launch_mlp_x3(const MlpInput& in, const void* packed, int ins_num, float* ra
     const int64_t tiles = (in.n_points + tc::kTile - 1) / tc::kTile;
     const int sms = persistent_ctas(sm_count);
     const unsigned grid = static_cast<unsigned>(tiles < sms ? tiles : sms);
-    DM_CUDA(cudaFuncSetAttribute(tc::x3::mlp_fwd_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
-    tc::x3::mlp_fwd_x3_kernel<<<grid, tc::x3::kThreads, tc::kFwSmTotal, st>>>(in, static_cast<const uint8_t*>(packed),
-                                                                            tc::x3::make_image_x3(ins_num), raw_out, tc_debug_flags());
+    if (dens) {
+        DM_CUDA(cudaFuncSetAttribute(tc::x3::mlp_fwd_x3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+        tc::x3::mlp_fwd_x3_kernel<true><<<grid, tc::x3::kThreads, tc::kFwSmTotal, st>>>(in, static_cast<const uint8_t*>(packed),
+                                                                                      tc::x3::make_image_x3(ins_num), raw_out, tc_debug_flags());
+    } else {
+        DM_CUDA(cudaFuncSetAttribute(tc::x3::mlp_fwd_x3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kFwSmTotal));
+        tc::x3::mlp_fwd_x3_kernel<false><<<grid, tc::x3::kThreads, tc::kFwSmTotal, st>>>(in, static_cast<const uint8_t*>(packed),
+                                                                                       tc::x3::make_image_x3(ins_num), raw_out, tc_debug_flags());
+    }
 
     DM_LAUNCH_CHECK("mlp_fwd_x3_kernel");
     return DMNERF_OK;

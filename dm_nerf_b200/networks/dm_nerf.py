@@ -12,7 +12,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from .._lib import MODE_BF16, MODE_F16, MODE_FP32
+from .._lib import MODE_BF16, MODE_F16, MODE_FP32, MODE_TC32
 
 
 class Embedder:
@@ -105,7 +105,7 @@ class DM_NeRF(nn.Module):
         """sigma[N,S] = ``query_rays(...)[..., 3]`` (same bits), inference only.  In the tensor-core modes the trunk and
         ``density_linear`` alone are evaluated (dm_nerf.py:82-92); the other modes take the column of the full query."""
         mode = ops.get_mode()
-        if mode in (MODE_BF16, MODE_F16):
+        if mode in (MODE_BF16, MODE_F16, MODE_TC32):
             return ops.mlp_density(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)
         return ops.mlp_fwd(rays_o, rays_d, z_vals, self.packed(mode), self.ins_num, mode)[0][..., 3].contiguous()
 

@@ -71,7 +71,7 @@ int  dmnerf_mlp_fwd_embedded(const float* x, int64_t m, const void* packed, int 
 /* Density only (inference): sigma_out [n_rays, n_samples] = raw[..., 3] of dmnerf_mlp_fwd, bit for bit, from the trunk
  * mlps.0..7 + density_linear alone (networks/dm_nerf.py:82-92); the colour / instance layers are not evaluated.  What a
  * coarse RENDER pass needs: its rgb / instance outputs are never read (networks/tester.py:73-76 keeps *_fine), only its
- * weights steer the fine samples (render.py:63-70).  DMNERF_MODE_BF16 / DMNERF_MODE_F16 only. */
+ * weights steer the fine samples (render.py:63-70).  Tensor-core modes (BF16 / F16 / TC32) only. */
 int  dmnerf_mlp_density(const float* rays_o, const float* rays_d, const float* z, int64_t n_rays, int n_samples,
                         const void* packed, int ins_num, int mode, float* sigma_out, void* stream);
 /* weights [n,s] of render_train (render.py:9-14: dists, alpha, transmittance, w = alpha T) from sigma [n,s] alone -- the same
