@@ -1,17 +1,19 @@
 // mlp_tc_x3.cu -- a1+a2+a9 in DMNERF_MODE_TC32: the fp32-accurate tensor-core chain.  Same network walk as
 // mlp_tc.cu (T0..T9, the two linear->linear pairs composed at pack time) but every operand is an fp16 hi+lo
-// PAIR (x = hi + lo, 22 significand bits) and every layer is three tcgen05 products with fp32 accumulation:
-//     D0 = A_hi W_hi^T + A_hi W_lo^T + bias        D1 = A_lo W_hi^T        out = D0 + D1
+// PAIR (x = hi + lo, 22 significand bits) and every layer is three tcgen05 products into ONE fp32 accumulator:
+//     D = A_hi W_hi^T + A_lo W_hi^T + A_hi W_lo^T + bias (a three-term fp16 split against a ones operand)
 // (the dropped A_lo W_lo^T term is ~2^-22 relative).  This is the "3x split" SURVEY 7 hard-part 1 names: it
-// holds the reference's fp32 forward (networks/dm_nerf.py:80-106) to ~1e-6 relative where the bf16/fp16
-// chains sit at 4e-3 / 5e-4, at 3x the MMA count instead of the CUDA-core kernel's 34x the time.
+// holds the reference's fp32 forward (networks/dm_nerf.py:80-106) to ~1e-6 where the bf16 / fp16 chains sit at
+// 2e-3 / 2e-4, at 3x the MMA count instead of the CUDA-core kernel's 34x the time.
 //
-// Work decomposition: one CTA per SM, ONE 128-point tile at a time (the hi and lo images of the activations
-// fill the two A regions the bf16 kernel uses for its tile pair).  Warps 0-15 epilogue (thread == TMEM lane x
-// column quarter), warp 16 weight producer, warp 17 issues the D0 products, warp 18 the D1 products.  The
-// weight stream interleaves [chunk c hi][chunk c lo]; both issuers walk every ring stage (w_empty counts 2).
-// Embeddings: sin/cos of x*2^f evaluated per octave in fp32 (no angle doubling -- its error grows as 2^f ulp).
-// Inference only (no activation stash).
+// Work decomposition: one CTA per SM, ONE 128-point tile at a time (the hi and lo images of the activations fill
+// the two A regions the pair kernel uses for its two tiles).  Warps 0-15 epilogue (thread == TMEM lane x 16-column
+// slot of every output quarter), warp 16 weight producer, warp 17 the issuer.  The weight stream interleaves
+// [chunk c hi][chunk c lo] through a 4 x 16 KB ring: a hi stage feeds 4 MMAs, a lo stage 2.  The accumulator
+// alternates between the two halves of TMEM from layer to layer and the epilogue hands the output on in four
+// 64-column quarters (a_ready[j]), so the next layer's products start one quarter into the epilogue (see the
+// comment at the kernel).  Embeddings: sin/cos of x*2^f evaluated per octave in fp32 (no angle doubling -- its
+// error grows as 2^f ulp).  Inference only (no activation stash); kDens = density-only coarse pass.
 #include "mlp_tc_common.cuh"
 #include <cuda_fp16.h>
 
