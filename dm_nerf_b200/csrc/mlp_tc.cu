@@ -3,6 +3,9 @@
 // shared memory (activations never touch HBM), weights streamed L2 -> smem by the TMA engine
 // (1-D bulk async copies into a 3-stage mbarrier ring).
 //
+// Template switches of the one kernel: kStash (training: operands and ReLU sign masks mirrored to HBM), kF16 (fp16
+// instead of bf16 operands: DMNERF_MODE_F16, inference), kDens (density-only coarse pass: T0..T7, sigma out).
+//
 // Work decomposition: one CTA per SM, each looping over pairs of 128-point tiles (X, Y).  Both
 // tiles walk the layers in lockstep so every streamed weight chunk feeds 4 MMAs (2 k-steps x 2
 // tiles).  Warp roles: warps 0-3 epilogue of X, warps 4-7 epilogue of Y (thread == point/TMEM lane),

@@ -21,8 +21,9 @@ launches = 0
 
 
 def set_mode(mode) -> None:
-    """'fp32' (CUDA-core parity mode) or 'bf16' (tcgen05 tensor-core mode) for MLP queries, forward and
-    (when gradients are enabled) backward."""
+    """Arithmetic of the MLP queries: 'fp32' (CUDA cores, parity mode), 'bf16' (tcgen05 chain, forward and -- with
+    gradients enabled -- backward: the training mode), 'fp16' (same chain, fp16 operands, inference only: the rendering
+    mode), 'tc32' (tcgen05, fp16 hi+lo split x3: fp32-accurate, inference only)."""
     global _default_mode
     _default_mode = _MODE_NAMES[mode] if isinstance(mode, str) else int(mode)
 
