@@ -118,6 +118,10 @@ _SIGNATURES = {
     "dmnerf_sample_pdf": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
     "dmnerf_sample_cdf": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
     "dmnerf_fine_z": (_int, [_p, _p, _p, _i64, _i64, _int, _int, _p, _p, _p]),
+    "dmnerf_coarse_tail": (_int, [_p, _p, _i64, _p, _p, _i64, _i64, _int, _int, _int, _p, _p, _p]),
+    "dmnerf_render_workspace_bytes": (_i64, [_i64, _i64, _int, _int, _int, _int]),
+    "dmnerf_render_full": (_int, [_int, _int, _p, _p, _i64, _i64, _p, _p, _int, _int, _p, _p, _int, _int, _i64, _p, _i64,
+                                  _p, _p, _p, _p, _p]),
     "dmnerf_sort_cat": (_int, [C.POINTER(_p), C.POINTER(_int), _int, _i64, _p, _p]),
     "dmnerf_jitter_z": (_int, [_p, _p, _i64, _int, _p, _p]),
     "dmnerf_penalizer_fwd": (_int, [_p, _p, _p, _p, _i64, _int, _int, _f, _f, _int, _p, _p, _p]),

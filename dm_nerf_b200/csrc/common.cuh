@@ -69,4 +69,23 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// per-sample alpha / transmittance for one chunk of <= 32 samples of a ray (render.py:9-14), one lane per sample;
+// returns w, updates carry.  Shared by the compositing kernels and the coarse tail so that both produce the same bits.
+__device__ __forceinline__ void scan_chunk(float sigma, float dist, bool valid, int lane, float& carry,
+                                           float& alpha, float& trans, float& w) {
+    alpha = 1.0f - expf(-fmaxf(sigma, 0.0f) * dist);
+    float t = valid ? (1.0f - alpha) + 1e-10f : 1.0f;
+    float incl = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl *= v;
+    }
+    float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane == 0) excl = 1.0f;
+    trans = carry * excl;
+    w = valid ? alpha * trans : 0.0f;
+    carry *= __shfl_sync(0xffffffffu, incl, 31);
+}
+
 }  // namespace dmnerf

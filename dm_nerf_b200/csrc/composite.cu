@@ -34,24 +34,6 @@ __device__ __forceinline__ void unstage_chunk(const float* tile, float* __restri
     }
 }
 
-// per-sample alpha / transmittance for one chunk; returns w, updates carry.
-__device__ __forceinline__ void scan_chunk(float sigma, float dist, bool valid, int lane, float& carry,
-                                           float& alpha, float& trans, float& w) {
-    alpha = 1.0f - expf(-fmaxf(sigma, 0.0f) * dist);
-    float t = valid ? (1.0f - alpha) + 1e-10f : 1.0f;
-    float incl = t;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        float v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl *= v;
-    }
-    float excl = __shfl_up_sync(0xffffffffu, incl, 1);
-    if (lane == 0) excl = 1.0f;
-    trans = carry * excl;
-    w = valid ? alpha * trans : 0.0f;
-    carry *= __shfl_sync(0xffffffffu, incl, 31);
-}
-
 __global__ void __launch_bounds__(kCompWarps * 32)
 composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays_d,
                      int64_t n, int S, int C, int flags, float* __restrict__ rgb, float* __restrict__ depth,

@@ -154,10 +154,15 @@ __device__ __forceinline__ bool warp_sorted(const float* v, int n, int lane) {
     return __all_sync(0xffffffffu, ok);
 }
 
+// kFromSigma: `weights` holds the coarse DENSITIES [n,sc] instead; the compositing weights (render.py:9-14) are first
+// rebuilt from them with the compositing kernels' own chunked scan (CH samples per step -> the same bits) and never
+// leave the SM unless weights_out asks for them.  z_stride: row stride of z_coarse (0 = one row for every ray).
+template <bool kFromSigma>
 __global__ void __launch_bounds__(kSampWarps * 32)
-fine_z_kernel(const float* __restrict__ z_coarse, const float* __restrict__ weights, const float* __restrict__ u,
-              int64_t u_stride, int64_t n, int sc, int n_imp, int P, int P2, float* __restrict__ z_fine,
-              float* __restrict__ z_samples) {
+fine_z_kernel(const float* __restrict__ z_coarse, int64_t z_stride, const float* __restrict__ weights,
+              const float* __restrict__ rays_d, int CH, const float* __restrict__ u, int64_t u_stride, int64_t n, int sc,
+              int n_imp, int P, int P2, float* __restrict__ z_fine, float* __restrict__ z_samples,
+              float* __restrict__ weights_out) {
     extern __shared__ float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t ray = static_cast<int64_t>(blockIdx.x) * kSampWarps + warp;
@@ -169,10 +174,33 @@ fine_z_kernel(const float* __restrict__ z_coarse, const float* __restrict__ weig
     float* s_w = s_cdf + sc;
     float* s_samp = s_w + sc;
     float* s_zc = s_sort + (P - sc);                       // coarse depths parked at the tail of the output buffer
-    for (int j = lane; j < sc; j += 32) s_zc[j] = z_coarse[ray * sc + j];
+    for (int j = lane; j < sc; j += 32) s_zc[j] = z_coarse[ray * z_stride + j];
     __syncwarp();
     for (int j = lane; j < nb; j += 32) s_bins[j] = __fmul_rn(0.5f, __fadd_rn(s_zc[j + 1], s_zc[j]));
-    for (int j = lane; j < nb - 1; j += 32) s_w[j] = __fadd_rn(weights[ray * sc + 1 + j], 1e-5f);
+    if constexpr (kFromSigma) {
+        const float dx = __ldg(rays_d + ray * 3 + 0), dy = __ldg(rays_d + ray * 3 + 1), dz = __ldg(rays_d + ray * 3 + 2);
+        const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
+        float carry = 1.0f;
+        for (int c0 = 0; c0 < sc; c0 += CH) {
+            const int cnt = min(CH, sc - c0);
+            const int s = c0 + lane;
+            const bool valid = lane < cnt;
+            float dist = 0.f, sg = 0.f;
+            if (valid) {
+                const float zc = s_zc[s];
+                dist = ((s + 1 < sc) ? (s_zc[s + 1] - zc) : 1e10f) * norm;
+                sg = __ldg(weights + ray * sc + s);
+            }
+            float alpha, trans, w;
+            scan_chunk(sg, dist, valid, lane, carry, alpha, trans, w);
+            if (valid) {
+                if (s >= 1 && s <= nb - 1) s_w[s - 1] = __fadd_rn(w, 1e-5f);
+                if (weights_out) weights_out[ray * sc + s] = w;
+            }
+        }
+    } else {
+        for (int j = lane; j < nb - 1; j += 32) s_w[j] = __fadd_rn(weights[ray * sc + 1 + j], 1e-5f);
+    }
     __syncwarp();
     build_cdf(s_cdf, s_w, nb, lane);
     for (int i = lane; i < n_imp; i += 32) {
@@ -280,22 +308,46 @@ extern "C" int dmnerf_sample_cdf(const float* bins, const float* cdf, const floa
     return launch_sample(bins, cdf, 1, u, u_stride, n, n_bins, n_samples, z_out, inds_out, stream);
 }
 
-extern "C" int dmnerf_fine_z(const float* z_coarse, const float* weights, const float* u, int64_t u_stride, int64_t n,
-                             int sc, int n_imp, float* z_fine, float* z_samples, void* stream) {
-    if (n <= 0) return DMNERF_OK;
-    DM_REQUIRE(z_coarse && weights && z_fine, DMNERF_EINVAL, "fine_z: null pointer");
+static int launch_fine_z(bool from_sigma, const float* z_coarse, int64_t z_stride, const float* w_or_sigma,
+                         const float* rays_d, int ch, const float* u, int64_t u_stride, int64_t n, int sc, int n_imp,
+                         float* z_fine, float* z_samples, float* weights_out, void* stream, const char* who) {
     DM_REQUIRE(sc >= 4 && sc <= 512 && n_imp >= 2 && sc + n_imp <= 1024, DMNERF_EUNSUPPORTED,
-               "fine_z: sc %d / n_importance %d unsupported", sc, n_imp);
-    if (n <= 0) return DMNERF_OK;
+               "%s: sc %d / n_importance %d unsupported", who, sc, n_imp);
     int P = 1, P2 = 1;
     while (P < sc + n_imp) P <<= 1;
     while (P2 < n_imp) P2 <<= 1;
     const size_t smem = static_cast<size_t>(kSampWarps) * (P + 3 * sc + P2) * sizeof(float);
     const unsigned grid = static_cast<unsigned>((n + kSampWarps - 1) / kSampWarps);
-    fine_z_kernel<<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(z_coarse, weights, u, u_stride, n, sc, n_imp, P,
-                                                                     P2, z_fine, z_samples);
+    if (from_sigma)
+        fine_z_kernel<true><<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(
+            z_coarse, z_stride, w_or_sigma, rays_d, ch, u, u_stride, n, sc, n_imp, P, P2, z_fine, z_samples, weights_out);
+    else
+        fine_z_kernel<false><<<grid, kSampWarps * 32, smem, as_stream(stream)>>>(
+            z_coarse, z_stride, w_or_sigma, nullptr, 32, u, u_stride, n, sc, n_imp, P, P2, z_fine, z_samples, nullptr);
     DM_LAUNCH_CHECK("fine_z_kernel");
     return DMNERF_OK;
+}
+
+extern "C" int dmnerf_fine_z(const float* z_coarse, const float* weights, const float* u, int64_t u_stride, int64_t n,
+                             int sc, int n_imp, float* z_fine, float* z_samples, void* stream) {
+    if (n <= 0) return DMNERF_OK;
+    DM_REQUIRE(z_coarse && weights && z_fine, DMNERF_EINVAL, "fine_z: null pointer");
+    return launch_fine_z(false, z_coarse, sc, weights, nullptr, 32, u, u_stride, n, sc, n_imp, z_fine, z_samples, nullptr,
+                         stream, "fine_z");
+}
+
+extern "C" int dmnerf_coarse_tail(const float* sigma, const float* z_coarse, int64_t z_stride, const float* rays_d,
+                                  const float* u, int64_t u_stride, int64_t n, int sc, int c, int n_imp, float* z_fine,
+                                  float* weights_out, void* stream) {
+    if (n <= 0) return DMNERF_OK;
+    DM_REQUIRE(sigma && z_coarse && rays_d && z_fine, DMNERF_EINVAL, "coarse_tail: null pointer");
+    DM_REQUIRE(z_stride == 0 || z_stride >= sc, DMNERF_EINVAL, "coarse_tail: z_stride %lld (0 or >= sc)",
+               static_cast<long long>(z_stride));
+    DM_REQUIRE(c >= 6 && c <= 128, DMNERF_EUNSUPPORTED, "coarse_tail: channels %d unsupported", c);
+    // the scan step dmnerf_composite_fwd would use for raw [n,sc,c] (16 samples for wide rows on its bulk path)
+    const int ch = (c > 64 && (static_cast<int64_t>(sc) * c) % 4 == 0) ? 16 : 32;
+    return launch_fine_z(true, z_coarse, z_stride, sigma, rays_d, ch, u, u_stride, n, sc, n_imp, z_fine, nullptr,
+                         weights_out, stream, "coarse_tail");
 }
 
 extern "C" int dmnerf_sort_cat(const float* const* srcs, const int* lens, int parts, int64_t n, float* out,

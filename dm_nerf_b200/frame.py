@@ -20,12 +20,14 @@ def render_pixels(position_embedder, view_embedder, model_coarse, model_fine, hw
                   n_samples: int = 64, n_importance: int = 128, pix0: int = 0, count: Optional[int] = None,
                   chunk: int = 32768, rays: Optional[torch.Tensor] = None, labels: bool = True,
                   out: Optional[Dict[str, torch.Tensor]] = None, balance: bool = True,
-                  lean_coarse: bool = True) -> Dict[str, torch.Tensor]:
+                  lean_coarse: bool = True, paced: bool = True) -> Dict[str, torch.Tensor]:
     """Deterministic (perturb=0) render of a pixel range.  Returns rgb [n,3], depth [n], ins [n,K]
     and (optionally) labels uint8 [n].  ``rays`` [2,n,3] overrides in-kernel ray generation.
     ``chunk`` bounds the rays per pass (raw_fine scratch = chunk * 192 * C * 4 bytes); with ``balance`` the range is cut
     into equal passes of at most ``chunk`` rays instead of full chunks plus a short tail (the persistent MLP kernels
-    deal 256-point tile pairs round-robin to the SMs: a 5,632-ray tail costs whole rounds for a fraction of the work)."""
+    deal 256-point tile pairs round-robin to the SMs: a 5,632-ray tail costs whole rounds for a fraction of the work).
+    ``paced`` (with ``lean_coarse``, in-kernel ray generation and ``balance``): the whole range goes through ONE
+    ``dmnerf_render_full`` call -- same kernels, same results bit for bit, no interpreter or staging copy between launches."""
     H, W, K = hwk
     dev = next(model_fine.parameters()).device
     if count is None:
@@ -47,6 +49,13 @@ def render_pixels(position_embedder, view_embedder, model_coarse, model_fine, hw
     lean = bool(lean_coarse) and hasattr(model_coarse, "query_density") and hasattr(model_fine, "query_rays") \
         and getattr(position_embedder, "num_freqs", None) == 10 and getattr(view_embedder, "num_freqs", None) == 4
     u_det = torch.linspace(0., 1., steps=n_importance, device=dev)
+    if lean and rays is None and paced and balance and count > 0 and model_coarse.ins_num == kins:
+        # every launch of every pass enqueued by ONE C call, compositing straight into the frame buffers
+        mode = ops.get_mode()
+        with torch.no_grad():
+            ops.render_full(int(H), int(W), K, c2w, pix0, count, z_row, int(n_importance), model_coarse.packed(mode),
+                            model_fine.packed(mode), kins, mode, chunk, out, labels, u_row=u_det)
+        return out
     with torch.no_grad():
         for a in range(0, count, chunk):
             b = min(count, a + chunk)

@@ -178,6 +178,68 @@ def weights_from_sigma(sigma, z, rays_d, channels: int) -> torch.Tensor:
     return w
 
 
+def coarse_tail(sigma, z_coarse, rays_d, channels: int, n_importance: int, u: Optional[torch.Tensor] = None,
+                want_weights: bool = False):
+    """``weights_from_sigma`` + ``fine_z`` in one launch (``dmnerf_coarse_tail``): z_fine [n, sc + n_importance] (and the
+    coarse weights when asked).  ``z_coarse`` [n,sc], or one row [sc] / [1,sc] shared by every ray."""
+    sigma, z_coarse, rays_d = _f32(sigma, "sigma"), _f32(z_coarse, "z_vals_coarse"), _f32(rays_d, "rays_d")
+    n, sc = sigma.shape
+    if z_coarse.numel() == sc:
+        z_stride = 0
+    else:
+        assert z_coarse.shape == (n, sc), (z_coarse.shape, sigma.shape)
+        z_stride = sc
+    u, stride = _u_args(u, n, n_importance)
+    z_fine = torch.empty((n, sc + n_importance), dtype=torch.float32, device=sigma.device)
+    w = torch.empty((n, sc), dtype=torch.float32, device=sigma.device) if want_weights else None
+    _timed_call("dmnerf_coarse_tail", _lib.lib().dmnerf_coarse_tail, _ptr(sigma), _ptr(z_coarse), z_stride, _ptr(rays_d),
+                _ptr(u), stride, n, sc, int(channels), int(n_importance), _ptr(z_fine), _ptr(w), _stream())
+    _count()
+    return (z_fine, w) if want_weights else z_fine
+
+
+def render_launches(count: int, chunk: int, mode: int, labels: bool = True) -> int:
+    """Kernel launches one ``render_full`` call enqueues (for ``launches`` bookkeeping)."""
+    if count <= 0:
+        return 0
+    passes = -(-count // chunk)
+    per = 5 if mode != MODE_FP32 else 6
+    return 1 + passes * (per + (1 if labels else 0))
+
+
+def render_full(H: int, W: int, K, c2w, pix0: int, count: int, z_row: torch.Tensor, n_importance: int, packed_coarse,
+                packed_fine, ins_num: int, mode: int, chunk: int, out, labels: bool = True,
+                u_row: Optional[torch.Tensor] = None) -> None:
+    """``dmnerf_render_full``: pixels [pix0, pix0+count) of the frame rendered into ``out`` (rgb [count,3], depth
+    [count], ins [count,K], labels uint8 [count]) with every launch enqueued by the one C call."""
+    if count <= 0:
+        return
+    dev = packed_fine.device
+    z_row = _f32(z_row, "z_row").reshape(-1)
+    sc = z_row.numel()
+    if u_row is not None:
+        u_row = _f32(u_row, "u_row").reshape(-1)
+        assert u_row.numel() == n_importance
+    kf = (C.c_float * 9)(*[float(v) for v in torch.as_tensor(K, dtype=torch.float32).cpu().reshape(-1)[:9]])
+    cm = torch.as_tensor(c2w, dtype=torch.float32).cpu()[:3, :4].reshape(-1)
+    cf = (C.c_float * 12)(*[float(v) for v in cm])
+    need = int(_lib.lib().dmnerf_render_workspace_bytes(count, chunk, sc, int(n_importance), int(ins_num), int(mode)))
+    if need < 0:
+        raise RuntimeError(f"render_full: unsupported shape (n_samples {sc}, n_importance {n_importance}, ins_num {ins_num})")
+    ws = torch.empty((need,), dtype=torch.uint8, device=dev)
+    for k, shape, dt in (("rgb", (count, 3), torch.float32), ("depth", (count,), torch.float32),
+                         ("ins", (count, ins_num), torch.float32)) + ((("labels", (count,), torch.uint8),) if labels else ()):
+        t = out[k]
+        if tuple(t.shape) != shape or t.dtype != dt or not t.is_contiguous() or t.device != dev:
+            raise RuntimeError(f"render_full: out[{k!r}] must be a contiguous {dt} tensor of shape {shape} on {dev}")
+    _timed_call("dmnerf_render_full", _lib.lib().dmnerf_render_full, int(H), int(W), kf, cf, int(pix0), int(count),
+                _ptr(z_row), _ptr(u_row), sc, int(n_importance), _ptr(packed_coarse), _ptr(packed_fine), int(ins_num), int(mode),
+                int(chunk), _ptr(ws), need, _ptr(out["rgb"]), _ptr(out["depth"]), _ptr(out["ins"]),
+                _ptr(out["labels"]) if labels else C.c_void_p(0), _stream())
+    passes = -(-count // chunk)
+    _count(render_launches(count, -(-count // passes), mode, labels))
+
+
 def mlp_fwd_embedded(x, packed, ins_num: int, mode: int, stash: bool = False):
     x = _f32(x, "x")
     if x.shape[-1] != 90:

@@ -138,6 +138,15 @@ int  dmnerf_sample_cdf(const float* bins, const float* cdf, const float* u, int6
  * new samples.  z_fine [n, sc+n_imp]; z_samples [n,n_imp] may be NULL. */
 int  dmnerf_fine_z(const float* z_coarse, const float* weights, const float* u, int64_t u_stride, int64_t n,
                    int sc, int n_imp, float* z_fine, float* z_samples, void* stream);
+/* The whole coarse tail of a render pass in one launch (SURVEY 8b `dmnerf_coarse_tail`; networks/render.py:9-14 + 63-70):
+ * compositing weights from the coarse DENSITIES sigma [n,sc] (= raw_coarse[...,3], e.g. dmnerf_mlp_density), then
+ * dmnerf_fine_z on them.  z_coarse: row r at z_coarse + r*z_stride (z_stride = sc for a dense [n,sc] tensor, 0 to share one
+ * row); rays_d [n,3]; c = ins_num + 5 (selects the scan step of the compositing kernel for raw [n,sc,c], so the weights
+ * carry its bits); u / u_stride as in dmnerf_sample_pdf.  z_fine [n, sc+n_imp]; weights_out [n,sc] may be NULL.
+ * Same z_fine, bit for bit, as dmnerf_weights_from_sigma followed by dmnerf_fine_z. */
+int  dmnerf_coarse_tail(const float* sigma, const float* z_coarse, int64_t z_stride, const float* rays_d, const float* u,
+                        int64_t u_stride, int64_t n, int sc, int c, int n_imp, float* z_fine, float* weights_out,
+                        void* stream);
 /* Sorted merge of `parts` ascending-unsorted rows: out[n, sum(len)] = sort(cat(...)) along the
  * last dim (networks/manipulator.py:190,195).  srcs/lens are HOST arrays (<= 8 parts). */
 int  dmnerf_sort_cat(const float* const* srcs, const int* lens, int parts, int64_t n, float* out, void* stream);
@@ -180,6 +189,23 @@ int  dmnerf_rays_k(int H, int W, const float* K_host, const float* c2w_host, int
  * the launch, so a captured training step replays for any view (train_dmsr.py:30-36 draws a new image per step). */
 int  dmnerf_rays_k_dev(int H, int W, const float* K_dev, const float* c2w_dev, int64_t pix0,
                        const int64_t* pix_idx, int64_t n, float* rays_o, float* rays_d, void* stream);
+/* ---- adjacent (8f-1): whole-range deterministic render, paced from C (SURVEY 8b `dmnerf_render_full`) ---------------
+ * Replaces the chunk loop of render_test (networks/tester.py:62-76; perturb = 0, det sampling) for pixels
+ * [pix0, pix0+count) of an HxW frame: per pass of <= chunk rays (count is cut into equal passes of whole 128-point tiles)
+ * dmnerf_rays_k -> coarse pass -> fine depths -> fine query -> compositing -> label argmax, every launch enqueued by this
+ * one call and the compositing kernel writing straight into rgb [count,3], depth [count], ins [count,ins_num];
+ * labels uint8 [count] may be NULL.  Tensor-core modes evaluate the density-only coarse trunk (dmnerf_mlp_density +
+ * dmnerf_coarse_tail); DMNERF_MODE_FP32 the full coarse query + compositing + dmnerf_fine_z.  Results equal the
+ * step-by-step entry points bit for bit.  K_host: 9 floats, c2w_host: 12 floats (3x4), both HOST; z_row: DEVICE, the
+ * n_samples coarse depths shared by every ray (z_val_sample, networks/helpers.py:114-119); u_row: DEVICE, the n_importance
+ * uniforms shared by every ray (helpers.py:137), NULL = linspace(0,1) evaluated in the kernel; packed_*: dmnerf_weights_pack
+ * images of the two models for `mode`; workspace: DEVICE scratch, 256-byte aligned, at least
+ * dmnerf_render_workspace_bytes(count, chunk, ...) bytes (-1: unsupported arguments).  Nothing is allocated. */
+int64_t dmnerf_render_workspace_bytes(int64_t count, int64_t chunk, int n_samples, int n_importance, int ins_num, int mode);
+int  dmnerf_render_full(int H, int W, const float* K_host, const float* c2w_host, int64_t pix0, int64_t count,
+                        const float* z_row, const float* u_row, int n_samples, int n_importance,
+                        const void* packed_coarse, const void* packed_fine, int ins_num, int mode, int64_t chunk, void* workspace,
+                        int64_t workspace_bytes, float* rgb, float* depth, float* ins, uint8_t* labels, void* stream);
 /* Standalone Embedder.embed (networks/dm_nerf.py:37-38): x [n,3] -> out [n, 3+6*n_freqs]. */
 int  dmnerf_embed(const float* x, int64_t n, int n_freqs, float* out, void* stream);
 /* Per-ray label image: plain argmax of a composited instance map whose entries are probabilities already (first

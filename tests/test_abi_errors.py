@@ -168,3 +168,56 @@ def test_inference_only_modes_refuse_training_calls():
     rc = lib.dmnerf_exchange(_p(ori), _p(tar), _p(acc), _p(acc), 1, 0, n, s, c, _p(None), _p(None), _st())
     assert rc == einval and "ori_label" in _lib.last_error(), (rc, _lib.last_error())
     torch.cuda.synchronize()
+
+
+def test_render_full_refuses_bad_arguments():
+    """dmnerf_render_full / dmnerf_coarse_tail (the calls a frame driver makes once per pixel range): short or misaligned
+    workspace, pixels outside the frame, null buffers and unsupported shapes come back as codes with a message, and the
+    call after them renders."""
+    from dm_nerf_b200 import _lib, ops, synth
+    from dm_nerf_b200.networks.dm_nerf import DM_NeRF
+    lib = _lib.lib()
+    codes = _codes()
+    einval, eunsup = codes["DMNERF_EINVAL"], codes["DMNERF_EUNSUPPORTED"]
+    k, H, W, sc, n_imp = 32, 8, 16, 64, 128
+    net = DM_NeRF(8, 256, 63, 27, [4], k)
+    net.load_state_dict(orc.init_params(k, 1))
+    net = net.to(DEV)
+    mode = _lib.MODE_F16
+    packed = net.packed(mode)
+    Kmat, c2w = synth.dmsr_camera(H, W, 0)
+    kf = (C.c_float * 9)(*[float(v) for v in torch.as_tensor(Kmat, dtype=torch.float32).reshape(-1)[:9]])
+    cf = (C.c_float * 12)(*[float(v) for v in torch.as_tensor(c2w, dtype=torch.float32)[:3, :4].reshape(-1)])
+    count = H * W
+    z_row = (4.0 + torch.linspace(0., 1., sc) * 11.0).to(DEV)
+    need = lib.dmnerf_render_workspace_bytes(count, 4096, sc, n_imp, k, mode)
+    assert need > count * (sc + n_imp) * (k + 5) * 4
+    assert lib.dmnerf_render_workspace_bytes(count, 4096, sc, n_imp, 124, mode) == -1
+    assert lib.dmnerf_render_workspace_bytes(0, 4096, sc, n_imp, k, mode) == 0
+    ws = torch.empty(need + 256, dtype=torch.uint8, device=DEV)
+    rgb, depth, ins = torch.empty(count, 3, device=DEV), torch.empty(count, device=DEV), torch.empty(count, k, device=DEV)
+    lab = torch.empty(count, dtype=torch.uint8, device=DEV)
+
+    def run(pix0=0, cnt=count, ws_ptr=None, ws_bytes=need, rgb_t=rgb, n_imp_=n_imp, mode_=mode):
+        ptr = C.c_void_p(ws.data_ptr() if ws_ptr is None else ws_ptr)
+        return lib.dmnerf_render_full(H, W, kf, cf, pix0, cnt, _p(z_row), _p(None), sc, n_imp_, _p(packed), _p(packed), k, mode_,
+                                      4096, ptr, ws_bytes, _p(rgb_t), _p(depth), _p(ins), _p(lab), _st())
+
+    assert run(ws_bytes=need - 1) == einval and "workspace" in _lib.last_error().lower()
+    assert run(ws_ptr=ws.data_ptr() + 4) == einval and "align" in _lib.last_error().lower()
+    assert run(pix0=1) == einval and "frame" in _lib.last_error().lower()
+    assert run(rgb_t=None) == einval and "null" in _lib.last_error().lower()
+    assert run(n_imp_=2000) == eunsup and _lib.last_error()
+    assert run(mode_=9) == eunsup and "mode" in _lib.last_error().lower()
+    assert run(cnt=0) == 0
+    sigma = torch.rand(4, sc, device=DEV)
+    rd = torch.randn(4, 3, device=DEV)
+    zf = torch.empty(4, sc + n_imp, device=DEV)
+    rc = lib.dmnerf_coarse_tail(_p(sigma), _p(z_row), 3, _p(rd), _p(None), 0, 4, sc, k + 5, n_imp, _p(zf), _p(None), _st())
+    assert rc == einval and "z_stride" in _lib.last_error()
+    rc = lib.dmnerf_coarse_tail(_p(None), _p(z_row), 0, _p(rd), _p(None), 0, 4, sc, k + 5, n_imp, _p(zf), _p(None), _st())
+    assert rc == einval and "null" in _lib.last_error().lower()
+    # ... and the next call renders
+    assert run() == 0
+    torch.cuda.synchronize()
+    assert torch.isfinite(rgb).all() and torch.isfinite(ins).all() and int(lab.max()) < k

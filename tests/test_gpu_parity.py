@@ -605,6 +605,56 @@ def test_lean_coarse_pass_renders_the_same_frame(mode):
         ops.set_mode("fp32")
 
 
+def test_coarse_tail_is_weights_from_sigma_plus_fine_z():
+    """``dmnerf_coarse_tail`` (weights from the densities + sample_pdf + sorted merge in one launch, render.py:9-14 and
+    63-70) against the two launches it replaces: z_fine and weights bit for bit -- per-ray and shared coarse depths, det
+    and injected uniforms, negative densities (ReLU), channel counts on both sides of the compositing kernel's wide-row
+    threshold, ragged ray counts."""
+    from dm_nerf_b200 import ops
+    gen = torch.Generator().manual_seed(5)
+    for n, sc, n_imp, c in ((1, 64, 128, 37), (37, 64, 128, 37), (130, 64, 128, 98), (9, 48, 40, 21), (5, 7, 9, 98)):
+        d = torch.randn(n, 3, generator=gen).to(DEV)
+        sigma = (torch.randn(n, sc, generator=gen) * 3).to(DEV)
+        z_full = torch.sort(torch.rand(n, sc, generator=gen) * 11 + 4, -1)[0].to(DEV)
+        z_row = (4.0 + torch.linspace(0., 1., sc) * 11.0).to(DEV)
+        for z in (z_full, z_row):
+            z_dense = z if z.dim() == 2 else z[None].expand(n, sc).contiguous()
+            for u in (None, torch.rand(n, n_imp, generator=gen).to(DEV)):
+                w_ref = ops.weights_from_sigma(sigma, z_dense, d, c)
+                ref = ops.fine_z(z_dense, w_ref, n_imp, u)
+                got, w = ops.coarse_tail(sigma, z, d, c, n_imp, u, want_weights=True)
+                assert torch.equal(w, w_ref), (n, sc, c)
+                assert torch.equal(got, ref), (n, sc, n_imp, c, z.dim(), u is None)
+                assert torch.equal(ops.coarse_tail(sigma, z, d, c, n_imp, u), ref)
+
+
+@pytest.mark.parametrize("mode", ["fp16", "bf16", "tc32", "fp32"])
+def test_render_full_is_the_stepwise_frame(mode):
+    """``dmnerf_render_full`` (tester.py:62-76 paced from C: one call enqueues every launch of every pass and composites
+    straight into the frame buffers) against the same frame driven launch by launch from Python: rgb, depth, instance map
+    and labels bit for bit -- whole frame in one pass, a pixel sub-range in several ragged passes, labels on and off."""
+    from dm_nerf_b200 import ops, synth
+    from dm_nerf_b200.frame import render_pixels
+    H, W = 24, 40
+    try:
+        ops.set_mode(mode)
+        for k in (32, 93):
+            mc, mf = make_model(k, 51, 8.0), make_model(k, 52, 8.0)
+            pe, ve = embedders()
+            Kmat, c2w = synth.dmsr_camera(H, W, 2)
+            for kw in (dict(), dict(pix0=77, count=613, chunk=256), dict(pix0=H * W - 130, chunk=128, labels=False)):
+                a = {k_: v.clone() for k_, v in
+                     render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0, paced=False, **kw).items()}
+                n0 = ops.launches
+                b = render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0, paced=True, **kw)
+                assert ops.launches > n0
+                assert set(a) == set(b)
+                for key in a:
+                    assert torch.equal(a[key], b[key]), (mode, k, key, kw)
+    finally:
+        ops.set_mode("fp32")
+
+
 def test_render_tensor_modes_on_a_trained_field():
     """north_star's reduced-precision clause (PSNR within 0.05 dB, label agreement >= 99.9 %), WITHOUT a margin filter,
     on a 160x120 frame of a field trained here (600 graph steps on a 16-block synthetic view make the instance head

@@ -1,0 +1,33 @@
+"""A/B on one box: the 640x480 frame (C2) through dmnerf_render_full (one C call) against the same frame driven launch
+by launch from Python.  usage: python tools/paced_ab.py [mode] [frames]"""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from dm_nerf_b200 import ops, synth
+from dm_nerf_b200.frame import render_pixels
+from dm_nerf_b200.networks.dm_nerf import DM_NeRF, get_embedder
+
+mode = sys.argv[1] if len(sys.argv) > 1 else "fp16"
+frames = int(sys.argv[2]) if len(sys.argv) > 2 else 10
+H, W, k = 480, 640, 32
+ops.set_mode(mode)
+mc, mf = DM_NeRF(8, 256, 63, 27, [4], k), DM_NeRF(8, 256, 63, 27, [4], k)
+mc.load_state_dict(synth.init_state_dict(k, 1)); mf.load_state_dict(synth.init_state_dict(k, 2))
+mc, mf = mc.cuda(), mf.cuda()
+pe, ve = get_embedder(10, 0)[0], get_embedder(4, 0)[0]
+Kmat, c2w = synth.dmsr_camera(H, W, 0)
+out = None
+res = {}
+for rep in range(3):
+    for paced in (False, True):
+        for _ in range(3):
+            out = render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0, paced=paced, out=out)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(frames):
+            out = render_pixels(pe, ve, mc, mf, (H, W, Kmat), c2w, 4.0, 15.0, paced=paced, out=out)
+        b.record(); torch.cuda.synchronize()
+        res.setdefault(paced, []).append(a.elapsed_time(b) / frames)
+for paced, v in res.items():
+    print("paced" if paced else "stepwise", " ".join(f"{x:.3f}" for x in v), "ms/frame")
