@@ -430,6 +430,8 @@ class FrameJob:
         self.local = {kk: v[self.a:self.b] for kk, v in bufs.items()} if cx.rank == 0 else bufs
         self.host_rays = self.host_out = None
         self.lean = True           # render_pixels' default: density-only coarse pass (same frame bit for bit)
+        self.paced = False         # launch by launch from Python, so that KernelTimer brackets every kernel of the timed
+                                   # region; render_pixels' default (ONE dmnerf_render_full call) is timed as render_full_call
 
     def step(self, rays=None):
         from dm_nerf_b200.frame import render_pixels
@@ -437,7 +439,7 @@ class FrameJob:
         pe, ve, mc, mf = self.models
         render_pixels(pe, ve, mc, mf, (self.hw[0], self.hw[1], self.Kmat), self.c2w, self.near, self.far, SC, NIMP,
                       pix0=self.a, count=self.b - self.a, chunk=self.chunk, rays=rays, out=self.local,
-                      lean_coarse=self.lean)
+                      lean_coarse=self.lean, paced=self.paced)
         gather_frame(self.local, self.frame, self.total, self.KEYS)
 
     def prepare_host(self):
@@ -820,6 +822,23 @@ def run_gpu(args):
         finally:
             job.lean = True
 
+    # ---- the same frame through ONE dmnerf_render_full call per rank (frame.render_pixels' default): same kernels, no
+    # interpreter between launches, compositing straight into the frame buffers; speed, and the same frame bit for bit ------
+    paced_leg = None
+    if not args.no_extra:
+        job.paced = True
+        try:
+            job.step()
+            ms_paced = cx.timed(job.step, max(2, min(args.steps, 5)))
+            if cx.rank == 0:
+                same = all(bool(torch.equal(job.frame[kk], frame_tc[kk])) for kk in FrameJob.KEYS)
+                paced_leg = {"ms_per_frame": ms_paced, "value": N_RAYS / (ms_paced / 1000), "unit": "rays/s",
+                             "frame_bit_identical_to_headline": same,
+                             "note": "headline: the same launches issued one by one from Python with a CUDA-event pair around "
+                                     "each (the roofline's per-kernel times); this leg: one C call per rank"}
+        finally:
+            job.paced = False
+
     # ---- the same frame with bf16 operands (round 1's headline mode, the training chain): speed only -- its parity is in
     # parity_trained.other_modes; it misses the label clause, which is why it is not the headline ---------------------------
     bf16_leg = None
@@ -891,7 +910,7 @@ def run_gpu(args):
 
     if cx.rank == 0:
         emit(headline(cx, job, mode, mode_id, ms_step, ms_e2e, launches, totals, clocks, cpu_arm, samples,
-                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, bf16_mode=bf16_leg, full_coarse_pass=full_coarse, weak=weak, c4=c4, c5=c5, train=train)))
+                      dict(parity=parity, parity_trained=parity_trained, fp32_mode=fp32_leg, fp32_accurate_tensor_mode=tc32_leg, bf16_mode=bf16_leg, full_coarse_pass=full_coarse, render_full_call=paced_leg, weak=weak, c4=c4, c5=c5, train=train)))
     if cx.world > 1:
         cx.dist.destroy_process_group()
 
